@@ -1,0 +1,142 @@
+// Shared host-side plumbing for libdimreduce4gpu.so: error handling, the persistent device
+// context (replaces the reference's per-call DeviceContext, src/device_context.cuh:8-30, and
+// per-object cudaMalloc Matrix<T>, src/matrix.cuh:16-303) and kernel launcher prototypes.
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstddef>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+namespace dr4g {
+
+// ---------------------------------------------------------------- errors
+void set_last_error(const char* fmt, ...);
+const char* last_error();
+
+struct Error : std::runtime_error {
+  using std::runtime_error::runtime_error;
+};
+
+[[noreturn]] void fail(const char* fmt, ...);
+
+#define DR4G_CUDA(expr)                                                                      \
+  do {                                                                                       \
+    cudaError_t _e = (expr);                                                                 \
+    if (_e != cudaSuccess)                                                                   \
+      ::dr4g::fail("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+  } while (0)
+
+// ---------------------------------------------------------------- NCCL (dlopen'ed, see nccl_dyn.cu)
+struct NcclApi;
+NcclApi* nccl_api();  // throws if libnccl.so.2 cannot be loaded
+
+// ---------------------------------------------------------------- context
+constexpr int kNumStages = 6;
+
+struct Arena {
+  char* base = nullptr;
+  size_t cap = 0;
+  size_t off = 0;
+  void reset() { off = 0; }
+  // grow-only; growing synchronises the device (only happens while shapes are still warming up)
+  void reserve(size_t bytes);
+  void* take(size_t bytes, size_t align = 256);
+  template <typename T>
+  T* take_n(size_t n) { return static_cast<T*>(take(n * sizeof(T))); }
+  void release();
+};
+
+struct Ctx {
+  int device = 0;
+  int sm_count = 148;
+  cudaStream_t own_stream = nullptr;
+  cudaStream_t stream = nullptr;
+  Arena arena;        // fit/transform workspace
+  // pinned staging for the legacy host-pointer symbols
+  void* pinned[2] = {nullptr, nullptr};
+  size_t pinned_cap = 0;
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t copy_ev[2] = {nullptr, nullptr};
+  cudaEvent_t comp_ev[2] = {nullptr, nullptr};
+  // stage timing
+  cudaEvent_t stage_ev[kNumStages + 1] = {};
+  bool stage_valid = false;
+  // NCCL
+  void* comm = nullptr;
+  int rank = 0, world = 1;
+  // options
+  int gram_path = 0;          // 0 auto, 1 generic, 2 tcgen05
+  int flush_rows = 2048;      // rows between TMEM flushes in the tcgen05 Gram
+  int pilot_rows = 4096;      // rows sampled for the pilot shift
+  double jacobi_tol = 0.0;    // 0 -> per-dtype default
+  int jacobi_sweeps = 30;
+  int timing = 1;             // record per-stage events
+  // telemetry
+  int last_gram_path = 0;
+  long long launches = 0;
+  // tensor-map encoder (driver entry point fetched lazily)
+  void* encode_tiled = nullptr;
+};
+
+// ---------------------------------------------------------------- kernel launchers (one .cu each)
+// K1: column sums / sums of squares of (x - shift), double outputs (accumulated into dsum/dsumsq,
+// which the caller zeroes).
+template <typename T>
+void launch_colstats(Ctx& c, const T* dX, long long n, int d, const T* dshift, double* dsum, double* dsumsq);
+
+// Gram, generic path (DMMA, fp64 accumulate).  Accumulates the upper block triangle into dG
+// (double d x d, zeroed by caller); mirror_upper() completes the symmetric matrix.
+template <typename T>
+void launch_gram_generic(Ctx& c, const T* dX, long long n, int d, const T* dshift, double* dG);
+void launch_mirror_upper(Ctx& c, double* dG, int d);
+
+// Gram + column statistics, tcgen05 path (fp32 input, 3xTF32).  Returns false if the shape is not
+// eligible (caller falls back to the generic path).  Writes the full symmetric dG (double) and,
+// if dsum != nullptr, the column sums / sums of squares of (x - stat_shift).
+bool gram_tc_eligible(const Ctx& c, const float* dX, long long n, int d);
+void launch_gram_tc(Ctx& c, const float* dX, long long n, int d, const float* dgram_shift,
+                    const float* dstat_shift, double* dG, double* dsum, double* dsumsq);
+
+// K3: finalize.  packed = [G (d*d) | s (d) | q (d) | n (1)] doubles.
+// dsum_and_count = [column sums (d) | row count (1)] of the pilot sample (all-reduced across ranks)
+void launch_pilot_finish(Ctx& c, const double* dsum_and_count, int d, float* shift_f, double* shift_d);
+void launch_set_scalar(Ctx& c, double* dst, double value);
+void launch_center(Ctx& c, const double* packed, int d, int center, const double* shift_d,
+                   double* dC /* d x d, may alias packed G */, double* dmean, double* dtotal_var);
+
+// K4: blocked cyclic Jacobi (double).  A (dp x dp, row-major, symmetric; destroyed), V out.
+// dp must be a multiple of 2*kJacobiBlock; use jacobi_padded_dim().
+int jacobi_padded_dim(int d);
+size_t jacobi_workspace_bytes(int dp);
+void launch_jacobi(Ctx& c, double* dA, double* dV, int dp, double* dW, void* workspace, double tol, int max_sweeps);
+void launch_pad_copy(Ctx& c, const double* src, int d, double* dst, int dp);
+
+// K5: subspace iteration on the d x d Gram/covariance ("power" algorithm).
+size_t power_workspace_bytes(int d, int l);
+int power_padded_block(int l);  // rows of dW_out / dVt_out
+void launch_power(Ctx& c, const double* dC, int d, int k, int l, int n_iter, double tol, int seed,
+                  double* dW_out /* l */, double* dVt_out /* l x d rows = Ritz vectors */, void* workspace);
+
+// K6: sort descending, sign-normalise, truncate, derive outputs.
+template <typename T>
+void launch_postproc(Ctx& c, const double* dW, int nw, const double* dV, int ldv, bool vectors_in_rows,
+                     bool check_mass, int d, int k, const double* packed_n /* pointer to n */, const double* dtotal_var,
+                     const double* dmean_d, T* dQ, T* dw, T* dev, T* devr, T* dmean);
+
+// K7: projection and its inverse.
+template <typename T>
+void launch_project(Ctx& c, const T* dX, long long n, int d, int k, const T* dQ, const T* dmean,
+                    const T* dw, T* dZ, T* dU);
+template <typename T>
+void launch_inverse(Ctx& c, const T* dZ, long long n, int d, int k, const T* dQ, const T* dmean, T* dX);
+
+inline int ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }
+
+}  // namespace dr4g

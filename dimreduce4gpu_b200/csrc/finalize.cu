@@ -1,0 +1,110 @@
+// K3 - d-sized bookkeeping between the streamed pass and the eigensolve.
+//
+//  * pilot shift c = column means of a row sample (keeps the rank-1 centring correction
+//    G_c - s_c s_c^T / n free of catastrophic cancellation, SURVEY 7.3 hard part 5);
+//  * centring: C = G_c - s_c s_c^T / n  (replaces the reference's materialised 1*mu^T and X - 1*mu^T,
+//    src/pca.cu:46-49), mean = c + s_c / n (src/pca.cu:37-43), and the total variance
+//    sum_j (q_j - s_j^2/n) / max(1, n-1) that the reference gets from two more sweeps over X
+//    (src/tsvd.cu:274-290; definition follows the CPU backend, src/cpu_backend.cpp:283-296).
+// Packed layout (doubles): [G d*d | s d | q d | n 1] - the buffer that is all-reduced across ranks.
+#include "common.cuh"
+
+namespace dr4g {
+namespace {
+
+__global__ void pilot_finish_kernel(const double* __restrict__ sum, const double* __restrict__ count_or_null,
+                                    double n_rows, int d, float* __restrict__ shift_f,
+                                    double* __restrict__ shift_d) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= d) return;
+  const double cnt = count_or_null ? *count_or_null : n_rows;
+  const double m = cnt > 0 ? sum[j] / cnt : 0.0;
+  // the shift is rounded to fp32 so that the fp32 kernels and the fp64 bookkeeping use the
+  // exact same number
+  const float mf = (float)m;
+  if (shift_f) shift_f[j] = mf;
+  if (shift_d) shift_d[j] = shift_f ? (double)mf : m;
+}
+
+__global__ void set_scalar_kernel(double* dst, double v) { *dst = v; }
+
+__global__ void center_kernel(const double* __restrict__ packed, int d, int center,
+                              const double* __restrict__ shift_d, double* __restrict__ C) {
+  const double* G = packed;
+  const double* s = packed + (size_t)d * d;
+  const double n = packed[(size_t)d * d + 2 * d];
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  const int r = blockIdx.y;
+  if (c >= d) return;
+  double v = G[(size_t)r * d + c];
+  if (center && n > 0) v -= s[r] * s[c] / n;
+  C[(size_t)r * d + c] = v;
+}
+
+__global__ void moments_kernel(const double* __restrict__ packed, int d, const double* __restrict__ shift_d,
+                               double* __restrict__ mean, double* __restrict__ total_var) {
+  const double* s = packed + (size_t)d * d;
+  const double* q = s + d;
+  const double n = packed[(size_t)d * d + 2 * d];
+  __shared__ double red[256];
+  double acc = 0;
+  for (int j = threadIdx.x; j < d; j += blockDim.x) {
+    const double sj = s[j];
+    if (mean) mean[j] = (shift_d ? shift_d[j] : 0.0) + (n > 0 ? sj / n : 0.0);
+    double ss = q[j] - (n > 0 ? sj * sj / n : 0.0);  // sum of squared deviations about the mean
+    if (ss < 0) ss = 0;
+    acc += ss;
+  }
+  red[threadIdx.x] = acc;
+  __syncthreads();
+  for (int o = blockDim.x / 2; o > 0; o >>= 1) {
+    if (threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    const double denom = n - 1 > 1 ? n - 1 : 1;  // max(1, n-1), src/cpu_backend.cpp:279
+    double tv = red[0] / denom;
+    if (!(tv > 0)) tv = 1.0;                      // src/cpu_backend.cpp:296
+    *total_var = tv;
+  }
+}
+
+__global__ void pad_copy_kernel(const double* __restrict__ src, int d, double* __restrict__ dst, int dp) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  const int r = blockIdx.y;
+  if (c >= dp) return;
+  dst[(size_t)r * dp + c] = (r < d && c < d) ? src[(size_t)r * d + c] : 0.0;
+}
+
+}  // namespace
+
+void launch_pilot_finish(Ctx& c, const double* dsum_and_count, int d, float* shift_f, double* shift_d) {
+  pilot_finish_kernel<<<ceil_div(d, 128), 128, 0, c.stream>>>(dsum_and_count, dsum_and_count + d, 0.0, d,
+                                                               shift_f, shift_d);
+  c.launches++;
+  DR4G_CUDA(cudaGetLastError());
+}
+
+void launch_set_scalar(Ctx& c, double* dst, double value) {
+  set_scalar_kernel<<<1, 1, 0, c.stream>>>(dst, value);
+  c.launches++;
+  DR4G_CUDA(cudaGetLastError());
+}
+
+void launch_center(Ctx& c, const double* packed, int d, int center, const double* shift_d, double* dC,
+                   double* dmean, double* dtotal_var) {
+  dim3 grid(ceil_div(d, 128), d);
+  center_kernel<<<grid, 128, 0, c.stream>>>(packed, d, center, shift_d, dC);
+  moments_kernel<<<1, 256, 0, c.stream>>>(packed, d, shift_d, dmean, dtotal_var);
+  c.launches += 2;
+  DR4G_CUDA(cudaGetLastError());
+}
+
+void launch_pad_copy(Ctx& c, const double* src, int d, double* dst, int dp) {
+  dim3 grid(ceil_div(dp, 128), dp);
+  pad_copy_kernel<<<grid, 128, 0, c.stream>>>(src, d, dst, dp);
+  c.launches++;
+  DR4G_CUDA(cudaGetLastError());
+}
+
+}  // namespace dr4g

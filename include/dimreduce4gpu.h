@@ -1,0 +1,141 @@
+/* dimreduce4gpu.h - C ABI of libdimreduce4gpu.so (B200 / sm_100a build).
+ *
+ * This is the drop-in boundary for the PCA / TruncatedSVD fit+transform hot path.  Everything is
+ * `extern "C"`, plain pointers and sizes; no C++/torch types cross it.
+ *
+ * Part 1 ("legacy symbols") is what the reference's ctypes layer binds today and is preserved
+ * bit-for-bit:
+ *     params                  reference include/tsvd.h:24-35, include/pca.h:24-35,
+ *                             dimreduce4gpu/lib_dimreduce4gpu.py:6-18 (ctypes mirror)
+ *     truncated_svd_float     reference include/tsvd.h:48   (src/tsvd.cu:427-438)
+ *     truncated_svd_double    reference include/tsvd.h:49   (src/tsvd.cu:440-452)
+ *     pca_float               reference include/pca.h:48    (src/pca.cu:22-62)
+ *     pca_double              reference include/pca.h:49    (src/pca.cu:76-116)
+ *   The two *_float symbols are the reference's CI contract (ci/expected_symbols.txt:4-5).
+ *   Layout convention: the one the reference's Python wrapper and CPU backend use
+ *   (dimreduce4gpu/truncated_svd.py:72-86, src/cpu_backend.cpp:340-345): X is row-major
+ *   X_n (samples) x X_m (features) in HOST memory; Q is k x X_m, U and X_transformed are X_n x k.
+ *   Output conventions are the CPU backend's (src/cpu_backend.cpp:277-332), see DESIGN.md.
+ *
+ * Part 2 ("dr4g_* symbols") is additive: device-resident, row-sharded operation that the
+ * reference does not have (it is single-device, src/tsvd.cu:429).  The legacy symbols are thin
+ * wrappers over it (H2D -> fit -> transform -> D2H).
+ *
+ * Error convention: the legacy symbols return void like the reference; on failure they print one
+ * line to stderr and leave the caller's (pre-zeroed) outputs untouched, never exit() (the reference
+ * calls exit(-1), src/utils.cuh:36-50).  dr4g_last_error() returns the thread's last message.
+ * dr4g_* functions return 0 on success, non-zero on failure.
+ */
+#ifndef DIMREDUCE4GPU_H
+#define DIMREDUCE4GPU_H
+
+#include <stdbool.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* 48 bytes, align 8: X_n@0 X_m@4 k@8 algorithm@16 n_iter@24 random_state@28 tol@32 verbose@36
+ * gpu_id@40 whiten@44.  Passed BY VALUE.  `algorithm` is borrowed for the call only. */
+typedef struct params {
+  int X_n;          /* samples (rows)     */
+  int X_m;          /* features (columns) */
+  int k;            /* components         */
+  char* algorithm;  /* "cusolver" -> exact eigensolve; anything else -> "power" (src/tsvd.cu:457-471) */
+  int n_iter;
+  int random_state;
+  float tol;
+  int verbose;
+  int gpu_id;
+  bool whiten;      /* accepted, ignored: the CPU backend (the parity oracle) ignores it */
+} params;
+
+/* ---------------------------------------------------------------- Part 1: legacy symbols */
+void truncated_svd_float(const float* X, float* Q, float* w, float* U, float* X_transformed,
+                         float* explained_variance, float* explained_variance_ratio, params p);
+void truncated_svd_double(const double* X, double* Q, double* w, double* U, double* X_transformed,
+                          double* explained_variance, double* explained_variance_ratio, params p);
+void pca_float(const float* X, float* Q, float* w, float* U, float* X_transformed,
+               float* explained_variance, float* explained_variance_ratio, float* mean, params p);
+void pca_double(const double* X, double* Q, double* w, double* U, double* X_transformed,
+                double* explained_variance, double* explained_variance_ratio, double* mean, params p);
+
+/* ---------------------------------------------------------------- Part 2: dr4g_* symbols */
+typedef struct dr4g_ctx dr4g_ctx;
+
+/* Thread-local message of the last failure on this thread ("" if none). */
+const char* dr4g_last_error(void);
+/* ABI version of this header (bumped when a dr4g_* signature changes). */
+int dr4g_abi_version(void);
+
+/* Persistent per-device context: private stream, workspace arena, optional NCCL communicator.
+ * Replaces the reference's per-call DeviceContext (src/device_context.cuh:8-30). */
+dr4g_ctx* dr4g_ctx_create(int device);
+void dr4g_ctx_destroy(dr4g_ctx* ctx);
+/* Run this context's work on a caller-owned CUDA stream (a cudaStream_t; NULL -> private stream). */
+int dr4g_ctx_set_stream(dr4g_ctx* ctx, void* cuda_stream);
+/* Block until everything enqueued on the context's stream is done; returns deferred errors. */
+int dr4g_sync(dr4g_ctx* ctx);
+/* Tunables / test hooks.  Keys: "gram_path" (0 auto, 1 generic DMMA kernel, 2 tcgen05 kernel),
+ * "flush_rows" (rows between TMEM accumulator flushes), "pilot_rows", "jacobi_tol", "jacobi_sweeps". */
+int dr4g_set_option(dr4g_ctx* ctx, const char* key, double value);
+
+/* Row-sharded operation: rank 0 obtains a 128-byte NCCL unique id, the host layer ships it to
+ * every rank, each rank calls dr4g_comm_init.  After that dr4g_fit_* all-reduces the packed
+ * [Gram | column sums | column sums of squares | row count] partials once per fit. */
+int dr4g_nccl_unique_id(void* out128);
+int dr4g_comm_init(dr4g_ctx* ctx, const void* unique_id128, int rank, int world);
+int dr4g_comm_world(dr4g_ctx* ctx);
+
+/* fit on a device-resident row shard.  dX: n_local x d row-major on ctx's device.  center=1 ->
+ * PCA (covariance of centred data), 0 -> TruncatedSVD.  p supplies algorithm / n_iter /
+ * random_state / tol / verbose (X_n, X_m, k, gpu_id in p are ignored here).  Outputs are device
+ * pointers: dQ k x d (components_), dw k (singular_values_), dev k, devr k, dmean d (may be NULL
+ * when center=0).  Asynchronous on ctx's stream. */
+int dr4g_fit_float(dr4g_ctx* ctx, const float* dX, long long n_local, int d, int k, int center,
+                   params p, float* dQ, float* dw, float* dev, float* devr, float* dmean);
+int dr4g_fit_double(dr4g_ctx* ctx, const double* dX, long long n_local, int d, int k, int center,
+                    params p, double* dQ, double* dw, double* dev, double* devr, double* dmean);
+
+/* transform on a device-resident row shard (no communication):
+ *   dZ[n x k] = (dX - dmean) * dQ^T   (dmean NULL -> no centring, the reference's transform,
+ *                                      dimreduce4gpu/truncated_svd.py:116-118)
+ *   dU[n x k] = dZ / dw               (only if dU and dw are non-NULL; 0 where dw == 0,
+ *                                      src/tsvd.cu:171-175) */
+int dr4g_transform_float(dr4g_ctx* ctx, const float* dX, long long n, int d, int k, const float* dQ,
+                         const float* dmean, const float* dw, float* dZ, float* dU);
+int dr4g_transform_double(dr4g_ctx* ctx, const double* dX, long long n, int d, int k, const double* dQ,
+                          const double* dmean, const double* dw, double* dZ, double* dU);
+/* inverse_transform: dX[n x d] = dZ * dQ (+ dmean).  Not in the reference. */
+int dr4g_inverse_transform_float(dr4g_ctx* ctx, const float* dZ, long long n, int d, int k,
+                                 const float* dQ, const float* dmean, float* dX);
+int dr4g_inverse_transform_double(dr4g_ctx* ctx, const double* dZ, long long n, int d, int k,
+                                  const double* dQ, const double* dmean, double* dX);
+
+/* Building blocks, exported for parity tests and micro-benchmarks (device pointers).
+ *   colstats: per-column sum and sum of squares of (x - shift) in double; shift may be NULL.
+ *   gram:     dG[d x d] (double, row-major, full symmetric) = (X - shift)^T (X - shift).
+ *   eigh:     symmetric eigen-decomposition by blocked cyclic Jacobi; dA (d x d) is destroyed,
+ *             dW gets the d eigenvalues (unsorted), dV (d x d row-major) eigenvectors in columns. */
+int dr4g_colstats_float(dr4g_ctx* ctx, const float* dX, long long n, int d, const float* dshift,
+                        double* dsum, double* dsumsq);
+int dr4g_colstats_double(dr4g_ctx* ctx, const double* dX, long long n, int d, const double* dshift,
+                         double* dsum, double* dsumsq);
+int dr4g_gram_float(dr4g_ctx* ctx, const float* dX, long long n, int d, const float* dshift, double* dG);
+int dr4g_gram_double(dr4g_ctx* ctx, const double* dX, long long n, int d, const double* dshift, double* dG);
+int dr4g_eigh_double(dr4g_ctx* ctx, double* dA, int d, double* dW, double* dV);
+
+/* Per-stage device times (ms) of the last dr4g_fit_* on this context, valid after dr4g_sync:
+ * [0] pilot shift, [1] Gram + column stats, [2] partial reduce + allreduce + centring,
+ * [3] eigensolve (Jacobi or subspace iteration), [4] sort/flip/outputs, [5] total.
+ * Returns the number of entries written (<= n). */
+int dr4g_stage_times(dr4g_ctx* ctx, double* ms, int n);
+/* Which Gram kernel the last fit used (1 generic DMMA, 2 tcgen05), and launches it issued. */
+int dr4g_last_gram_path(dr4g_ctx* ctx);
+long long dr4g_launch_count(dr4g_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DIMREDUCE4GPU_H */
