@@ -1,0 +1,240 @@
+"""Device-resident, row-sharded operation on top of the dr4g_* symbols of include/dimreduce4gpu.h.
+
+The reference has no such layer: it uploads X on every call (src/tsvd.cu:430-431) and is single
+device (src/tsvd.cu:429).  Here X stays in HBM as a torch CUDA tensor (torch is only the
+allocator / stream / rendezvous plumbing; every kernel is in libdimreduce4gpu.so).
+
+One process per GPU: ``DeviceContext.init_comm_from_torch()`` ships rank 0's NCCL unique id through
+``torch.distributed`` and gives the context its own communicator; ``fit`` then all-reduces the
+packed [Gram | column sums | sums of squares | row count] once."""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional
+
+import numpy as np
+
+from ._native import last_error, load_library
+from .lib_dimreduce4gpu import params
+
+
+def _check(rc: int, what: str) -> None:
+    if rc != 0:
+        raise RuntimeError(f"{what} failed: {last_error()}")
+
+
+def _suffix(t) -> str:
+    import torch
+
+    if t.dtype == torch.float32:
+        return "float"
+    if t.dtype == torch.float64:
+        return "double"
+    raise TypeError(f"float32 or float64 expected, got {t.dtype}")
+
+
+def _need_cuda_contig(t, name: str, device: int):
+    if not t.is_cuda or t.device.index != device:
+        raise ValueError(f"{name} must live on cuda:{device}")
+    if not t.is_contiguous():
+        raise ValueError(f"{name} must be C-contiguous (row-major)")
+    return t
+
+
+class DeviceContext:
+    """Persistent per-device context (stream, workspace arena, optional NCCL communicator)."""
+
+    def __init__(self, device: int = 0) -> None:
+        self._lib = load_library()
+        self.device = int(device)
+        self._h = self._lib.dr4g_ctx_create(self.device)
+        if not self._h:
+            raise RuntimeError(f"dr4g_ctx_create({device}) failed: {last_error()}")
+        self.rank, self.world = 0, 1
+
+    # ------------------------------------------------------------------ lifecycle
+    def close(self) -> None:
+        if getattr(self, "_h", None):
+            self._lib.dr4g_ctx_destroy(self._h)
+            self._h = None
+
+    def __del__(self):  # pragma: no cover
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def _on_torch_stream(self) -> None:
+        import torch
+
+        s = torch.cuda.current_stream(self.device).cuda_stream
+        _check(self._lib.dr4g_ctx_set_stream(self._h, ctypes.c_void_p(s)), "dr4g_ctx_set_stream")
+
+    def set_option(self, key: str, value: float) -> None:
+        _check(self._lib.dr4g_set_option(self._h, key.encode(), float(value)), f"dr4g_set_option({key})")
+
+    def sync(self) -> None:
+        _check(self._lib.dr4g_sync(self._h), "dr4g_sync")
+
+    # ------------------------------------------------------------------ multi-GPU
+    def init_comm(self, unique_id: bytes, rank: int, world: int) -> None:
+        buf = ctypes.create_string_buffer(bytes(unique_id), 128)
+        _check(self._lib.dr4g_comm_init(self._h, buf, int(rank), int(world)), "dr4g_comm_init")
+        self.rank, self.world = int(rank), int(world)
+
+    def new_unique_id(self) -> bytes:
+        buf = ctypes.create_string_buffer(128)
+        _check(self._lib.dr4g_nccl_unique_id(buf), "dr4g_nccl_unique_id")
+        return buf.raw
+
+    def init_comm_from_torch(self) -> None:
+        """Rendezvous through an initialised torch.distributed group (any backend)."""
+        import torch
+        import torch.distributed as dist
+
+        rank, world = dist.get_rank(), dist.get_world_size()
+        if world == 1:
+            return
+        uid = [self.new_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        with torch.cuda.device(self.device):
+            self.init_comm(uid[0], rank, world)
+
+    # ------------------------------------------------------------------ fit / transform
+    def fit(self, X, n_components: int, center: bool, algorithm: str = "cusolver", n_iter: int = 5,
+            random_state: int = 0, tol: float = 1e-5, verbose: bool = False, out: Optional[dict] = None) -> dict:
+        """X: (n_local, d) CUDA tensor, this rank's row shard.  Returns device tensors
+        components (k,d), singular_values, explained_variance, explained_variance_ratio (k,), mean (d,)|None.
+        Asynchronous on the current torch stream."""
+        import torch
+
+        _need_cuda_contig(X, "X", self.device)
+        if X.dim() != 2:
+            raise ValueError("X must be 2-D (n_samples, n_features)")
+        n, d = X.shape
+        k = min(int(n_components), d) if self.world > 1 else min(int(n_components), n, d)
+        sfx = _suffix(X)
+        if out is None:
+            z = lambda *s: torch.empty(*s, dtype=X.dtype, device=X.device)  # noqa: E731
+            out = dict(components=z(k, d), singular_values=z(k), explained_variance=z(k),
+                       explained_variance_ratio=z(k), mean=z(d) if center else None)
+        p = params()
+        p.X_n, p.X_m, p.k = min(n, 2**31 - 1), d, k
+        p.algorithm = algorithm.encode("utf-8")
+        p.n_iter, p.random_state, p.tol = int(n_iter), int(random_state) & 0x7FFFFFFF, float(tol)
+        p.verbose, p.gpu_id, p.whiten = int(bool(verbose)), self.device, False
+        self._on_torch_stream()
+        mean_ptr = out["mean"].data_ptr() if center else None
+        rc = getattr(self._lib, f"dr4g_fit_{sfx}")(
+            self._h, X.data_ptr(), n, d, k, 1 if center else 0, p, out["components"].data_ptr(),
+            out["singular_values"].data_ptr(), out["explained_variance"].data_ptr(),
+            out["explained_variance_ratio"].data_ptr(), mean_ptr)
+        _check(rc, f"dr4g_fit_{sfx}")
+        return out
+
+    def transform(self, X, components, mean=None, singular_values=None, want_u: bool = False, out=None, out_u=None):
+        """Z = (X - mean) @ components.T on this rank's rows (no communication); optionally U = Z / sigma."""
+        import torch
+
+        _need_cuda_contig(X, "X", self.device)
+        _need_cuda_contig(components, "components", self.device)
+        n, d = X.shape
+        k = components.shape[0]
+        if components.shape[1] != d or components.dtype != X.dtype:
+            raise ValueError("components must be (k, n_features) with X's dtype")
+        sfx = _suffix(X)
+        Z = out if out is not None else torch.empty(n, k, dtype=X.dtype, device=X.device)
+        U = None
+        if want_u:
+            if singular_values is None:
+                raise ValueError("want_u needs singular_values")
+            U = out_u if out_u is not None else torch.empty(n, k, dtype=X.dtype, device=X.device)
+        self._on_torch_stream()
+        rc = getattr(self._lib, f"dr4g_transform_{sfx}")(
+            self._h, X.data_ptr(), n, d, k, components.data_ptr(), mean.data_ptr() if mean is not None else None,
+            singular_values.data_ptr() if want_u else None, Z.data_ptr(), U.data_ptr() if want_u else None)
+        _check(rc, f"dr4g_transform_{sfx}")
+        return (Z, U) if want_u else Z
+
+    def inverse_transform(self, Z, components, mean=None, out=None):
+        import torch
+
+        _need_cuda_contig(Z, "Z", self.device)
+        _need_cuda_contig(components, "components", self.device)
+        n, k = Z.shape
+        d = components.shape[1]
+        if components.shape[0] != k or components.dtype != Z.dtype:
+            raise ValueError("components must be (k, n_features) with Z's dtype")
+        sfx = _suffix(Z)
+        X = out if out is not None else torch.empty(n, d, dtype=Z.dtype, device=Z.device)
+        self._on_torch_stream()
+        rc = getattr(self._lib, f"dr4g_inverse_transform_{sfx}")(
+            self._h, Z.data_ptr(), n, d, k, components.data_ptr(), mean.data_ptr() if mean is not None else None,
+            X.data_ptr())
+        _check(rc, f"dr4g_inverse_transform_{sfx}")
+        return X
+
+    # ------------------------------------------------------------------ building blocks
+    def colstats(self, X, shift=None):
+        import torch
+
+        _need_cuda_contig(X, "X", self.device)
+        n, d = X.shape
+        s = torch.empty(d, dtype=torch.float64, device=X.device)
+        q = torch.empty(d, dtype=torch.float64, device=X.device)
+        self._on_torch_stream()
+        rc = getattr(self._lib, f"dr4g_colstats_{_suffix(X)}")(
+            self._h, X.data_ptr(), n, d, shift.data_ptr() if shift is not None else None, s.data_ptr(), q.data_ptr())
+        _check(rc, "dr4g_colstats")
+        return s, q
+
+    def gram(self, X, shift=None):
+        import torch
+
+        _need_cuda_contig(X, "X", self.device)
+        n, d = X.shape
+        G = torch.empty(d, d, dtype=torch.float64, device=X.device)
+        self._on_torch_stream()
+        rc = getattr(self._lib, f"dr4g_gram_{_suffix(X)}")(
+            self._h, X.data_ptr(), n, d, shift.data_ptr() if shift is not None else None, G.data_ptr())
+        _check(rc, "dr4g_gram")
+        return G
+
+    def eigh(self, A):
+        """Symmetric eigendecomposition (fp64, blocked Jacobi).  Returns (w unsorted, V columns)."""
+        import torch
+
+        _need_cuda_contig(A, "A", self.device)
+        if A.dtype != torch.float64 or A.dim() != 2 or A.shape[0] != A.shape[1]:
+            raise ValueError("A must be a square float64 matrix")
+        d = A.shape[0]
+        work = A.clone()
+        w = torch.empty(d, dtype=torch.float64, device=A.device)
+        V = torch.empty(d, d, dtype=torch.float64, device=A.device)
+        self._on_torch_stream()
+        _check(self._lib.dr4g_eigh_double(self._h, work.data_ptr(), d, w.data_ptr(), V.data_ptr()), "dr4g_eigh_double")
+        return w, V
+
+    # ------------------------------------------------------------------ telemetry
+    def stage_times(self) -> Optional[dict]:
+        """Per-stage device ms of the last fit (call after sync)."""
+        buf = (ctypes.c_double * 6)()
+        m = self._lib.dr4g_stage_times(self._h, buf, 6)
+        if m < 6:
+            return None
+        names = ("pilot", "gram", "reduce_center", "eigensolve", "outputs", "total")
+        return dict(zip(names, np.frombuffer(buf, dtype=np.float64).tolist()))
+
+    @property
+    def last_gram_path(self) -> str:
+        return {0: "none", 1: "generic_dmma", 2: "tcgen05"}[int(self._lib.dr4g_last_gram_path(self._h))]
+
+    @property
+    def launch_count(self) -> int:
+        return int(self._lib.dr4g_launch_count(self._h))

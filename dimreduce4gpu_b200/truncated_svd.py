@@ -1,0 +1,197 @@
+"""TruncatedSVD estimator - same surface as the reference (dimreduce4gpu/truncated_svd.py:19-118).
+
+Constructor arguments, ``fit`` / ``fit_transform`` / ``transform`` and the attributes
+``components_``, ``singular_values_``, ``explained_variance_``, ``explained_variance_ratio_`` and
+the private ``_U`` are preserved.  Additions: ``inverse_transform`` (absent from the reference,
+SURVEY fact 8; sklearn semantics), ``transform`` runs on the GPU (reference: host numpy,
+truncated_svd.py:116-118), torch CUDA tensors are accepted and stay on the device, and
+``dtype="float64"`` keeps doubles (the reference always down-casts, truncated_svd.py:72)."""
+from __future__ import annotations
+
+import ctypes
+from typing import Literal, Optional
+
+import numpy as np
+
+from ._backend import select_backend
+from .lib_dimreduce4gpu import _load_tsvd_lib, params
+
+Backend = Literal["auto", "gpu", "cpu"]
+
+_contexts: dict[int, "object"] = {}
+
+
+def _device_context(gpu_id: int):
+    """One persistent DeviceContext per device for the estimator-level device paths."""
+    from .device import DeviceContext
+
+    ctx = _contexts.get(gpu_id)
+    if ctx is None:
+        ctx = _contexts[gpu_id] = DeviceContext(gpu_id)
+    return ctx
+
+
+def _is_torch_cuda(X) -> bool:
+    return type(X).__module__.startswith("torch") and getattr(X, "is_cuda", False)
+
+
+def _ptr(x: np.ndarray):
+    ct = ctypes.c_float if x.dtype == np.float32 else ctypes.c_double
+    return x.ctypes.data_as(ctypes.POINTER(ct))
+
+
+def _densify(X):
+    if type(X).__module__.startswith("scipy.sparse"):
+        return X.toarray()  # reference densifies CSR on the host (truncated_svd.py:67-70)
+    return X
+
+
+class TruncatedSVD:
+    """Truncated SVD on the B200 native backend."""
+
+    _center = False
+    _entry = "tsvd"
+
+    def __init__(self, n_components: int = 2, algorithm: str = "power", n_iter: int = 5,
+                 random_state: Optional[int] = None, tol: float = 1e-5, verbose: bool = False, gpu_id: int = 0,
+                 backend: Backend = "auto", *, dtype: Optional[str] = None) -> None:
+        self.n_components = int(n_components)
+        self.algorithm = str(algorithm)
+        self.n_iter = int(n_iter)
+        self.random_state = int(random_state) if random_state is not None else int(np.random.randint(0, 2**31 - 1))
+        self.tol = float(tol)
+        self.verbose = bool(verbose)
+        self.gpu_id = int(gpu_id)
+        self.backend: Backend = backend
+        self.dtype = np.dtype(dtype if dtype is not None else np.float32)
+        if self.dtype not in (np.dtype(np.float32), np.dtype(np.float64)):
+            raise ValueError("dtype must be float32 or float64")
+        self._Q = None
+        self._w = None
+        self._U = None
+        self.explained_variance_ = None
+        self.explained_variance_ratio_ = None
+        self.mean_ = None
+
+    # ------------------------------------------------------------------ attributes
+    @property
+    def components_(self):
+        if self._Q is None:
+            raise AttributeError("components_ is not available before fit/fit_transform.")
+        return self._Q
+
+    @property
+    def singular_values_(self):
+        if self._w is None:
+            raise AttributeError("singular_values_ is not available before fit/fit_transform.")
+        return self._w
+
+    # ------------------------------------------------------------------ fit
+    def _params(self, n: int, m: int, k: int) -> params:
+        p = params()
+        p.X_n, p.X_m, p.k = n, m, k
+        p.algorithm = self.algorithm.encode("utf-8")
+        p.n_iter, p.random_state, p.tol = self.n_iter, self.random_state, float(self.tol)
+        p.verbose, p.gpu_id = (1 if self.verbose else 0), self.gpu_id
+        p.whiten = bool(getattr(self, "whiten", False))
+        return p
+
+    def fit(self, X, y=None):
+        if _is_torch_cuda(X):
+            self._fit_device(X, want_scores=False)
+        else:
+            self.fit_transform(X)
+        return self
+
+    def fit_transform(self, X):
+        select_backend(self.backend)
+        if _is_torch_cuda(X):
+            return self._fit_device(X, want_scores=True)
+        X = np.ascontiguousarray(_densify(X), dtype=self.dtype)
+        if X.ndim != 2:
+            raise ValueError("X must be 2-D (n_samples, n_features)")
+        n, m = X.shape
+        k = min(self.n_components, n, m)
+        dt = self.dtype
+        Q = np.zeros((k, m), dtype=dt)
+        w = np.zeros((k,), dtype=dt)
+        U = np.zeros((n, k), dtype=dt)
+        Xt = np.zeros((n, k), dtype=dt)
+        ev = np.zeros((k,), dtype=dt)
+        evr = np.zeros((k,), dtype=dt)
+        mean = np.zeros((m,), dtype=dt)
+        p = self._params(n, m, k)
+        sfx = "float" if dt == np.float32 else "double"
+        from ._native import last_error
+
+        if self._center:
+            from .lib_dimreduce4gpu import _load_pca_lib
+
+            _load_pca_lib(sfx)(_ptr(X), _ptr(Q), _ptr(w), _ptr(U), _ptr(Xt), _ptr(ev), _ptr(evr), _ptr(mean), p)
+        else:
+            _load_tsvd_lib(sfx)(_ptr(X), _ptr(Q), _ptr(w), _ptr(U), _ptr(Xt), _ptr(ev), _ptr(evr), p)
+        err = last_error()
+        if err:  # the C symbols are void like the reference's; the message is out of band
+            raise RuntimeError(f"libdimreduce4gpu: {err}")
+        self._Q, self._w, self._U = Q, w, U
+        self.explained_variance_, self.explained_variance_ratio_ = ev, evr
+        self.mean_ = mean if self._center else None
+        return Xt
+
+    def _fit_device(self, X, want_scores: bool):
+        """X is a torch CUDA tensor: nothing leaves the device except the k- and d-sized results."""
+        ctx = _device_context(X.device.index)
+        res = ctx.fit(X, self.n_components, center=self._center, algorithm=self.algorithm, n_iter=self.n_iter,
+                      random_state=self.random_state, tol=self.tol, verbose=self.verbose)
+        self._Q_dev, self._w_dev, self._mean_dev = res["components"], res["singular_values"], res["mean"]
+        Z = None
+        if want_scores:
+            Z = ctx.transform(X, res["components"], mean=res["mean"])
+        self._Q = res["components"].cpu().numpy()
+        self._w = res["singular_values"].cpu().numpy()
+        self.explained_variance_ = res["explained_variance"].cpu().numpy()
+        self.explained_variance_ratio_ = res["explained_variance_ratio"].cpu().numpy()
+        self.mean_ = res["mean"].cpu().numpy() if self._center else None
+        self._U = None
+        return Z
+
+    # ------------------------------------------------------------------ transform / inverse
+    def _to_device(self, A, dtype):
+        import torch
+
+        if _is_torch_cuda(A):
+            return A.contiguous().to(dtype), True
+        a = np.ascontiguousarray(_densify(A), dtype=np.float32 if dtype == torch.float32 else np.float64)
+        return torch.from_numpy(a).to(f"cuda:{self.gpu_id}"), False
+
+    def transform(self, X, center: bool = False):
+        """X @ components_.T on the GPU.  ``center=False`` reproduces the reference, whose transform
+        never subtracts the mean, not even for PCA (truncated_svd.py:116-118); ``center=True``
+        gives the sklearn behaviour (X - mean_) @ components_.T."""
+        import torch
+
+        select_backend(self.backend)
+        Q = self.components_
+        tdt = torch.float32 if Q.dtype == np.float32 else torch.float64
+        Xd, on_dev = self._to_device(X, tdt)
+        ctx = _device_context(Xd.device.index)
+        Qd = torch.from_numpy(np.ascontiguousarray(Q)).to(Xd.device)
+        md = None
+        if center and self.mean_ is not None:
+            md = torch.from_numpy(np.ascontiguousarray(self.mean_)).to(Xd.device)
+        Z = ctx.transform(Xd, Qd, mean=md)
+        return Z if on_dev else Z.cpu().numpy()
+
+    def inverse_transform(self, Z):
+        """Z @ components_ (+ mean_ for PCA).  Not in the reference; sklearn semantics."""
+        import torch
+
+        select_backend(self.backend)
+        Q = self.components_
+        tdt = torch.float32 if Q.dtype == np.float32 else torch.float64
+        Zd, on_dev = self._to_device(Z, tdt)
+        ctx = _device_context(Zd.device.index)
+        Qd = torch.from_numpy(np.ascontiguousarray(Q)).to(Zd.device)
+        md = torch.from_numpy(np.ascontiguousarray(self.mean_)).to(Zd.device) if self.mean_ is not None else None
+        X = ctx.inverse_transform(Zd, Qd, mean=md)
+        return X if on_dev else X.cpu().numpy()

@@ -32,6 +32,12 @@
 #include <stdbool.h>
 #include <stdint.h>
 
+#if defined(__GNUC__)
+#define DR4G_EXPORT __attribute__((visibility("default")))
+#else
+#define DR4G_EXPORT
+#endif
+
 #ifdef __cplusplus
 extern "C" {
 #endif
@@ -52,50 +58,50 @@ typedef struct params {
 } params;
 
 /* ---------------------------------------------------------------- Part 1: legacy symbols */
-void truncated_svd_float(const float* X, float* Q, float* w, float* U, float* X_transformed,
+DR4G_EXPORT void truncated_svd_float(const float* X, float* Q, float* w, float* U, float* X_transformed,
                          float* explained_variance, float* explained_variance_ratio, params p);
-void truncated_svd_double(const double* X, double* Q, double* w, double* U, double* X_transformed,
+DR4G_EXPORT void truncated_svd_double(const double* X, double* Q, double* w, double* U, double* X_transformed,
                           double* explained_variance, double* explained_variance_ratio, params p);
-void pca_float(const float* X, float* Q, float* w, float* U, float* X_transformed,
+DR4G_EXPORT void pca_float(const float* X, float* Q, float* w, float* U, float* X_transformed,
                float* explained_variance, float* explained_variance_ratio, float* mean, params p);
-void pca_double(const double* X, double* Q, double* w, double* U, double* X_transformed,
+DR4G_EXPORT void pca_double(const double* X, double* Q, double* w, double* U, double* X_transformed,
                 double* explained_variance, double* explained_variance_ratio, double* mean, params p);
 
 /* ---------------------------------------------------------------- Part 2: dr4g_* symbols */
 typedef struct dr4g_ctx dr4g_ctx;
 
 /* Thread-local message of the last failure on this thread ("" if none). */
-const char* dr4g_last_error(void);
+DR4G_EXPORT const char* dr4g_last_error(void);
 /* ABI version of this header (bumped when a dr4g_* signature changes). */
-int dr4g_abi_version(void);
+DR4G_EXPORT int dr4g_abi_version(void);
 
 /* Persistent per-device context: private stream, workspace arena, optional NCCL communicator.
  * Replaces the reference's per-call DeviceContext (src/device_context.cuh:8-30). */
-dr4g_ctx* dr4g_ctx_create(int device);
-void dr4g_ctx_destroy(dr4g_ctx* ctx);
+DR4G_EXPORT dr4g_ctx* dr4g_ctx_create(int device);
+DR4G_EXPORT void dr4g_ctx_destroy(dr4g_ctx* ctx);
 /* Run this context's work on a caller-owned CUDA stream (a cudaStream_t; NULL -> private stream). */
-int dr4g_ctx_set_stream(dr4g_ctx* ctx, void* cuda_stream);
+DR4G_EXPORT int dr4g_ctx_set_stream(dr4g_ctx* ctx, void* cuda_stream);
 /* Block until everything enqueued on the context's stream is done; returns deferred errors. */
-int dr4g_sync(dr4g_ctx* ctx);
+DR4G_EXPORT int dr4g_sync(dr4g_ctx* ctx);
 /* Tunables / test hooks.  Keys: "gram_path" (0 auto, 1 generic DMMA kernel, 2 tcgen05 kernel),
  * "flush_rows" (rows between TMEM accumulator flushes), "pilot_rows", "jacobi_tol", "jacobi_sweeps". */
-int dr4g_set_option(dr4g_ctx* ctx, const char* key, double value);
+DR4G_EXPORT int dr4g_set_option(dr4g_ctx* ctx, const char* key, double value);
 
 /* Row-sharded operation: rank 0 obtains a 128-byte NCCL unique id, the host layer ships it to
  * every rank, each rank calls dr4g_comm_init.  After that dr4g_fit_* all-reduces the packed
  * [Gram | column sums | column sums of squares | row count] partials once per fit. */
-int dr4g_nccl_unique_id(void* out128);
-int dr4g_comm_init(dr4g_ctx* ctx, const void* unique_id128, int rank, int world);
-int dr4g_comm_world(dr4g_ctx* ctx);
+DR4G_EXPORT int dr4g_nccl_unique_id(void* out128);
+DR4G_EXPORT int dr4g_comm_init(dr4g_ctx* ctx, const void* unique_id128, int rank, int world);
+DR4G_EXPORT int dr4g_comm_world(dr4g_ctx* ctx);
 
 /* fit on a device-resident row shard.  dX: n_local x d row-major on ctx's device.  center=1 ->
  * PCA (covariance of centred data), 0 -> TruncatedSVD.  p supplies algorithm / n_iter /
  * random_state / tol / verbose (X_n, X_m, k, gpu_id in p are ignored here).  Outputs are device
  * pointers: dQ k x d (components_), dw k (singular_values_), dev k, devr k, dmean d (may be NULL
  * when center=0).  Asynchronous on ctx's stream. */
-int dr4g_fit_float(dr4g_ctx* ctx, const float* dX, long long n_local, int d, int k, int center,
+DR4G_EXPORT int dr4g_fit_float(dr4g_ctx* ctx, const float* dX, long long n_local, int d, int k, int center,
                    params p, float* dQ, float* dw, float* dev, float* devr, float* dmean);
-int dr4g_fit_double(dr4g_ctx* ctx, const double* dX, long long n_local, int d, int k, int center,
+DR4G_EXPORT int dr4g_fit_double(dr4g_ctx* ctx, const double* dX, long long n_local, int d, int k, int center,
                     params p, double* dQ, double* dw, double* dev, double* devr, double* dmean);
 
 /* transform on a device-resident row shard (no communication):
@@ -103,14 +109,14 @@ int dr4g_fit_double(dr4g_ctx* ctx, const double* dX, long long n_local, int d, i
  *                                      dimreduce4gpu/truncated_svd.py:116-118)
  *   dU[n x k] = dZ / dw               (only if dU and dw are non-NULL; 0 where dw == 0,
  *                                      src/tsvd.cu:171-175) */
-int dr4g_transform_float(dr4g_ctx* ctx, const float* dX, long long n, int d, int k, const float* dQ,
+DR4G_EXPORT int dr4g_transform_float(dr4g_ctx* ctx, const float* dX, long long n, int d, int k, const float* dQ,
                          const float* dmean, const float* dw, float* dZ, float* dU);
-int dr4g_transform_double(dr4g_ctx* ctx, const double* dX, long long n, int d, int k, const double* dQ,
+DR4G_EXPORT int dr4g_transform_double(dr4g_ctx* ctx, const double* dX, long long n, int d, int k, const double* dQ,
                           const double* dmean, const double* dw, double* dZ, double* dU);
 /* inverse_transform: dX[n x d] = dZ * dQ (+ dmean).  Not in the reference. */
-int dr4g_inverse_transform_float(dr4g_ctx* ctx, const float* dZ, long long n, int d, int k,
+DR4G_EXPORT int dr4g_inverse_transform_float(dr4g_ctx* ctx, const float* dZ, long long n, int d, int k,
                                  const float* dQ, const float* dmean, float* dX);
-int dr4g_inverse_transform_double(dr4g_ctx* ctx, const double* dZ, long long n, int d, int k,
+DR4G_EXPORT int dr4g_inverse_transform_double(dr4g_ctx* ctx, const double* dZ, long long n, int d, int k,
                                   const double* dQ, const double* dmean, double* dX);
 
 /* Building blocks, exported for parity tests and micro-benchmarks (device pointers).
@@ -118,22 +124,22 @@ int dr4g_inverse_transform_double(dr4g_ctx* ctx, const double* dZ, long long n, 
  *   gram:     dG[d x d] (double, row-major, full symmetric) = (X - shift)^T (X - shift).
  *   eigh:     symmetric eigen-decomposition by blocked cyclic Jacobi; dA (d x d) is destroyed,
  *             dW gets the d eigenvalues (unsorted), dV (d x d row-major) eigenvectors in columns. */
-int dr4g_colstats_float(dr4g_ctx* ctx, const float* dX, long long n, int d, const float* dshift,
+DR4G_EXPORT int dr4g_colstats_float(dr4g_ctx* ctx, const float* dX, long long n, int d, const float* dshift,
                         double* dsum, double* dsumsq);
-int dr4g_colstats_double(dr4g_ctx* ctx, const double* dX, long long n, int d, const double* dshift,
+DR4G_EXPORT int dr4g_colstats_double(dr4g_ctx* ctx, const double* dX, long long n, int d, const double* dshift,
                          double* dsum, double* dsumsq);
-int dr4g_gram_float(dr4g_ctx* ctx, const float* dX, long long n, int d, const float* dshift, double* dG);
-int dr4g_gram_double(dr4g_ctx* ctx, const double* dX, long long n, int d, const double* dshift, double* dG);
-int dr4g_eigh_double(dr4g_ctx* ctx, double* dA, int d, double* dW, double* dV);
+DR4G_EXPORT int dr4g_gram_float(dr4g_ctx* ctx, const float* dX, long long n, int d, const float* dshift, double* dG);
+DR4G_EXPORT int dr4g_gram_double(dr4g_ctx* ctx, const double* dX, long long n, int d, const double* dshift, double* dG);
+DR4G_EXPORT int dr4g_eigh_double(dr4g_ctx* ctx, double* dA, int d, double* dW, double* dV);
 
 /* Per-stage device times (ms) of the last dr4g_fit_* on this context, valid after dr4g_sync:
  * [0] pilot shift, [1] Gram + column stats, [2] partial reduce + allreduce + centring,
  * [3] eigensolve (Jacobi or subspace iteration), [4] sort/flip/outputs, [5] total.
  * Returns the number of entries written (<= n). */
-int dr4g_stage_times(dr4g_ctx* ctx, double* ms, int n);
+DR4G_EXPORT int dr4g_stage_times(dr4g_ctx* ctx, double* ms, int n);
 /* Which Gram kernel the last fit used (1 generic DMMA, 2 tcgen05), and launches it issued. */
-int dr4g_last_gram_path(dr4g_ctx* ctx);
-long long dr4g_launch_count(dr4g_ctx* ctx);
+DR4G_EXPORT int dr4g_last_gram_path(dr4g_ctx* ctx);
+DR4G_EXPORT long long dr4g_launch_count(dr4g_ctx* ctx);
 
 #ifdef __cplusplus
 }
