@@ -74,6 +74,8 @@ class DeviceContext:
         import torch
 
         s = torch.cuda.current_stream(self.device).cuda_stream
+        if s == 0:
+            s = 1  # torch's default stream is the legacy NULL stream; NULL means "private stream" in the C ABI -> cudaStreamLegacy
         _check(self._lib.dr4g_ctx_set_stream(self._h, ctypes.c_void_p(s)), "dr4g_ctx_set_stream")
 
     def set_option(self, key: str, value: float) -> None:
