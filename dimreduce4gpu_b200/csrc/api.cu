@@ -176,6 +176,10 @@ static void fit_impl(Ctx& c, const T* dX, long long n_local, int d, int k, int c
   else
     need += up256(power_workspace_bytes(d, l)) + up256((size_t)lp * 8) + up256((size_t)lp * d * 8);
   need += up256((size_t)(exact ? dp : lp) * 8) + up256((size_t)k * 4) + 64 * 256;
+  bool want_tc = false;
+  if constexpr (sizeof(T) == 4)
+    want_tc = c.gram_path != 1 && gram_tc_eligible(c, reinterpret_cast<const float*>(dX), n_local, d);
+  if (want_tc) need += up256(gram_tc_workspace_bytes(c, d));
   c.arena.reserve(need);
   c.arena.reset();
 
@@ -221,9 +225,9 @@ static void fit_impl(Ctx& c, const T* dX, long long n_local, int d, int k, int c
   bool used_tc = false;
   if constexpr (sizeof(T) == 4) {
     const float* Xf = reinterpret_cast<const float*>(dX);
-    if (c.gram_path != 1 && gram_tc_eligible(c, Xf, n_local, d)) {
-      launch_gram_tc(c, Xf, n_local, d, reinterpret_cast<const float*>(shift_arg),
-                     reinterpret_cast<const float*>(shift_arg), G, s, q);
+    if (want_tc) {
+      void* slabs = c.arena.take(gram_tc_workspace_bytes(c, d));
+      launch_gram_tc(c, Xf, n_local, d, reinterpret_cast<const float*>(shift_arg), G, s, q, slabs);
       used_tc = true;
     } else if (c.gram_path == 2) {
       fail("gram_path=2 (tcgen05) requested but the shape is not eligible: n=%lld d=%d", n_local, d);
@@ -527,7 +531,10 @@ int dr4g_gram_float(dr4g_ctx* ctx, const float* dX, long long n, int d, const fl
   DeviceGuard g(ctx->device);
   DR4G_CUDA(cudaMemsetAsync(dG, 0, (size_t)d * d * 8, ctx->stream));
   if (ctx->gram_path != 1 && gram_tc_eligible(*ctx, dX, n, d)) {
-    launch_gram_tc(*ctx, dX, n, d, dshift, nullptr, dG, nullptr, nullptr);
+    const size_t ws = gram_tc_workspace_bytes(*ctx, d);
+    ctx->arena.reserve(ws + 4096);
+    ctx->arena.reset();
+    launch_gram_tc(*ctx, dX, n, d, dshift, dG, nullptr, nullptr, ctx->arena.take(ws));
     ctx->last_gram_path = 2;
   } else {
     if (ctx->gram_path == 2) fail("gram_path=2 (tcgen05) requested but the shape is not eligible: n=%lld d=%d", n, d);

@@ -73,7 +73,7 @@ struct Ctx {
   int rank = 0, world = 1;
   // options
   int gram_path = 0;          // 0 auto, 1 generic, 2 tcgen05
-  int flush_rows = 2048;      // rows between TMEM flushes in the tcgen05 Gram
+  int flush_rows = 1024;      // rows between TMEM flushes in the tcgen05 Gram
   int pilot_rows = 4096;      // rows sampled for the pilot shift
   double jacobi_tol = 0.0;    // 0 -> per-dtype default
   int jacobi_sweeps = 30;
@@ -101,8 +101,9 @@ void launch_mirror_upper(Ctx& c, double* dG, int d);
 // eligible (caller falls back to the generic path).  Writes the full symmetric dG (double) and,
 // if dsum != nullptr, the column sums / sums of squares of (x - stat_shift).
 bool gram_tc_eligible(const Ctx& c, const float* dX, long long n, int d);
-void launch_gram_tc(Ctx& c, const float* dX, long long n, int d, const float* dgram_shift,
-                    const float* dstat_shift, double* dG, double* dsum, double* dsumsq);
+size_t gram_tc_workspace_bytes(const Ctx& c, int d);  // per-CTA fp32 partial-tile slabs
+void launch_gram_tc(Ctx& c, const float* dX, long long n, int d, const float* dshift, double* dG, double* dsum,
+                    double* dsumsq, void* workspace);
 
 // K3: finalize.  packed = [G (d*d) | s (d) | q (d) | n (1)] doubles.
 // dsum_and_count = [column sums (d) | row count (1)] of the pilot sample (all-reduced across ranks)

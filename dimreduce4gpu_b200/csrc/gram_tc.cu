@@ -15,22 +15,27 @@
 // "super-block" pairs), so that a job's accumulators fill the SM's 512 TMEM columns and every
 // loaded X element feeds all MMAs that need it.  d <= 256 is one job: X is read exactly once.
 // A CTA owns one job and every ncta-th chunk of KT rows of it (split over rows, all SMs busy);
-// partial tiles are added into G with fp64 atomics.
+// partial tiles go to per-CTA fp32 slabs that a second small kernel sums in fp64 (fixed order).
 //
 // 3xTF32.  y = x - c is split exactly into hi = y with the 13 low mantissa bits cleared and
 // lo = y - hi (also cleared to 11 bits), both written to shared memory by the converter warps, and
 // each tile gets hi_a^T hi_b + hi_a^T lo_b + lo_a^T hi_b into one fp32 TMEM accumulator.  Because both
 // parts are exact tf32 numbers the result does not depend on whether the tensor core truncates or
-// rounds its inputs.  The accumulator is flushed into the fp64 G every `flush_rows` rows, which
-// bounds the fp32 accumulation error independently of n.
+// rounds its inputs.  The tensor core's fp32 accumulation TRUNCATES (measured on B200: relative
+// bias of G about 1e-8 per accumulated row), so the TMEM accumulators are flushed every
+// `flush_rows` (default 1024) rows: stored / RED-added (round-to-nearest, in L2) into the CTA's slab.
+// Each flush moves the job's accumulators through L2 (about 8 us at d = 256), so the window trades
+// ~1.6e-8 of relative bias per row against ~10 % of kernel time at 1024 rows.
 //
 // Warp roles (320 threads): warps 0-7 converters + epilogue (TMEM lane quadrant = warp % 4),
 // warp 8 TMA producer, warp 9 TMEM allocator + MMA issuer (one elected lane).
 // Pipeline per stage: full (TMA -> converters), conv (converters -> MMA), empty (MMA commit ->
 // TMA); per flush window: acc_full (MMA commit -> epilogue), acc_empty (epilogue -> MMA).
 //
-// Shared-memory stage (64 KB): [hi | lo], each [column group of 32][KT rows][128 B], 128-byte
-// swizzled exactly as TMA writes it and as the UMMA descriptor (SWIZZLE_128B, LBO = KT*128) reads it.
+// Shared-memory stage (64 KB): [hi | lo], each [column group of 32][KT rows][128 B], swizzled in
+// 32-byte chunks (chunk ^= row % 4) exactly as TMA writes it (SWIZZLE_128B_ATOM_32B) and as the UMMA
+// descriptor reads it (SWIZZLE_128B_BASE32B, the only layout kind::tf32 takes for MN-major
+// operands; LBO = KT*128, SBO = 512).
 #include <mutex>
 
 #include "common.cuh"
@@ -73,8 +78,8 @@ __device__ __forceinline__ float clear13(float v) { return __uint_as_float(__flo
 
 __global__ void __launch_bounds__(kThreads, 1)
 gram_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TcJobTable table, long long n, int d,
-               const float* __restrict__ shift, double* __restrict__ G, double* __restrict__ osum,
-               double* __restrict__ osq, int flush_chunks) {
+               const float* __restrict__ shift, float* __restrict__ slab, double* __restrict__ osum,
+               double* __restrict__ osq, int flush_rows) {
   // ---------------------------------------------------------------- which job / which chunks
   int ji = 0;
   while (ji + 1 < table.njobs && (int)blockIdx.x >= table.job[ji + 1].cta_begin) ++ji;
@@ -84,6 +89,7 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__
   const long long n_chunks = (n + kt - 1) / kt;
   if (split >= job.ncta || split >= n_chunks) return;
   const int my_chunks = (int)((n_chunks - split + job.ncta - 1) / job.ncta);
+  const int flush_chunks = flush_rows > kt ? flush_rows / kt : 1;  // chunks per flush window
 
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -165,10 +171,10 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__
           for (int t = 0; t < job.ntile; ++t) {
             const uint32_t a_off = (uint32_t)(job.ta[t] * 4 * kt) * 128u + (uint32_t)ks * 1024u;
             const uint32_t b_off = (uint32_t)(job.tb[t] * 4 * kt) * 128u + (uint32_t)ks * 1024u;
-            const uint64_t a_hi = ptx::make_smem_desc_sw128(sx + a_off, lbo, 1024);
-            const uint64_t b_hi = ptx::make_smem_desc_sw128(sx + b_off, lbo, 1024);
-            const uint64_t a_lo = ptx::make_smem_desc_sw128(sx + kHalfBytes + a_off, lbo, 1024);
-            const uint64_t b_lo = ptx::make_smem_desc_sw128(sx + kHalfBytes + b_off, lbo, 1024);
+            const uint64_t a_hi = ptx::make_smem_desc(sx + a_off, lbo, 512, ptx::kLayoutSw128Base32);
+            const uint64_t b_hi = ptx::make_smem_desc(sx + b_off, lbo, 512, ptx::kLayoutSw128Base32);
+            const uint64_t a_lo = ptx::make_smem_desc(sx + kHalfBytes + a_off, lbo, 512, ptx::kLayoutSw128Base32);
+            const uint64_t b_lo = ptx::make_smem_desc(sx + kHalfBytes + b_off, lbo, 512, ptx::kLayoutSw128Base32);
             const uint32_t dcol = tmem_base + (uint32_t)t * kBlk;
             ptx::mma_tf32_ss(dcol, a_hi, b_hi, idesc, acc);
             ptx::mma_tf32_ss(dcol, a_hi, b_lo, idesc, 1u);
@@ -199,25 +205,32 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__
     const uint32_t q_off = (uint32_t)((bi * 4 + sub) * kt) * 128u;
     const int quadrant = warp & 3, half = warp >> 2;
 
+    // Window flush: TMEM accumulators -> this CTA's private fp32 slab [tile][row m][col n] in global
+    // memory (L2 resident).  The first window stores, later ones use vector RED (fire-and-forget,
+    // round-to-nearest adds in L2), so the tensor core's truncating accumulation never runs longer
+    // than one window.  reduce_slabs_kernel sums the slabs in fp64 afterwards.
+    float* my_slab = slab + (size_t)blockIdx.x * (4 * kBlk * kBlk);
     auto epilogue = [&](int window) {
       ptx::mbar_wait(ptx::smem_u32(&bar_acc_full), (uint32_t)window & 1u);
       ptx::tc_fence_after_sync();
       for (int t = 0; t < job.ntile; ++t) {
-        const int ga = job.blk[job.ta[t]] * kBlk + quadrant * 32 + lane;  // row of the tile = G column written
 #pragma unroll
         for (int part = 0; part < 2; ++part) {
           const int c0 = half * 64 + part * 32;
           uint32_t v[32];
           ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(quadrant * 32) << 16) + (uint32_t)(t * kBlk + c0), v);
           ptx::tmem_ld_wait();
-          const int gb0 = job.blk[job.tb[t]] * kBlk + c0;
-          if (ga < d) {
+          float* dst = my_slab + ((size_t)t * kBlk + quadrant * 32 + lane) * kBlk + c0;
+          if (window == 0) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              const int gb = gb0 + j;
-              // transposed store (block lower triangle): consecutive lanes -> consecutive addresses
-              if (gb < d) atomicAdd(&G[(size_t)gb * d + ga], (double)__uint_as_float(v[j]));
-            }
+            for (int j = 0; j < 32; j += 4)
+              asm volatile("st.global.v4.b32 [%0], {%1,%2,%3,%4};" ::"l"(dst + j), "r"(v[j]), "r"(v[j + 1]), "r"(v[j + 2]), "r"(v[j + 3]) : "memory");
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4)
+              asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(dst + j), "f"(__uint_as_float(v[j])),
+                           "f"(__uint_as_float(v[j + 1])), "f"(__uint_as_float(v[j + 2])), "f"(__uint_as_float(v[j + 3]))
+                           : "memory");
           }
         }
       }
@@ -238,7 +251,8 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
           const int r = rg + nrg * i;
-          const uint32_t a = sx + (uint32_t)r * 128u + (uint32_t)((lc ^ (r & 7)) << 4);
+          // 32-byte chunks XOR (row % 4): the BASE32B swizzle, as TMA (SWIZZLE_128B_ATOM_32B) laid it out
+          const uint32_t a = sx + (uint32_t)r * 128u + (uint32_t)(((((lc >> 1) ^ (r & 3)) << 1) | (lc & 1)) << 4);
           float4 hi = make_float4(0.f, 0.f, 0.f, 0.f), lo = hi;
           if (col_ok && row0 + r < n) {
             float4 x;
@@ -283,12 +297,29 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__
   if (warp == kConvWarps + 1) ptx::tmem_dealloc(tmem_base, kTmemCols);
 }
 
-// upper block triangle (128-blocks) <- transpose of the lower one
-__global__ void mirror_lower_kernel(double* __restrict__ G, int d) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  const int r = blockIdx.y;
-  if (c >= d) return;
-  if (r / kBlk < c / kBlk) G[(size_t)r * d + c] = G[(size_t)c * d + r];
+// G (fp64, full symmetric) <- sum over a job's CTAs of their fp32 slabs, in a fixed order
+// (deterministic).  grid = (tiles of all jobs, 128 rows m), block = 128 threads (column n).
+// Tile (A, B), A <= B: D[m][n] = G[A*128+m][B*128+n] and, by symmetry, G[B*128+n][A*128+m].
+__global__ void __launch_bounds__(kBlk)
+reduce_slabs_kernel(const __grid_constant__ TcJobTable table, const float* __restrict__ slab, long long n, int d,
+                    double* __restrict__ G) {
+  int ji = 0, t = (int)blockIdx.x;
+  while (t >= table.job[ji].ntile) { t -= table.job[ji].ntile; ++ji; }
+  const TcJob& job = table.job[ji];
+  const int kt = 64 / job.nbp;
+  const long long n_chunks = (n + kt - 1) / kt;
+  const int active = (int)(n_chunks < job.ncta ? n_chunks : job.ncta);
+  const int m = (int)blockIdx.y, nn = (int)threadIdx.x;
+  const int ga = job.blk[job.ta[t]] * kBlk + m, gb = job.blk[job.tb[t]] * kBlk + nn;
+  if (ga >= d || gb >= d) return;
+  // diagonal tiles: the MMA computes both (m, n) and (n, m) with different accumulation orders;
+  // keep the upper one so that G is exactly symmetric
+  if (job.ta[t] == job.tb[t] && nn < m) return;
+  const float* p = slab + ((size_t)job.cta_begin * 4 + t) * (kBlk * kBlk) + (size_t)m * kBlk + nn;
+  double acc = 0.0;
+  for (int c = 0; c < active; ++c) acc += (double)p[(size_t)c * (4 * kBlk * kBlk)];
+  G[(size_t)ga * d + gb] = acc;
+  G[(size_t)gb * d + ga] = acc;
 }
 
 }  // namespace
@@ -370,19 +401,24 @@ bool gram_tc_eligible(const Ctx& c, const float* dX, long long n, int d) {
   return S * (S + 1) / 2 <= kMaxJobs;
 }
 
-void launch_gram_tc(Ctx& c, const float* dX, long long n, int d, const float* dgram_shift, const float* dstat_shift,
-                    double* dG, double* dsum, double* dsumsq) {
-  if (dstat_shift != dgram_shift && dsum != nullptr) fail("gram_tc: statistics use the Gram shift");
+size_t gram_tc_workspace_bytes(const Ctx& c, int d) {
+  TcJobTable tab;
+  if (!build_jobs(d, c.sm_count, tab)) return 0;
+  const int grid = tab.job[tab.njobs - 1].cta_begin + tab.job[tab.njobs - 1].ncta;
+  return (size_t)grid * 4 * kBlk * kBlk * sizeof(float);
+}
+
+void launch_gram_tc(Ctx& c, const float* dX, long long n, int d, const float* dshift, double* dG, double* dsum,
+                    double* dsumsq, void* workspace) {
   TcJobTable tab;
   if (!build_jobs(d, c.sm_count, tab)) fail("gram_tc: d=%d needs more than %d jobs", d, kMaxJobs);
-  // fewer CTAs when there are fewer row chunks than splits (tiny n)
   CUtensorMap tmap;
   const cuuint64_t gdim[2] = {(cuuint64_t)d, (cuuint64_t)n};
   const cuuint64_t gstride[1] = {(cuuint64_t)d * sizeof(float)};
   const cuuint32_t box[2] = {32, (cuuint32_t)kBoxRows};
   const cuuint32_t estride[2] = {1, 1};
   CUresult r = encode_tiled_fn(c)(&tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(dX), gdim, gstride, box,
-                                 estride, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                 estride, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B,
                                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) fail("cuTensorMapEncodeTiled failed (%d) for n=%lld d=%d", (int)r, n, d);
 
@@ -394,17 +430,15 @@ void launch_gram_tc(Ctx& c, const float* dX, long long n, int d, const float* dg
   });
   DR4G_CUDA(attr_err);
 
-  int flush_chunks_rows = c.flush_rows > 0 ? c.flush_rows : 4096;
-  int grid = tab.job[tab.njobs - 1].cta_begin + tab.job[tab.njobs - 1].ncta;
-  // flush_chunks is per job KT; the kernel takes chunks, so pass rows / 64 * nbp via the smallest KT
-  // (conservative: a window is at most flush_rows rows for every job)
-  int flush_chunks = flush_chunks_rows / 64;
-  if (flush_chunks < 1) flush_chunks = 1;
-  gram_tc_kernel<<<grid, kThreads, smem, c.stream>>>(tmap, tab, n, d, dgram_shift, dG, dsum, dsumsq, flush_chunks);
+  const int flush_rows = c.flush_rows > 0 ? c.flush_rows : 1024;
+  const int grid = tab.job[tab.njobs - 1].cta_begin + tab.job[tab.njobs - 1].ncta;
+  float* slab = static_cast<float*>(workspace);
+  gram_tc_kernel<<<grid, kThreads, smem, c.stream>>>(tmap, tab, n, d, dshift, slab, dsum, dsumsq, flush_rows);
   c.launches++;
   DR4G_CUDA(cudaGetLastError());
-  dim3 mg(ceil_div(d, 128), d);
-  mirror_lower_kernel<<<mg, 128, 0, c.stream>>>(dG, d);
+  int tiles = 0;
+  for (int i = 0; i < tab.njobs; ++i) tiles += tab.job[i].ntile;
+  reduce_slabs_kernel<<<dim3(tiles, kBlk), kBlk, 0, c.stream>>>(tab, slab, n, d, dG);
   c.launches++;
   DR4G_CUDA(cudaGetLastError());
 }

@@ -130,19 +130,25 @@ __device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&r)[32])
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
-// Shared-memory matrix descriptor, 128-byte swizzle, sm_100 version field.
+// Shared-memory matrix descriptor (sm_100 version field).
 //   start address, LBO and SBO are in 16-byte units (14 bits each); bits 46-47 = 0b01 (version),
-//   bits 61-63 = 2 (SWIZZLE_128B).
+//   bits 61-63 = layout type: 2 = SWIZZLE_128B (16-byte chunks XOR row % 8, 8-row atoms),
+//   1 = SWIZZLE_128B_BASE32B (32-byte chunks XOR row % 4, 4-row atoms).
 // For an MN-major operand (the contiguous dimension is M resp. N, which is what a row-major X tile
 // gives both operands of X^T X): LBO = byte distance between consecutive 128-byte groups along
-// M/N, SBO = byte distance between consecutive 8-row groups along K.
-__device__ __forceinline__ uint64_t make_smem_desc_sw128(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+// M/N, SBO = byte distance between consecutive row atoms along K.  32-bit MN-major operands
+// (kind::tf32) are only accepted in the BASE32B layout, which is what TMA writes with
+// CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B.
+constexpr uint32_t kLayoutSw128 = 2;
+constexpr uint32_t kLayoutSw128Base32 = 1;
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes,
+                                                   uint32_t layout_type) {
   uint64_t d = 0;
   d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
   d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
   d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
   d |= (uint64_t)1 << 46;
-  d |= (uint64_t)2 << 61;
+  d |= (uint64_t)layout_type << 61;
   return d;
 }
 

@@ -1,0 +1,119 @@
+"""The tcgen05 Gram + column-statistics kernel (csrc/gram_tc.cu) through the C ABI (dr4g_gram_float,
+dr4g_fit_float with gram_path=2) against an fp64 product of the same inputs.
+
+Tolerance: 3xTF32 with 1024-row flush windows reproduces X^T X to about 2e-5 of sqrt(G_ii G_jj)
+(the tensor core truncates its fp32 accumulation, about 1.6e-8 relative per accumulated row); the
+gate is 3e-5, inside what the 1e-4 singular-value tolerance of BASELINE.json needs (sigma^2 are
+eigenvalues of G, so sigma moves by half of that).  With flush_rows=128 the error is ~3e-6."""
+from __future__ import annotations
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+GRAM_TOL = 3e-5
+
+
+def _ctx(path=2, **opts):
+    import dimreduce4gpu_b200 as pkg
+
+    ctx = pkg.DeviceContext(0)
+    ctx.set_option("gram_path", path)
+    for k, v in opts.items():
+        ctx.set_option(k, v)
+    return ctx
+
+
+def _make(n, d, seed, offset=0.5):
+    import torch
+
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    return torch.randn(n, d, device="cuda", generator=g) * torch.linspace(1, 3, d, device="cuda") + offset
+
+
+def _rel_err(G, Xd):
+    import torch
+
+    Gr = Xd.T @ Xd
+    dg = torch.sqrt(torch.diag(Gr))
+    return float(((G - Gr).abs() / (dg[:, None] * dg[None, :]).clamp_min(1e-30)).max())
+
+
+# shapes: one/two/three/four/eight column blocks, ragged d (d % 128 != 0, d % 32 != 0), ragged n
+# (n % 64 != 0, n < one chunk, n < number of CTAs * chunk), and a long stream with many flush windows
+SHAPES = [(1, 4), (3, 8), (64, 128), (200, 128), (4099, 100), (5000, 256), (3001, 320), (2500, 384),
+          (8192, 512), (3000, 516), (4096, 1024), (300000, 256), (70000, 512)]
+
+
+@pytest.mark.parametrize("n,d", SHAPES)
+@pytest.mark.parametrize("shifted", [False, True])
+def test_gram_tc_matches_fp64(n, d, shifted):
+    ctx = _ctx()
+    X = _make(n, d, 11 * n + d)
+    shift = X[: min(n, 4096)].mean(0).contiguous() if shifted else None
+    G = ctx.gram(X, shift)
+    ctx.sync()
+    assert ctx.last_gram_path == "tcgen05"
+    Xd = X.double() - (shift.double() if shifted else 0.0)
+    assert _rel_err(G, Xd) < GRAM_TOL
+    assert float((G - G.T).abs().max()) == 0.0  # mirrored, exactly symmetric
+
+
+def test_gram_tc_agrees_with_generic_dmma_path():
+    X = _make(20000, 384, 5)
+    Gt = _ctx(2).gram(X)
+    Gg = _ctx(1).gram(X)
+    import torch
+
+    torch.cuda.synchronize()
+    dg = torch.sqrt(torch.diag(Gg))
+    assert float(((Gt - Gg).abs() / (dg[:, None] * dg[None, :])).max()) < GRAM_TOL
+
+
+@pytest.mark.parametrize("n,d", [(5000, 256), (4099, 100), (9000, 640)])
+def test_fused_column_statistics(n, d):
+    """mean_ and the total variance come from the same pass (sums / sums of squares of x - shift)."""
+    ctx = _ctx()
+    X = _make(n, d, 3, offset=7.0)
+    res = ctx.fit(X, min(8, d), center=True)
+    ctx.sync()
+    assert ctx.last_gram_path == "tcgen05"
+    Xd = X.double()
+    assert float((res["mean"].double() - Xd.mean(0)).abs().max()) < 2e-6
+    tot = float(Xd.var(0, unbiased=True).sum())
+    evr = res["explained_variance_ratio"].double()
+    ev = res["explained_variance"].double()
+    np.testing.assert_allclose(float((ev / evr).mean()), tot, rtol=2e-5)
+
+
+def test_flush_window_bounds_the_accumulation_bias():
+    """The tensor core truncates its fp32 accumulation: the error grows with the flush window,
+    which is why the accumulators are flushed every flush_rows rows."""
+    X = _make(400000, 256, 9)
+    Xd = X.double()
+    errs = {}
+    for rows in (128, 8192):
+        ctx = _ctx(2, flush_rows=rows)
+        G = ctx.gram(X)
+        ctx.sync()
+        errs[rows] = _rel_err(G, Xd)
+    assert errs[128] < 5e-6
+    assert errs[128] < errs[8192]
+
+
+def test_full_size_config2_linearity_and_trace():
+    """BASELINE configs[1] size (1M x 256): properties that need no oracle - the Gram of the stacked
+    halves is the sum of the halves' Grams, and trace(G) = sum of squares."""
+    import torch
+
+    ctx = _ctx()
+    X = _make(1_000_000, 256, 21)
+    G = ctx.gram(X).clone()
+    G1 = ctx.gram(X[:500_000]).clone()
+    G2 = ctx.gram(X[500_000:]).clone()
+    ctx.sync()
+    dg = torch.sqrt(torch.diag(G))
+    assert float(((G1 + G2 - G).abs() / (dg[:, None] * dg[None, :])).max()) < GRAM_TOL
+    ssq = float((X.double() ** 2).sum())
+    assert abs(float(torch.trace(G)) - ssq) / ssq < GRAM_TOL

@@ -17,6 +17,7 @@ def main():
     ap.add_argument("--flush", type=int, default=0)
     ap.add_argument("--path", type=int, default=2)
     ap.add_argument("--reps", type=int, default=5)
+    ap.add_argument("--verbose", action="store_true")
     a = ap.parse_args()
     ctx = pkg.DeviceContext(0)
     ctx.set_option("gram_path", a.path)
@@ -35,6 +36,16 @@ def main():
             dg = torch.sqrt(torch.diag(Gr))
             err = ((G - Gr).abs() / (dg[:, None] * dg[None, :])).max().item()
             sym = (G - G.T).abs().max().item()
+            if a.verbose:
+                print("G  ", G[:2, :4].tolist(), G[d - 1, d - 4:].tolist())
+                print("Gr ", Gr[:2, :4].tolist(), Gr[d - 1, d - 4:].tolist())
+                nz = (G != 0).sum().item()
+                print("nonzero", nz, "of", d * d, "nan", torch.isnan(G).sum().item())
+                if use_shift:
+                    res = ctx.fit(X, min(4, d), center=True)
+                    ctx.sync()
+                    print("mean err", (res["mean"].double() - X.double().mean(0)).abs().max().item(),
+                          "sv", res["singular_values"].tolist())
             t = []
             for _ in range(a.reps):
                 torch.cuda.synchronize()
