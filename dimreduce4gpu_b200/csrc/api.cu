@@ -171,8 +171,11 @@ static void fit_impl(Ctx& c, const T* dX, long long n_local, int d, int k, int c
   // workspace
   size_t need = up256(packed_count * 8) + up256((size_t)d * 8) * 4 + up256((size_t)d * sizeof(T)) + up256(dd * 8) + 4096;
   need += up256(((size_t)d + 1) * 8);
-  if (exact)
+  const bool use_jacobi = c.eig_solver == 1;
+  if (exact && use_jacobi)
     need += 2 * up256((size_t)dp * dp * 8) + up256((size_t)dp * 8) + up256(jacobi_workspace_bytes(dp));
+  else if (exact)
+    need += up256(eigh_topk_workspace_bytes(d, k)) + up256((size_t)k * 8) + up256((size_t)k * d * 8);
   else
     need += up256(power_workspace_bytes(d, l)) + up256((size_t)lp * 8) + up256((size_t)lp * d * 8);
   need += up256((size_t)(exact ? dp : lp) * 8) + up256((size_t)k * 4) + 64 * 256;
@@ -249,7 +252,15 @@ static void fit_impl(Ctx& c, const T* dX, long long n_local, int d, int k, int c
   mark(3);
 
   // [3] eigensolve + [4] outputs
-  if (exact) {
+  if (exact && !use_jacobi) {
+    void* ws = c.arena.take(eigh_topk_workspace_bytes(d, k));
+    double* W = c.arena.take_n<double>(k);
+    double* Vt = c.arena.take_n<double>((size_t)k * d);
+    launch_eigh_topk(c, C, d, k, W, Vt, ws);
+    mark(4);
+    launch_postproc<T>(c, W, k, Vt, d, /*vectors_in_rows=*/true, /*check_mass=*/false, d, k, cnt, total_var,
+                       center ? mean_d : nullptr, dQ, dw, dev, devr, center ? dmean : nullptr);
+  } else if (exact) {
     double* A = c.arena.take_n<double>((size_t)dp * dp);
     double* V = c.arena.take_n<double>((size_t)dp * dp);
     double* W = c.arena.take_n<double>(dp);
@@ -436,6 +447,7 @@ int dr4g_set_option(dr4g_ctx* ctx, const char* key, double value) {
   else if (k == "jacobi_tol") ctx->jacobi_tol = value;
   else if (k == "jacobi_sweeps") ctx->jacobi_sweeps = (int)value;
   else if (k == "timing") ctx->timing = (int)value;
+  else if (k == "eig_solver") ctx->eig_solver = (int)value;
   else fail("unknown option '%s'", key);
   DR4G_API_END
 }
@@ -578,6 +590,19 @@ int dr4g_eigh_double(dr4g_ctx* ctx, double* dA, int d, double* dW, double* dV) {
   // blocks) are exactly the eigenpairs of A.
   DR4G_CUDA(cudaMemcpy2DAsync(dV, (size_t)d * 8, V, (size_t)dp * 8, (size_t)d * 8, d, cudaMemcpyDeviceToDevice, ctx->stream));
   DR4G_CUDA(cudaMemcpyAsync(dW, W, (size_t)d * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+  DR4G_API_END
+}
+
+int dr4g_eigh_topk_double(dr4g_ctx* ctx, double* dA, int d, int k, double* dW, double* dVt) {
+  DR4G_API_BEGIN
+  if (!ctx || !dA || !dW || !dVt) fail("dr4g_eigh_topk_double: null argument");
+  if (d <= 0 || k <= 0 || k > d) fail("dr4g_eigh_topk_double: bad dimensions d=%d k=%d", d, k);
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  DeviceGuard g(ctx->device);
+  const size_t ws = eigh_topk_workspace_bytes(d, k);
+  ctx->arena.reserve(ws + 4096);
+  ctx->arena.reset();
+  launch_eigh_topk(*ctx, dA, d, k, dW, dVt, ctx->arena.take(ws));
   DR4G_API_END
 }
 

@@ -77,6 +77,7 @@ struct Ctx {
   int pilot_rows = 4096;      // rows sampled for the pilot shift
   double jacobi_tol = 0.0;    // 0 -> per-dtype default
   int jacobi_sweeps = 30;
+  int eig_solver = 0;         // exact path: 0 tridiagonal route (top-k), 1 blocked Jacobi (all pairs)
   int timing = 1;             // record per-stage events
   // telemetry
   int last_gram_path = 0;
@@ -118,6 +119,12 @@ int jacobi_padded_dim(int d);
 size_t jacobi_workspace_bytes(int dp);
 void launch_jacobi(Ctx& c, double* dA, double* dV, int dp, double* dW, void* workspace, double tol, int max_sweeps);
 void launch_pad_copy(Ctx& c, const double* src, int d, double* dst, int dp);
+
+// K4 (exact path): top-k eigenpairs via Householder tridiagonalisation + Sturm multisection +
+// inverse iteration + back-transformation.  dA (d x d, symmetric, row-major) is destroyed; dW gets
+// the k largest eigenvalues in descending order, dVt (k x d) the unit eigenvectors in rows.
+size_t eigh_topk_workspace_bytes(int d, int k);
+void launch_eigh_topk(Ctx& c, double* dA, int d, int k, double* dW, double* dVt, void* workspace);
 
 // K5: subspace iteration on the d x d Gram/covariance ("power" algorithm).
 size_t power_workspace_bytes(int d, int l);

@@ -1,0 +1,445 @@
+// K4 - device-resident symmetric eigensolver for the top-k eigenpairs (fp64), tridiagonal route:
+//   T1  Householder tridiagonalisation  A = Q T Q^T          (one cooperative launch, 1 grid barrier / column)
+//   T2  eigenvalues of T by Sturm-count multisection          (one warp per eigenvalue, 32 shifts per step)
+//   T3  eigenvectors of T by inverse iteration                (pivoted tridiagonal LU; clusters re-orthogonalised)
+//   T4  back-transformation  v = Q z                          (one CTA per vector)
+// Replaces cusolverDn{S,D}syevd (reference src/matrix.cu:231-273, called from src/tsvd.cu:329).
+// Only the k leading pairs are formed: everything the outputs need beyond them (the total variance)
+// comes from the column statistics, not from the spectrum.  The blocked Jacobi solver (jacobi.cu)
+// stays for dr4g_eigh_double (all pairs) and the small Rayleigh-Ritz problem of the 'power' path;
+// at d = 256 it needed 18 ms per fit on B200 against 0.65 ms for the Gram pass, which is why the
+// exact path moved here.
+//
+// T1 keeps the full symmetric trailing matrix in global memory (L2 resident: 8 d^2 bytes) and owns
+// rows cyclically, one warp per row.  Iteration s eliminates column s:
+//   A  every CTA (redundantly): corrected row s  r = A[s,:] - v_s w - w_s v  (previous reflector's
+//      rank-2 update applied on the fly), d_s = r_s, new reflector (v', tau') from r[s+1:], e_s = beta
+//   B  own rows i > s: A[i,c] -= v_i w_c + w_i v_c (c > s), and in the same pass p'_i = tau' A[i,:] v'
+//   -- grid barrier --
+//   C  every CTA (redundantly): w' = p' - (tau'/2)(p'.v') v'
+// so the rank-2 update of one column and the matrix-vector product of the next share one sweep
+// over the rows and one barrier.
+#include <cfloat>
+
+#include "common.cuh"
+
+namespace dr4g {
+namespace {
+
+constexpr int kTriThreads = 256;
+constexpr int kTriWarps = kTriThreads / 32;
+
+struct TriCtrl {
+  unsigned int barrier;
+  unsigned int pad;
+};
+
+__device__ __forceinline__ void tri_grid_barrier(TriCtrl* ctrl, unsigned int& target) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    target += gridDim.x;
+    __threadfence();
+    atomicAdd(&ctrl->barrier, 1u);
+    while (*reinterpret_cast<volatile unsigned int*>(&ctrl->barrier) < target) {}
+    __threadfence();
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ double tri_block_sum(double v, double* red) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  double t = 0;
+#pragma unroll
+  for (int w = 0; w < kTriWarps; ++w) t += red[w];
+  return t;
+}
+
+// A: d x d symmetric, row-major, destroyed.  Out: diag[d], off[d] (off[s] couples s and s+1; off[d-1] = 0),
+// tau[d], Vh[d x d] (row s = reflector of column s, entries s+1.. with Vh[s][s+1] = 1).
+__global__ void __launch_bounds__(kTriThreads)
+tridiag_kernel(double* __restrict__ A, int d, double* __restrict__ diag, double* __restrict__ off,
+               double* __restrict__ tau, double* __restrict__ Vh, double* __restrict__ pbuf, TriCtrl* ctrl) {
+  extern __shared__ double tri_sm[];
+  double* v = tri_sm;          // previous reflector (full length d, zero outside its support)
+  double* w = v + d;           // previous w
+  double* vn = w + d;          // new reflector
+  double* row = vn + d;        // corrected row s / p'
+  __shared__ double red[kTriWarps];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int gw = blockIdx.x * kTriWarps + warp, nw = gridDim.x * kTriWarps;
+  unsigned int target = 0;
+
+  for (int c = tid; c < d; c += kTriThreads) { v[c] = 0.0; w[c] = 0.0; vn[c] = 0.0; }
+  __syncthreads();
+
+  for (int s = 0; s < d - 1; ++s) {
+    // ---- A: corrected row s and the reflector that eliminates r[s+2:]
+    const double vs = v[s], ws = w[s];
+    double nrm2 = 0.0;
+    for (int c = s + tid; c < d; c += kTriThreads) {
+      const double r = __ldcg(&A[(size_t)s * d + c]) - vs * w[c] - ws * v[c];
+      row[c] = r;
+      if (c > s + 1) nrm2 += r * r;
+    }
+    nrm2 = tri_block_sum(nrm2, red);  // includes the barrier that publishes row[]
+    const double x0 = row[s + 1];
+    double beta = x0, t = 0.0, scale = 0.0;
+    if (nrm2 > 0.0 && s < d - 2) {
+      const double nrm = sqrt(x0 * x0 + nrm2);
+      beta = x0 >= 0.0 ? -nrm : nrm;
+      t = (beta - x0) / beta;
+      scale = 1.0 / (x0 - beta);
+    }
+    for (int c = tid; c < d; c += kTriThreads) vn[c] = c > s + 1 ? row[c] * scale : (c == s + 1 ? 1.0 : 0.0);
+    if (blockIdx.x == 0) {
+      if (tid == 0) { diag[s] = row[s]; off[s] = beta; tau[s] = t; }
+      for (int c = tid; c < d; c += kTriThreads) Vh[(size_t)s * d + c] = c > s + 1 ? row[c] * scale : (c == s + 1 ? 1.0 : 0.0);
+    }
+    __syncthreads();
+    // ---- B: rank-2 update of own rows fused with p' = tau' A' v'
+    for (int i = s + 1 + ((gw - (s + 1)) % nw + nw) % nw; i < d; i += nw) {
+      const double vi = v[i], wi = w[i];
+      double* Ai = A + (size_t)i * d;
+      double dot = 0.0;
+      for (int c = s + 1 + lane; c < d; c += 32) {
+        const double a = __ldcg(&Ai[c]) - vi * w[c] - wi * v[c];
+        __stcg(&Ai[c], a);
+        dot = fma(a, vn[c], dot);
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
+      if (lane == 0) __stcg(&pbuf[(size_t)(s & 1) * d + i], t * dot);
+    }
+    tri_grid_barrier(ctrl, target);
+    // ---- C: w' from p'
+    double pv = 0.0;
+    for (int c = s + 1 + tid; c < d; c += kTriThreads) {
+      const double p = __ldcg(&pbuf[(size_t)(s & 1) * d + c]);
+      row[c] = p;
+      pv += p * vn[c];
+    }
+    pv = tri_block_sum(pv, red);
+    const double kk = 0.5 * t * pv;
+    for (int c = tid; c < d; c += kTriThreads) {
+      const double vv = vn[c];
+      v[c] = vv;
+      w[c] = c > s ? row[c] - kk * vv : 0.0;
+    }
+    __syncthreads();
+  }
+  // last diagonal entry: A[d-1][d-1] with the final rank-2 correction (v, w hold reflector d-2's, tau = 0 -> w = 0)
+  if (blockIdx.x == 0 && tid == 0) {
+    const int s = d - 1;
+    diag[s] = __ldcg(&A[(size_t)s * d + s]) - 2.0 * v[s] * w[s];
+    off[s] = 0.0;
+    tau[s] = 0.0;
+  }
+}
+
+}  // namespace
+
+namespace {
+
+// ---------------------------------------------------------------- T2: eigenvalues by multisection
+// Number of eigenvalues of T smaller than x (Sturm count on the LDL^T pivots, LAPACK dlaebz style).
+__device__ __forceinline__ int sturm_count(const double* __restrict__ dg, const double* __restrict__ e2, int d,
+                                           double x, double pivmin) {
+  int cnt = 0;
+  double q = dg[0] - x;
+  if (fabs(q) < pivmin) q = -pivmin;
+  cnt += q < 0.0;
+  for (int i = 1; i < d; ++i) {
+    q = dg[i] - x - e2[i - 1] / q;
+    if (fabs(q) < pivmin) q = -pivmin;
+    cnt += q < 0.0;
+  }
+  return cnt;
+}
+
+// One warp per wanted eigenvalue (j-th largest, j = blockIdx.x*warps + warp).  lam[j] descending.
+// info[0] = ||T||_1-ish scale (max Gershgorin radius bound), written by warp 0 for T3.
+__global__ void __launch_bounds__(128)
+bisect_kernel(const double* __restrict__ diag, const double* __restrict__ off, int d, int k,
+              double* __restrict__ lam, double* __restrict__ info) {
+  extern __shared__ double bs_sm[];
+  double* dg = bs_sm;
+  double* e2 = dg + d;
+  __shared__ double s_lo[4], s_hi[4], s_emax[4];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  double lo = DBL_MAX, hi = -DBL_MAX, emax = 0.0;
+  for (int i = tid; i < d; i += blockDim.x) {
+    const double a = diag[i];
+    const double el = i > 0 ? fabs(off[i - 1]) : 0.0, er = i < d - 1 ? fabs(off[i]) : 0.0;
+    dg[i] = a;
+    e2[i] = i < d - 1 ? off[i] * off[i] : 0.0;
+    lo = fmin(lo, a - el - er);
+    hi = fmax(hi, a + el + er);
+    emax = fmax(emax, er * er);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    lo = fmin(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+    hi = fmax(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+    emax = fmax(emax, __shfl_xor_sync(0xffffffffu, emax, o));
+  }
+  if (lane == 0) { s_lo[warp] = lo; s_hi[warp] = hi; s_emax[warp] = emax; }
+  __syncthreads();
+  const int nwarp = blockDim.x / 32;
+  for (int i = 0; i < nwarp; ++i) { lo = fmin(lo, s_lo[i]); hi = fmax(hi, s_hi[i]); emax = fmax(emax, s_emax[i]); }
+  const double tnorm = fmax(fabs(lo), fabs(hi));
+  const double pivmin = fmax(DBL_MIN * fmax(1.0, emax), DBL_MIN);
+  // widen the Gershgorin interval a little (dstebz)
+  lo -= 2.0 * DBL_EPSILON * tnorm * d + 2.0 * pivmin;
+  hi += 2.0 * DBL_EPSILON * tnorm * d + 2.0 * pivmin;
+  if (blockIdx.x == 0 && tid == 0) { info[0] = tnorm; info[1] = pivmin; }
+
+  const int j = blockIdx.x * nwarp + warp;
+  if (j >= k) return;
+  const int idx = d - 1 - j;  // 0-based index in ascending order: count(x) <= idx  <=>  x <= lambda_idx
+  for (int it = 0; it < 16; ++it) {
+    const double width = hi - lo;
+    if (!(width > 2.0 * DBL_EPSILON * fmax(fabs(lo), fabs(hi)) + 2.0 * pivmin)) break;
+    const double x = lo + width * (double)(lane + 1) / 33.0;
+    const int cnt = sturm_count(dg, e2, d, x, pivmin);
+    const unsigned above = __ballot_sync(0xffffffffu, cnt > idx);  // x_l already to the right of lambda_idx
+    const int first = above ? __ffs(above) - 1 : 32;
+    const double nlo = first == 0 ? lo : lo + width * (double)first / 33.0;
+    const double nhi = first == 32 ? hi : lo + width * (double)(first + 1) / 33.0;
+    lo = nlo;
+    hi = nhi;
+  }
+  if (lane == 0) lam[j] = 0.5 * (lo + hi);
+}
+
+// ---------------------------------------------------------------- T3: eigenvectors by inverse iteration
+// One CTA per cluster of close eigenvalues (gap < 1e-3 ||T||, LAPACK dstein's criterion): the CTA of
+// the first member computes the cluster's vectors one after the other, re-orthogonalising against
+// the earlier ones inside every iteration.  Z: k x d (rows), unit vectors of T.
+constexpr int kInvThreads = 128;
+
+__device__ __forceinline__ double inv_block_sum(double v, double* red) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  double t = 0;
+#pragma unroll
+  for (int w = 0; w < kInvThreads / 32; ++w) t += red[w];
+  return t;
+}
+
+__device__ __forceinline__ double hash_uniform(unsigned a, unsigned b) {
+  unsigned x = a * 0x9E3779B1u ^ (b + 0x7F4A7C15u) * 0x85EBCA77u;
+  x ^= x >> 15; x *= 0x2C1B3C6Du; x ^= x >> 12; x *= 0x297A2D39u; x ^= x >> 15;
+  return ((double)x + 0.5) * (1.0 / 4294967296.0) - 0.5;
+}
+
+__global__ void __launch_bounds__(kInvThreads)
+invit_kernel(const double* __restrict__ diag, const double* __restrict__ off, int d, int k,
+             const double* __restrict__ lam, const double* __restrict__ info, double* __restrict__ Z) {
+  const int j0 = blockIdx.x;
+  const double tnorm = info[0];
+  const double ortol = 1e-3 * tnorm;
+  if (j0 > 0 && fabs(lam[j0 - 1] - lam[j0]) <= ortol) return;  // not the head of a cluster
+  int j1 = j0 + 1;
+  while (j1 < k && fabs(lam[j1 - 1] - lam[j1]) <= ortol) ++j1;
+
+  extern __shared__ double iv_sm[];
+  double* a = iv_sm;        // U diagonal
+  double* b = a + d;        // U first super-diagonal
+  double* c = b + d;        // multipliers
+  double* d2 = c + d;       // U second super-diagonal
+  double* z = d2 + d;       // iterate
+  int* piv = reinterpret_cast<int*>(z + d);
+  __shared__ double red[kInvThreads / 32];
+  const int tid = threadIdx.x;
+  const double eps = DBL_EPSILON;
+  const double tiny = fmax(eps * tnorm, DBL_MIN * 1e16);
+
+  double prev = 0.0;
+  for (int j = j0; j < j1; ++j) {
+    // perturb repeated values so that cluster members get distinct shifts (dstein)
+    double x = lam[j];
+    if (j > j0 && prev - x < 10.0 * eps * tnorm) x = prev - 10.0 * eps * tnorm;
+    prev = x;
+    // ---- factor T - x I = P L U (partial pivoting), sequential
+    if (tid == 0) {
+      for (int i = 0; i < d; ++i) { a[i] = diag[i] - x; b[i] = i < d - 1 ? off[i] : 0.0; c[i] = b[i]; d2[i] = 0.0; }
+      for (int i = 0; i < d - 1; ++i) {
+        if (fabs(a[i]) >= fabs(c[i])) {
+          double pv = a[i];
+          if (fabs(pv) < tiny) { pv = pv < 0 ? -tiny : tiny; a[i] = pv; }
+          const double m = c[i] / pv;
+          a[i + 1] -= m * b[i];
+          c[i] = m;
+          piv[i] = 0;
+        } else {
+          const double m = a[i] / c[i];
+          a[i] = c[i];
+          const double t = a[i + 1];
+          a[i + 1] = b[i] - m * t;
+          if (i < d - 2) { d2[i] = b[i + 1]; b[i + 1] = -m * d2[i]; }
+          b[i] = t;
+          c[i] = m;
+          piv[i] = 1;
+        }
+      }
+      if (fabs(a[d - 1]) < tiny) a[d - 1] = a[d - 1] < 0 ? -tiny : tiny;
+    }
+    for (int i = tid; i < d; i += kInvThreads) z[i] = hash_uniform((unsigned)i, (unsigned)j * 7919u + 13u);
+    __syncthreads();
+    for (int iter = 0; iter < 4; ++iter) {
+      if (tid == 0) {
+        if (iter > 0) {  // apply P, L to the right-hand side (the first solve uses U only, as dstein does)
+          for (int i = 0; i < d - 1; ++i) {
+            if (piv[i] == 0) z[i + 1] -= c[i] * z[i];
+            else { const double t = z[i]; z[i] = z[i + 1]; z[i + 1] = t - c[i] * z[i]; }
+          }
+        }
+        for (int i = d - 1; i >= 0; --i) {  // U z = y
+          double t = z[i];
+          if (i < d - 1) t -= b[i] * z[i + 1];
+          if (i < d - 2) t -= d2[i] * z[i + 2];
+          z[i] = t / a[i];
+        }
+      }
+      __syncthreads();
+      // re-orthogonalise against the cluster's earlier vectors, normalise
+      for (int p = j0; p < j; ++p) {
+        double dot = 0.0;
+        for (int i = tid; i < d; i += kInvThreads) dot += z[i] * Z[(size_t)p * d + i];
+        dot = inv_block_sum(dot, red);
+        for (int i = tid; i < d; i += kInvThreads) z[i] -= dot * Z[(size_t)p * d + i];
+        __syncthreads();
+      }
+      double mx = 0.0;
+      for (int i = tid; i < d; i += kInvThreads) mx = fmax(mx, fabs(z[i]));
+      // max via sum of squares after a power-of-two-free rescale: two passes keep it overflow safe
+      __syncthreads();
+      red[tid >> 5] = 0.0;
+      __syncthreads();
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+      if ((tid & 31) == 0) red[tid >> 5] = mx;
+      __syncthreads();
+      double gmx = 0.0;
+      for (int wv = 0; wv < kInvThreads / 32; ++wv) gmx = fmax(gmx, red[wv]);
+      __syncthreads();
+      const double inv = gmx > 0.0 && isfinite(gmx) ? 1.0 / gmx : 1.0;
+      double ss = 0.0;
+      for (int i = tid; i < d; i += kInvThreads) { const double t = z[i] * inv; z[i] = t; ss += t * t; }
+      ss = inv_block_sum(ss, red);
+      const double rn = ss > 0.0 ? rsqrt(ss) : 0.0;
+      for (int i = tid; i < d; i += kInvThreads) z[i] *= rn;
+      __syncthreads();
+    }
+    for (int i = tid; i < d; i += kInvThreads) Z[(size_t)j * d + i] = z[i];
+    __threadfence_block();
+    __syncthreads();
+  }
+}
+
+// ---------------------------------------------------------------- T4: v = H_0 H_1 ... H_{d-3} z
+__global__ void __launch_bounds__(256)
+backtransform_kernel(const double* __restrict__ Vh, const double* __restrict__ tau, int d, int k,
+                     double* __restrict__ Z) {
+  extern __shared__ double bt_sm[];
+  double* z = bt_sm;
+  __shared__ double red[8];
+  const int tid = threadIdx.x, j = blockIdx.x;
+  for (int i = tid; i < d; i += 256) z[i] = Z[(size_t)j * d + i];
+  __syncthreads();
+  for (int s = d - 3; s >= 0; --s) {
+    const double t = tau[s];
+    if (t == 0.0) continue;
+    const double* vr = Vh + (size_t)s * d;
+    double dot = 0.0;
+    for (int i = s + 1 + tid; i < d; i += 256) dot += vr[i] * z[i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
+    if ((tid & 31) == 0) red[tid >> 5] = dot;
+    __syncthreads();
+    double tot = 0.0;
+#pragma unroll
+    for (int wv = 0; wv < 8; ++wv) tot += red[wv];
+    tot *= t;
+    for (int i = s + 1 + tid; i < d; i += 256) z[i] -= tot * vr[i];
+    __syncthreads();
+  }
+  for (int i = tid; i < d; i += 256) Z[(size_t)j * d + i] = z[i];
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------- host side
+static size_t tri_r256(size_t b) { return (b + 255) / 256 * 256; }
+
+size_t eigh_topk_workspace_bytes(int d, int k) {
+  return tri_r256((size_t)d * d * 8)      // Vh
+         + 3 * tri_r256((size_t)d * 8)    // diag, off, tau
+         + tri_r256((size_t)2 * d * 8)    // pbuf
+         + tri_r256((size_t)k * 8)        // lam
+         + 256 + 256;                     // info, ctrl
+}
+
+void launch_eigh_topk(Ctx& c, double* dA, int d, int k, double* dW, double* dVt, void* workspace) {
+  if (k > d) k = d;
+  char* p = static_cast<char*>(workspace);
+  auto take = [&](size_t bytes) { char* q = p; p += tri_r256(bytes); return q; };
+  double* Vh = reinterpret_cast<double*>(take((size_t)d * d * 8));
+  double* diag = reinterpret_cast<double*>(take((size_t)d * 8));
+  double* off = reinterpret_cast<double*>(take((size_t)d * 8));
+  double* tau = reinterpret_cast<double*>(take((size_t)d * 8));
+  double* pbuf = reinterpret_cast<double*>(take((size_t)2 * d * 8));
+  double* info = reinterpret_cast<double*>(take(256));
+  TriCtrl* ctrl = reinterpret_cast<TriCtrl*>(take(256));
+  (void)take((size_t)k * 8);
+  DR4G_CUDA(cudaMemsetAsync(ctrl, 0, sizeof(TriCtrl), c.stream));
+
+  // T1
+  const size_t tri_smem = (size_t)4 * d * sizeof(double);
+  static size_t tri_smem_set = 0;
+  if (tri_smem > 48 * 1024 && tri_smem > tri_smem_set) {
+    DR4G_CUDA(cudaFuncSetAttribute(tridiag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tri_smem));
+    tri_smem_set = tri_smem;
+  }
+  int per_sm = 0;
+  DR4G_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tridiag_kernel, kTriThreads, tri_smem));
+  if (per_sm < 1) fail("eigh: tridiagonalisation kernel cannot be made resident for d=%d", d);
+  int grid = (d + kTriWarps - 1) / kTriWarps;
+  if (grid > c.sm_count) grid = c.sm_count;
+  if (grid < 1) grid = 1;
+  {
+    void* args[] = {&dA, &d, &diag, &off, &tau, &Vh, &pbuf, &ctrl};
+    DR4G_CUDA(cudaLaunchCooperativeKernel((const void*)tridiag_kernel, dim3(grid), dim3(kTriThreads), args, tri_smem,
+                                          c.stream));
+  }
+  // T2
+  const size_t bs_smem = (size_t)2 * d * sizeof(double);
+  static size_t bs_smem_set = 0;
+  if (bs_smem > 48 * 1024 && bs_smem > bs_smem_set) {
+    DR4G_CUDA(cudaFuncSetAttribute(bisect_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bs_smem));
+    bs_smem_set = bs_smem;
+  }
+  bisect_kernel<<<(k + 3) / 4, 128, bs_smem, c.stream>>>(diag, off, d, k, dW, info);
+  // T3
+  const size_t iv_smem = (size_t)5 * d * sizeof(double) + (size_t)d * sizeof(int);
+  static size_t iv_smem_set = 0;
+  if (iv_smem > 48 * 1024 && iv_smem > iv_smem_set) {
+    DR4G_CUDA(cudaFuncSetAttribute(invit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)iv_smem));
+    iv_smem_set = iv_smem;
+  }
+  invit_kernel<<<k, kInvThreads, iv_smem, c.stream>>>(diag, off, d, k, dW, info, dVt);
+  // T4
+  const size_t bt_smem = (size_t)d * sizeof(double);
+  backtransform_kernel<<<k, 256, bt_smem, c.stream>>>(Vh, tau, d, k, dVt);
+  c.launches += 4;
+  DR4G_CUDA(cudaGetLastError());
+}
+
+}  // namespace dr4g

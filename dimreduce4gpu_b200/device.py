@@ -223,6 +223,23 @@ class DeviceContext:
         _check(self._lib.dr4g_eigh_double(self._h, work.data_ptr(), d, w.data_ptr(), V.data_ptr()), "dr4g_eigh_double")
         return w, V
 
+    def eigh_topk(self, A, k: int):
+        """k largest eigenpairs of a symmetric fp64 matrix (the exact fit's solver).  Returns
+        (w descending (k,), Vt (k, d) unit eigenvectors in rows)."""
+        import torch
+
+        _need_cuda_contig(A, "A", self.device)
+        if A.dtype != torch.float64 or A.dim() != 2 or A.shape[0] != A.shape[1]:
+            raise ValueError("A must be a square float64 matrix")
+        d = A.shape[0]
+        work = A.clone()
+        w = torch.empty(k, dtype=torch.float64, device=A.device)
+        Vt = torch.empty(k, d, dtype=torch.float64, device=A.device)
+        self._on_torch_stream()
+        _check(self._lib.dr4g_eigh_topk_double(self._h, work.data_ptr(), d, int(k), w.data_ptr(), Vt.data_ptr()),
+               "dr4g_eigh_topk_double")
+        return w, Vt
+
     # ------------------------------------------------------------------ telemetry
     def stage_times(self) -> Optional[dict]:
         """Per-stage device ms of the last fit (call after sync)."""

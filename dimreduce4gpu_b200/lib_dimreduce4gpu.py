@@ -56,6 +56,7 @@ def _bind(lib: ctypes.CDLL) -> None:
     lib.dr4g_comm_init.argtypes, lib.dr4g_comm_init.restype = [vp, vp, ci, ci], ci
     lib.dr4g_comm_world.argtypes, lib.dr4g_comm_world.restype = [vp], ci
     lib.dr4g_eigh_double.argtypes, lib.dr4g_eigh_double.restype = [vp, vp, ci, vp, vp], ci
+    lib.dr4g_eigh_topk_double.argtypes, lib.dr4g_eigh_topk_double.restype = [vp, vp, ci, ci, vp, vp], ci
     lib.dr4g_stage_times.argtypes, lib.dr4g_stage_times.restype = [vp, c_double_p, ci], ci
     lib.dr4g_last_gram_path.argtypes, lib.dr4g_last_gram_path.restype = [vp], ci
     lib.dr4g_launch_count.argtypes, lib.dr4g_launch_count.restype = [vp], ll
@@ -68,7 +69,7 @@ EXPORTED_SYMBOLS = (
     "dr4g_sync", "dr4g_set_option", "dr4g_nccl_unique_id", "dr4g_comm_init", "dr4g_comm_world",
     "dr4g_fit_float", "dr4g_fit_double", "dr4g_transform_float", "dr4g_transform_double",
     "dr4g_inverse_transform_float", "dr4g_inverse_transform_double", "dr4g_colstats_float",
-    "dr4g_colstats_double", "dr4g_gram_float", "dr4g_gram_double", "dr4g_eigh_double", "dr4g_stage_times",
+    "dr4g_colstats_double", "dr4g_gram_float", "dr4g_gram_double", "dr4g_eigh_double", "dr4g_eigh_topk_double", "dr4g_stage_times",
     "dr4g_last_gram_path", "dr4g_launch_count",
 )
 

@@ -84,7 +84,8 @@ DR4G_EXPORT int dr4g_ctx_set_stream(dr4g_ctx* ctx, void* cuda_stream);
 /* Block until everything enqueued on the context's stream is done; returns deferred errors. */
 DR4G_EXPORT int dr4g_sync(dr4g_ctx* ctx);
 /* Tunables / test hooks.  Keys: "gram_path" (0 auto, 1 generic DMMA kernel, 2 tcgen05 kernel),
- * "flush_rows" (rows between TMEM accumulator flushes), "pilot_rows", "jacobi_tol", "jacobi_sweeps". */
+ * "flush_rows" (rows between TMEM accumulator flushes), "pilot_rows", "jacobi_tol", "jacobi_sweeps",
+ * "eig_solver" (exact path: 0 tridiagonal route for the top k, 1 blocked Jacobi), "timing". */
 DR4G_EXPORT int dr4g_set_option(dr4g_ctx* ctx, const char* key, double value);
 
 /* Row-sharded operation: rank 0 obtains a 128-byte NCCL unique id, the host layer ships it to
@@ -131,6 +132,10 @@ DR4G_EXPORT int dr4g_colstats_double(dr4g_ctx* ctx, const double* dX, long long 
 DR4G_EXPORT int dr4g_gram_float(dr4g_ctx* ctx, const float* dX, long long n, int d, const float* dshift, double* dG);
 DR4G_EXPORT int dr4g_gram_double(dr4g_ctx* ctx, const double* dX, long long n, int d, const double* dshift, double* dG);
 DR4G_EXPORT int dr4g_eigh_double(dr4g_ctx* ctx, double* dA, int d, double* dW, double* dV);
+/*   eigh_topk: the k largest eigenpairs of the symmetric dA (d x d, destroyed) by the tridiagonal
+ *             route the exact fit uses (replaces cusolverDn?syevd, src/matrix.cu:231-273): dW gets k
+ *             eigenvalues in descending order, dVt (k x d, row-major) unit eigenvectors in rows. */
+DR4G_EXPORT int dr4g_eigh_topk_double(dr4g_ctx* ctx, double* dA, int d, int k, double* dW, double* dVt);
 
 /* Per-stage device times (ms) of the last dr4g_fit_* on this context, valid after dr4g_sync:
  * [0] pilot shift, [1] Gram + column stats, [2] partial reduce + allreduce + centring,
