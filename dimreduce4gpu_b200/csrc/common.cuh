@@ -77,7 +77,7 @@ struct Ctx {
   int pilot_rows = 4096;      // rows sampled for the pilot shift
   double jacobi_tol = 0.0;    // 0 -> per-dtype default
   int jacobi_sweeps = 30;
-  int eig_solver = 0;         // exact path: 0 tridiagonal route (top-k), 1 blocked Jacobi (all pairs)
+  int eig_solver = 0;         // exact path: 0 tridiagonal route (top-k), 1 blocked Jacobi (all pairs), 2 tridiagonal route without the cluster-resident T1
   int timing = 1;             // record per-stage events
   // telemetry
   int last_gram_path = 0;

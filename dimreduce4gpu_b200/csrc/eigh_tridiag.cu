@@ -34,6 +34,17 @@ struct TriCtrl {
   unsigned int pad;
 };
 
+// Branch-free fp64 reciprocal: hardware seed (rcp.approx.ftz.f64, ~2^-23) + two Newton steps.  The
+// IEEE division is a ~160-cycle call-like sequence on sm_100 that also defeats ILP across
+// independent recurrences; this one is ~5 dependent instructions.  |x| must be a normal number.
+__device__ __forceinline__ double fast_rcp(double x) {
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+  r = fma(r, fma(-x, r, 1.0), r);
+  r = fma(r, fma(-x, r, 1.0), r);
+  return r;
+}
+
 __device__ __forceinline__ void tri_grid_barrier(TriCtrl* ctrl, unsigned int& target) {
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -60,32 +71,66 @@ __device__ __forceinline__ double tri_block_sum(double v, double* red) {
 
 // A: d x d symmetric, row-major, destroyed.  Out: diag[d], off[d] (off[s] couples s and s+1; off[d-1] = 0),
 // tau[d], Vh[d x d] (row s = reflector of column s, entries s+1.. with Vh[s][s+1] = 1).
+// xbuf: 4 x d doubles of exchange space: p' (two parities) and the published next row (two parities).
+// kRowsInSmem: every CTA keeps its rows of the trailing matrix in shared memory (no L2 round trip
+// in the row sweep); otherwise they stay in A (large d).
+template <bool kRowsInSmem>
 __global__ void __launch_bounds__(kTriThreads)
 tridiag_kernel(double* __restrict__ A, int d, double* __restrict__ diag, double* __restrict__ off,
-               double* __restrict__ tau, double* __restrict__ Vh, double* __restrict__ pbuf, TriCtrl* ctrl) {
+               double* __restrict__ tau, double* __restrict__ Vh, double* __restrict__ xbuf, TriCtrl* ctrl) {
   extern __shared__ double tri_sm[];
   double* v = tri_sm;          // previous reflector (full length d, zero outside its support)
   double* w = v + d;           // previous w
   double* vn = w + d;          // new reflector
-  double* row = vn + d;        // corrected row s / p'
+  double* row = vn + d;        // row s: raw, then corrected
+  double* pl = row + d;        // p of the previous iteration
+  double* R = pl + d;          // own rows (kRowsInSmem): slot (i / nw) * kTriWarps + warp
   __shared__ double red[kTriWarps];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int gw = blockIdx.x * kTriWarps + warp, nw = gridDim.x * kTriWarps;
   unsigned int target = 0;
+  double* pbuf = xbuf;
+  double* rbuf = xbuf + 2 * (size_t)d;
 
-  for (int c = tid; c < d; c += kTriThreads) { v[c] = 0.0; w[c] = 0.0; vn[c] = 0.0; }
+  for (int c = tid; c < d; c += kTriThreads) { v[c] = 0.0; w[c] = 0.0; vn[c] = 0.0; pl[c] = 0.0; }
+  if (kRowsInSmem) {
+    for (int i = gw; i < d; i += nw) {
+      double* Ri = R + (size_t)((i / nw) * kTriWarps + warp) * d;
+      for (int c = lane; c < d; c += 32) Ri[c] = A[(size_t)i * d + c];
+    }
+  }
   __syncthreads();
 
+  double tprev = 0.0;  // tau of reflector s-1 (every CTA computes the same value)
   for (int s = 0; s < d - 1; ++s) {
-    // ---- A: corrected row s and the reflector that eliminates r[s+2:]
+    // ---- (after the barrier) fetch p of reflector s-1 and the published row s in one round trip
+    if (s == 0) {
+      for (int c = tid; c < d; c += kTriThreads) row[c] = A[c];
+    } else {
+      const double* pp = pbuf + (size_t)((s - 1) & 1) * d;
+      const double* rp = rbuf + (size_t)(s & 1) * d;
+      for (int c = s + tid; c < d; c += kTriThreads) { pl[c] = __ldcg(&pp[c]); row[c] = __ldcg(&rp[c]); }
+    }
+    // w of reflector s-1:  w = p - (tau/2)(p.v) v   (vn still holds reflector s-1, tprev its tau)
+    double pv = 0.0;
+    for (int c = s + tid; c < d; c += kTriThreads) pv += pl[c] * vn[c];
+    pv = tri_block_sum(pv, red);
+    const double kk = 0.5 * tprev * pv;
+    for (int c = tid; c < d; c += kTriThreads) {
+      const double vv = vn[c];
+      v[c] = vv;
+      w[c] = c >= s ? pl[c] - kk * vv : 0.0;
+    }
+    __syncthreads();
+    // corrected row s and the reflector that eliminates r[s+2:]
     const double vs = v[s], ws = w[s];
     double nrm2 = 0.0;
     for (int c = s + tid; c < d; c += kTriThreads) {
-      const double r = __ldcg(&A[(size_t)s * d + c]) - vs * w[c] - ws * v[c];
+      const double r = row[c] - vs * w[c] - ws * v[c];
       row[c] = r;
       if (c > s + 1) nrm2 += r * r;
     }
-    nrm2 = tri_block_sum(nrm2, red);  // includes the barrier that publishes row[]
+    nrm2 = tri_block_sum(nrm2, red);
     const double x0 = row[s + 1];
     double beta = x0, t = 0.0, scale = 0.0;
     if (nrm2 > 0.0 && s < d - 2) {
@@ -100,41 +145,152 @@ tridiag_kernel(double* __restrict__ A, int d, double* __restrict__ diag, double*
       for (int c = tid; c < d; c += kTriThreads) Vh[(size_t)s * d + c] = c > s + 1 ? row[c] * scale : (c == s + 1 ? 1.0 : 0.0);
     }
     __syncthreads();
-    // ---- B: rank-2 update of own rows fused with p' = tau' A' v'
+    // ---- rank-2 update of own rows fused with p' = tau' A' v'; the owner of row s+1 publishes it
     for (int i = s + 1 + ((gw - (s + 1)) % nw + nw) % nw; i < d; i += nw) {
       const double vi = v[i], wi = w[i];
-      double* Ai = A + (size_t)i * d;
+      double* Ai = kRowsInSmem ? R + (size_t)((i / nw) * kTriWarps + warp) * d : A + (size_t)i * d;
+      double* pub = (i == s + 1) ? rbuf + (size_t)((s + 1) & 1) * d : nullptr;
       double dot = 0.0;
       for (int c = s + 1 + lane; c < d; c += 32) {
-        const double a = __ldcg(&Ai[c]) - vi * w[c] - wi * v[c];
-        __stcg(&Ai[c], a);
+        const double a = (kRowsInSmem ? Ai[c] : __ldcg(&Ai[c])) - vi * w[c] - wi * v[c];
+        if (kRowsInSmem) Ai[c] = a; else __stcg(&Ai[c], a);
+        if (pub) __stcg(&pub[c], a);
         dot = fma(a, vn[c], dot);
       }
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
       if (lane == 0) __stcg(&pbuf[(size_t)(s & 1) * d + i], t * dot);
     }
+    tprev = t;
     tri_grid_barrier(ctrl, target);
-    // ---- C: w' from p'
-    double pv = 0.0;
-    for (int c = s + 1 + tid; c < d; c += kTriThreads) {
-      const double p = __ldcg(&pbuf[(size_t)(s & 1) * d + c]);
-      row[c] = p;
-      pv += p * vn[c];
+  }
+  // last diagonal entry: row d-1 as published in iteration d-2 (that reflector is the identity: no correction)
+  if (blockIdx.x == 0 && tid == 0) {
+    const int s = d - 1;
+    diag[s] = d > 1 ? __ldcg(&rbuf[(size_t)(s & 1) * d + s]) : A[0];
+    off[s] = 0.0;
+    tau[s] = 0.0;
+  }
+}
+
+// ---------------------------------------------------------------- T1, cluster-resident variant (d <= 512)
+// Same algorithm inside ONE thread-block cluster (1, 8 or 16 CTAs): the trailing matrix lives in the
+// cluster's shared memory (rows cyclic over CTAs), the per-column exchange of p' goes through
+// distributed shared memory (each owner pushes its entry into every CTA), the hardware cluster
+// barrier replaces the atomic-counter grid barrier, and only the published row travels through L2.
+__device__ __forceinline__ unsigned cluster_rank() {
+  unsigned r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ unsigned cluster_size() {
+  unsigned r;
+  asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_barrier() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void st_cluster_f64(double* local_ptr, unsigned cta, double val) {
+  const unsigned la = static_cast<unsigned>(__cvta_generic_to_shared(local_ptr));
+  unsigned ra;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(la), "r"(cta));
+  asm volatile("st.shared::cluster.f64 [%0], %1;" ::"r"(ra), "d"(val) : "memory");
+}
+
+__global__ void __launch_bounds__(kTriThreads)
+tridiag_cluster_kernel(const double* __restrict__ A, int d, double* __restrict__ diag, double* __restrict__ off,
+                       double* __restrict__ tau, double* __restrict__ Vh, double* __restrict__ xbuf) {
+  extern __shared__ double tri_sm[];
+  double* v = tri_sm;
+  double* w = v + d;
+  double* vn = w + d;
+  double* row = vn + d;
+  double* pl = row + d;        // p, two parities (pushed into every CTA by the row owners)
+  double* R = pl + 2 * (size_t)d;  // own rows: slot i / cs
+  __shared__ double red[kTriWarps];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int rank = (int)cluster_rank(), cs = (int)cluster_size();
+  double* rbuf = xbuf + 2 * (size_t)d;  // published rows, two parities (global)
+
+  for (int c = tid; c < d; c += kTriThreads) { v[c] = 0.0; w[c] = 0.0; vn[c] = 0.0; pl[c] = 0.0; pl[d + c] = 0.0; }
+  for (int i = rank + cs * warp; i < d; i += cs * kTriWarps) {
+    double* Ri = R + (size_t)(i / cs) * d;
+    for (int c = lane; c < d; c += 32) Ri[c] = A[(size_t)i * d + c];
+  }
+  cluster_barrier();  // also orders the zero-initialisation of pl before any remote push
+
+  double tprev = 0.0;
+  for (int s = 0; s < d - 1; ++s) {
+    const double* pcur = pl + (size_t)((s + 1) & 1) * d;  // parity (s-1)&1
+    // row s: from own shared memory when this CTA owns it, else the copy its owner published
+    if (s == 0) {
+      for (int c = tid; c < d; c += kTriThreads) row[c] = A[c];
+    } else if (s % cs == rank) {
+      const double* Rs = R + (size_t)(s / cs) * d;
+      for (int c = s + tid; c < d; c += kTriThreads) row[c] = Rs[c];
+    } else {
+      const double* rp = rbuf + (size_t)(s & 1) * d;
+      for (int c = s + tid; c < d; c += kTriThreads) row[c] = __ldcg(&rp[c]);
     }
+    double pv = 0.0;
+    for (int c = s + tid; c < d; c += kTriThreads) pv += pcur[c] * vn[c];
     pv = tri_block_sum(pv, red);
-    const double kk = 0.5 * t * pv;
+    const double kk = 0.5 * tprev * pv;
     for (int c = tid; c < d; c += kTriThreads) {
       const double vv = vn[c];
       v[c] = vv;
-      w[c] = c > s ? row[c] - kk * vv : 0.0;
+      w[c] = c >= s ? pcur[c] - kk * vv : 0.0;
     }
     __syncthreads();
+    const double vs = v[s], ws = w[s];
+    double nrm2 = 0.0;
+    for (int c = s + tid; c < d; c += kTriThreads) {
+      const double r = row[c] - vs * w[c] - ws * v[c];
+      row[c] = r;
+      if (c > s + 1) nrm2 += r * r;
+    }
+    nrm2 = tri_block_sum(nrm2, red);
+    const double x0 = row[s + 1];
+    double beta = x0, t = 0.0, scale = 0.0;
+    if (nrm2 > 0.0 && s < d - 2) {
+      const double nrm = sqrt(x0 * x0 + nrm2);
+      beta = x0 >= 0.0 ? -nrm : nrm;
+      t = (beta - x0) / beta;
+      scale = 1.0 / (x0 - beta);
+    }
+    for (int c = tid; c < d; c += kTriThreads) vn[c] = c > s + 1 ? row[c] * scale : (c == s + 1 ? 1.0 : 0.0);
+    if (rank == 0) {
+      if (tid == 0) { diag[s] = row[s]; off[s] = beta; tau[s] = t; }
+      for (int c = tid; c < d; c += kTriThreads) Vh[(size_t)s * d + c] = c > s + 1 ? row[c] * scale : (c == s + 1 ? 1.0 : 0.0);
+    }
+    __syncthreads();
+    // own rows i > s: rank-2 update fused with p'_i; push p'_i into every CTA; publish row s+1
+    double* pnext = pl + (size_t)(s & 1) * d;
+    const int first = s + 1 + ((rank - (s + 1)) % cs + cs) % cs;  // first own row > s
+    for (int i = first + cs * warp; i < d; i += cs * kTriWarps) {
+      const double vi = v[i], wi = w[i];
+      double* Ri = R + (size_t)(i / cs) * d;
+      double* pub = (i == s + 1 && cs > 1) ? rbuf + (size_t)((s + 1) & 1) * d : nullptr;
+      double dot = 0.0;
+      for (int c = s + 1 + lane; c < d; c += 32) {
+        const double a = Ri[c] - vi * w[c] - wi * v[c];
+        Ri[c] = a;
+        if (pub) __stcg(&pub[c], a);
+        dot = fma(a, vn[c], dot);
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
+      if (lane < cs) st_cluster_f64(&pnext[i], (unsigned)lane, t * dot);
+    }
+    tprev = t;
+    cluster_barrier();
   }
-  // last diagonal entry: A[d-1][d-1] with the final rank-2 correction (v, w hold reflector d-2's, tau = 0 -> w = 0)
-  if (blockIdx.x == 0 && tid == 0) {
+  if (d == 1) {
+    if (tid == 0) { diag[0] = A[0]; off[0] = 0.0; tau[0] = 0.0; }
+  } else if ((d - 1) % cs == rank && tid == 0) {
     const int s = d - 1;
-    diag[s] = __ldcg(&A[(size_t)s * d + s]) - 2.0 * v[s] * w[s];
+    diag[s] = R[(size_t)(s / cs) * d + s];
     off[s] = 0.0;
     tau[s] = 0.0;
   }
@@ -153,7 +309,7 @@ __device__ __forceinline__ int sturm_count(const double* __restrict__ dg, const 
   if (fabs(q) < pivmin) q = -pivmin;
   cnt += q < 0.0;
   for (int i = 1; i < d; ++i) {
-    q = dg[i] - x - e2[i - 1] / q;
+    q = dg[i] - x - e2[i - 1] * fast_rcp(q);
     if (fabs(q) < pivmin) q = -pivmin;
     cnt += q < 0.0;
   }
@@ -200,15 +356,39 @@ bisect_kernel(const double* __restrict__ diag, const double* __restrict__ off, i
   const int j = blockIdx.x * nwarp + warp;
   if (j >= k) return;
   const int idx = d - 1 - j;  // 0-based index in ascending order: count(x) <= idx  <=>  x <= lambda_idx
-  for (int it = 0; it < 16; ++it) {
+  // 128-section: 4 independent Sturm recurrences per lane (the divide latency is the cost of a pass).
+  // Stops at 1e-13 ||T||: T3 refines every value with the Rayleigh quotient of its vector.
+  const double atol = 1e-13 * tnorm + 2.0 * pivmin;
+  for (int it = 0; it < 12; ++it) {
     const double width = hi - lo;
-    if (!(width > 2.0 * DBL_EPSILON * fmax(fabs(lo), fabs(hi)) + 2.0 * pivmin)) break;
-    const double x = lo + width * (double)(lane + 1) / 33.0;
-    const int cnt = sturm_count(dg, e2, d, x, pivmin);
-    const unsigned above = __ballot_sync(0xffffffffu, cnt > idx);  // x_l already to the right of lambda_idx
-    const int first = above ? __ffs(above) - 1 : 32;
-    const double nlo = first == 0 ? lo : lo + width * (double)first / 33.0;
-    const double nhi = first == 32 ? hi : lo + width * (double)(first + 1) / 33.0;
+    if (!(width > atol)) break;
+    double x[4], q[4];
+    int cnt[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      x[u] = lo + width * (double)(4 * lane + u + 1) / 129.0;
+      q[u] = dg[0] - x[u];
+      if (fabs(q[u]) < pivmin) q[u] = -pivmin;
+      cnt[u] = q[u] < 0.0;
+    }
+    for (int i = 1; i < d; ++i) {
+      const double di = dg[i], ei = e2[i - 1];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        q[u] = di - x[u] - ei * fast_rcp(q[u]);
+        if (fabs(q[u]) < pivmin) q[u] = -pivmin;
+        cnt[u] += q[u] < 0.0;
+      }
+    }
+    int fl = 4;
+#pragma unroll
+    for (int u = 3; u >= 0; --u) if (cnt[u] > idx) fl = u;  // counts are monotone in x: first shift right of lambda_idx
+    const unsigned m = __ballot_sync(0xffffffffu, fl < 4);
+    const int lane1 = m ? __ffs(m) - 1 : 0;
+    const int u1 = __shfl_sync(0xffffffffu, fl, lane1);
+    const int first = m ? lane1 * 4 + u1 : 128;
+    const double nlo = first == 0 ? lo : lo + width * (double)first / 129.0;
+    const double nhi = first == 128 ? hi : lo + width * (double)(first + 1) / 129.0;
     lo = nlo;
     hi = nhi;
   }
@@ -241,7 +421,8 @@ __device__ __forceinline__ double hash_uniform(unsigned a, unsigned b) {
 
 __global__ void __launch_bounds__(kInvThreads)
 invit_kernel(const double* __restrict__ diag, const double* __restrict__ off, int d, int k,
-             const double* __restrict__ lam, const double* __restrict__ info, double* __restrict__ Z) {
+             const double* __restrict__ lam, const double* __restrict__ info, double* __restrict__ lam_out,
+             double* __restrict__ Z) {
   const int j0 = blockIdx.x;
   const double tnorm = info[0];
   const double ortol = 1e-3 * tnorm;
@@ -267,20 +448,23 @@ invit_kernel(const double* __restrict__ diag, const double* __restrict__ off, in
     double x = lam[j];
     if (j > j0 && prev - x < 10.0 * eps * tnorm) x = prev - 10.0 * eps * tnorm;
     prev = x;
-    // ---- factor T - x I = P L U (partial pivoting), sequential
+    // ---- factor T - x I = P L U (partial pivoting), sequential; a[] ends up holding 1 / pivot
     if (tid == 0) {
       for (int i = 0; i < d; ++i) { a[i] = diag[i] - x; b[i] = i < d - 1 ? off[i] : 0.0; c[i] = b[i]; d2[i] = 0.0; }
       for (int i = 0; i < d - 1; ++i) {
-        if (fabs(a[i]) >= fabs(c[i])) {
+        if (fabs(a[i]) >= fabs(c[i]) || fabs(c[i]) < tiny) {
           double pv = a[i];
-          if (fabs(pv) < tiny) { pv = pv < 0 ? -tiny : tiny; a[i] = pv; }
-          const double m = c[i] / pv;
+          if (fabs(pv) < tiny) pv = pv < 0 ? -tiny : tiny;
+          const double ip = fast_rcp(pv);
+          const double m = c[i] * ip;
+          a[i] = ip;
           a[i + 1] -= m * b[i];
           c[i] = m;
           piv[i] = 0;
         } else {
-          const double m = a[i] / c[i];
-          a[i] = c[i];
+          const double ip = fast_rcp(c[i]);
+          const double m = a[i] * ip;
+          a[i] = ip;
           const double t = a[i + 1];
           a[i + 1] = b[i] - m * t;
           if (i < d - 2) { d2[i] = b[i + 1]; b[i + 1] = -m * d2[i]; }
@@ -289,11 +473,13 @@ invit_kernel(const double* __restrict__ diag, const double* __restrict__ off, in
           piv[i] = 1;
         }
       }
-      if (fabs(a[d - 1]) < tiny) a[d - 1] = a[d - 1] < 0 ? -tiny : tiny;
+      double pv = a[d - 1];
+      if (fabs(pv) < tiny) pv = pv < 0 ? -tiny : tiny;
+      a[d - 1] = fast_rcp(pv);
     }
     for (int i = tid; i < d; i += kInvThreads) z[i] = hash_uniform((unsigned)i, (unsigned)j * 7919u + 13u);
     __syncthreads();
-    for (int iter = 0; iter < 4; ++iter) {
+    for (int iter = 0; iter < 3; ++iter) {
       if (tid == 0) {
         if (iter > 0) {  // apply P, L to the right-hand side (the first solve uses U only, as dstein does)
           for (int i = 0; i < d - 1; ++i) {
@@ -305,7 +491,7 @@ invit_kernel(const double* __restrict__ diag, const double* __restrict__ off, in
           double t = z[i];
           if (i < d - 1) t -= b[i] * z[i + 1];
           if (i < d - 2) t -= d2[i] * z[i + 2];
-          z[i] = t / a[i];
+          z[i] = t * a[i];
         }
       }
       __syncthreads();
@@ -338,7 +524,18 @@ invit_kernel(const double* __restrict__ diag, const double* __restrict__ off, in
       for (int i = tid; i < d; i += kInvThreads) z[i] *= rn;
       __syncthreads();
     }
-    for (int i = tid; i < d; i += kInvThreads) Z[(size_t)j * d + i] = z[i];
+    // Rayleigh quotient z^T T z refines the multisection value (lam itself stays read-only: the
+    // other CTAs derive the cluster boundaries from it)
+    double rq = 0.0;
+    for (int i = tid; i < d; i += kInvThreads) {
+      double tz = diag[i] * z[i];
+      if (i > 0) tz += off[i - 1] * z[i - 1];
+      if (i < d - 1) tz += off[i] * z[i + 1];
+      rq += z[i] * tz;
+      Z[(size_t)j * d + i] = z[i];
+    }
+    rq = inv_block_sum(rq, red);
+    if (tid == 0) lam_out[j] = rq;
     __threadfence_block();
     __syncthreads();
   }
@@ -354,12 +551,35 @@ backtransform_kernel(const double* __restrict__ Vh, const double* __restrict__ t
   const int tid = threadIdx.x, j = blockIdx.x;
   for (int i = tid; i < d; i += 256) z[i] = Z[(size_t)j * d + i];
   __syncthreads();
+  // reflector rows are prefetched one step ahead (registers), so the L2 latency is off the
+  // dependent chain; d <= 256 * kBtPer elements per row, longer rows fall back to direct loads
+  constexpr int kBtPer = 4;
+  const bool pre = d <= 256 * kBtPer;
+  double nxt[kBtPer];
+  auto fetch = [&](int s) {
+    const double* vr = Vh + (size_t)s * d;
+#pragma unroll
+    for (int u = 0; u < kBtPer; ++u) {
+      const int i = tid + 256 * u;
+      nxt[u] = (i > s && i < d) ? __ldg(&vr[i]) : 0.0;
+    }
+  };
+  if (pre && d >= 3) fetch(d - 3);
   for (int s = d - 3; s >= 0; --s) {
     const double t = tau[s];
+    double cur[kBtPer];
+#pragma unroll
+    for (int u = 0; u < kBtPer; ++u) cur[u] = nxt[u];
+    if (pre && s > 0) fetch(s - 1);
     if (t == 0.0) continue;
     const double* vr = Vh + (size_t)s * d;
     double dot = 0.0;
-    for (int i = s + 1 + tid; i < d; i += 256) dot += vr[i] * z[i];
+    if (pre) {
+#pragma unroll
+      for (int u = 0; u < kBtPer; ++u) { const int i = tid + 256 * u; if (i < d) dot += cur[u] * z[i]; }
+    } else {
+      for (int i = s + 1 + tid; i < d; i += 256) dot += vr[i] * z[i];
+    }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
     if ((tid & 31) == 0) red[tid >> 5] = dot;
@@ -368,7 +588,12 @@ backtransform_kernel(const double* __restrict__ Vh, const double* __restrict__ t
 #pragma unroll
     for (int wv = 0; wv < 8; ++wv) tot += red[wv];
     tot *= t;
-    for (int i = s + 1 + tid; i < d; i += 256) z[i] -= tot * vr[i];
+    if (pre) {
+#pragma unroll
+      for (int u = 0; u < kBtPer; ++u) { const int i = tid + 256 * u; if (i < d) z[i] -= tot * cur[u]; }
+    } else {
+      for (int i = s + 1 + tid; i < d; i += 256) z[i] -= tot * vr[i];
+    }
     __syncthreads();
   }
   for (int i = tid; i < d; i += 256) Z[(size_t)j * d + i] = z[i];
@@ -382,7 +607,7 @@ static size_t tri_r256(size_t b) { return (b + 255) / 256 * 256; }
 size_t eigh_topk_workspace_bytes(int d, int k) {
   return tri_r256((size_t)d * d * 8)      // Vh
          + 3 * tri_r256((size_t)d * 8)    // diag, off, tau
-         + tri_r256((size_t)2 * d * 8)    // pbuf
+         + tri_r256((size_t)4 * d * 8)    // p' / published-row exchange
          + tri_r256((size_t)k * 8)        // lam
          + 256 + 256;                     // info, ctrl
 }
@@ -395,29 +620,57 @@ void launch_eigh_topk(Ctx& c, double* dA, int d, int k, double* dW, double* dVt,
   double* diag = reinterpret_cast<double*>(take((size_t)d * 8));
   double* off = reinterpret_cast<double*>(take((size_t)d * 8));
   double* tau = reinterpret_cast<double*>(take((size_t)d * 8));
-  double* pbuf = reinterpret_cast<double*>(take((size_t)2 * d * 8));
+  double* xbuf = reinterpret_cast<double*>(take((size_t)4 * d * 8));
   double* info = reinterpret_cast<double*>(take(256));
   TriCtrl* ctrl = reinterpret_cast<TriCtrl*>(take(256));
-  (void)take((size_t)k * 8);
+  double* lam = reinterpret_cast<double*>(take((size_t)k * 8));
   DR4G_CUDA(cudaMemsetAsync(ctrl, 0, sizeof(TriCtrl), c.stream));
 
-  // T1
-  const size_t tri_smem = (size_t)4 * d * sizeof(double);
-  static size_t tri_smem_set = 0;
-  if (tri_smem > 48 * 1024 && tri_smem > tri_smem_set) {
-    DR4G_CUDA(cudaFuncSetAttribute(tridiag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tri_smem));
-    tri_smem_set = tri_smem;
-  }
-  int per_sm = 0;
-  DR4G_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tridiag_kernel, kTriThreads, tri_smem));
-  if (per_sm < 1) fail("eigh: tridiagonalisation kernel cannot be made resident for d=%d", d);
-  int grid = (d + kTriWarps - 1) / kTriWarps;
-  if (grid > c.sm_count) grid = c.sm_count;
-  if (grid < 1) grid = 1;
-  {
-    void* args[] = {&dA, &d, &diag, &off, &tau, &Vh, &pbuf, &ctrl};
-    DR4G_CUDA(cudaLaunchCooperativeKernel((const void*)tridiag_kernel, dim3(grid), dim3(kTriThreads), args, tri_smem,
-                                          c.stream));
+  // T1: d <= 512 runs inside one thread-block cluster (hardware barrier, DSMEM exchange); larger d uses
+  // the cooperative grid with an atomic barrier, rows in shared memory whenever they fit
+  if (d <= 512 && c.eig_solver != 2) {
+    const int cs = d <= 128 ? 1 : (d <= 256 ? 8 : 16);
+    const size_t smem = ((size_t)6 * d + (size_t)((d + cs - 1) / cs) * d) * sizeof(double);
+    static size_t smem_set = 0;
+    static bool nonportable_set = false;
+    if (smem > 48 * 1024 && smem > smem_set) {
+      DR4G_CUDA(cudaFuncSetAttribute(tridiag_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      smem_set = smem;
+    }
+    if (cs > 8 && !nonportable_set) {
+      DR4G_CUDA(cudaFuncSetAttribute(tridiag_cluster_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+      nonportable_set = true;
+    }
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(cs);
+    cfg.blockDim = dim3(kTriThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = c.stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = cs;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    DR4G_CUDA(cudaLaunchKernelEx(&cfg, tridiag_cluster_kernel, (const double*)dA, d, diag, off, tau, Vh, xbuf));
+  } else {
+    int grid = (d + 2 * kTriWarps - 1) / (2 * kTriWarps);
+    if (grid > c.sm_count) grid = c.sm_count;
+    if (grid < 1) grid = 1;
+    const int nw = grid * kTriWarps;
+    const size_t vec_smem = (size_t)5 * d * sizeof(double);
+    const size_t rows_smem = (size_t)((d + nw - 1) / nw) * kTriWarps * d * sizeof(double);
+    const bool in_smem = vec_smem + rows_smem <= 200 * 1024;
+    const size_t tri_smem = vec_smem + (in_smem ? rows_smem : 0);
+    const void* tri_fn = in_smem ? (const void*)tridiag_kernel<true> : (const void*)tridiag_kernel<false>;
+    static size_t tri_smem_set[2] = {0, 0};
+    if (tri_smem > 48 * 1024 && tri_smem > tri_smem_set[in_smem]) {
+      DR4G_CUDA(cudaFuncSetAttribute(tri_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tri_smem));
+      tri_smem_set[in_smem] = tri_smem;
+    }
+    void* args[] = {&dA, &d, &diag, &off, &tau, &Vh, &xbuf, &ctrl};
+    DR4G_CUDA(cudaLaunchCooperativeKernel(tri_fn, dim3(grid), dim3(kTriThreads), args, tri_smem, c.stream));
   }
   // T2
   const size_t bs_smem = (size_t)2 * d * sizeof(double);
@@ -426,7 +679,7 @@ void launch_eigh_topk(Ctx& c, double* dA, int d, int k, double* dW, double* dVt,
     DR4G_CUDA(cudaFuncSetAttribute(bisect_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bs_smem));
     bs_smem_set = bs_smem;
   }
-  bisect_kernel<<<(k + 3) / 4, 128, bs_smem, c.stream>>>(diag, off, d, k, dW, info);
+  bisect_kernel<<<(k + 3) / 4, 128, bs_smem, c.stream>>>(diag, off, d, k, lam, info);
   // T3
   const size_t iv_smem = (size_t)5 * d * sizeof(double) + (size_t)d * sizeof(int);
   static size_t iv_smem_set = 0;
@@ -434,7 +687,7 @@ void launch_eigh_topk(Ctx& c, double* dA, int d, int k, double* dW, double* dVt,
     DR4G_CUDA(cudaFuncSetAttribute(invit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)iv_smem));
     iv_smem_set = iv_smem;
   }
-  invit_kernel<<<k, kInvThreads, iv_smem, c.stream>>>(diag, off, d, k, dW, info, dVt);
+  invit_kernel<<<k, kInvThreads, iv_smem, c.stream>>>(diag, off, d, k, lam, info, dW, dVt);
   // T4
   const size_t bt_smem = (size_t)d * sizeof(double);
   backtransform_kernel<<<k, 256, bt_smem, c.stream>>>(Vh, tau, d, k, dVt);
