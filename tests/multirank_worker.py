@@ -1,0 +1,119 @@
+"""Worker for the world_size > 1 tests (launched by torch.distributed.run).
+
+mode=cpu : gloo.  Mirrors, in numpy, the exchange structure of fit_impl (csrc/api.cu): pilot-shift
+           allreduce of (d+1) numbers, one allreduce of the packed [G | s | q | n] partials, replicated
+           centring + eigensolve, and checks the result against the oracle on the concatenated rows.
+mode=gpu : nccl, one process per GPU.  The real thing: DeviceContext.init_comm_from_torch + sharded
+           dr4g_fit_float, compared with a single-GPU fit of the concatenated rows on rank 0 and
+           with the oracle."""
+from __future__ import annotations
+
+import os
+import sys
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parents[1]
+sys.path.insert(0, str(ROOT))
+sys.path.insert(0, str(ROOT / "tests"))
+
+
+def make_rows(rank: int, n: int, d: int) -> np.ndarray:
+    rng = np.random.default_rng(4321 + rank)
+    X = rng.standard_normal((n, d)) * np.linspace(1.0, 3.0, d) + np.linspace(-5.0, 5.0, d)
+    return X.astype(np.float32)
+
+
+def main() -> None:
+    import torch
+    import torch.distributed as dist
+
+    from oracle import cpu_oracle as O
+
+    mode, n, d, k = sys.argv[1], int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4])
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    n_local = n + 7 * rank  # ragged shards
+    X = make_rows(rank, n_local, d)
+
+    if mode == "cpu":
+        dist.init_process_group("gloo")
+        Xd = X.astype(np.float64)
+        rows = min(n_local, 4096)
+        pilot = torch.from_numpy(np.concatenate([Xd[:rows].sum(0), [float(rows)]]))
+        dist.all_reduce(pilot)
+        c = (pilot[:d] / pilot[d]).numpy().astype(np.float32).astype(np.float64)  # shift is held in fp32
+        Y = Xd - c
+        packed = torch.from_numpy(np.concatenate([(Y.T @ Y).ravel(), Y.sum(0), (Y * Y).sum(0), [float(n_local)]]))
+        dist.all_reduce(packed)
+        p = packed.numpy()
+        G, s, q, nt = p[: d * d].reshape(d, d), p[d * d: d * d + d], p[d * d + d: d * d + 2 * d], p[-1]
+        C = G - np.outer(s, s) / nt
+        mean = c + s / nt
+        total_var = float(((q - s * s / nt) / (nt - 1)).sum())
+        w, V = np.linalg.eigh(C)
+        w, V = w[::-1][:k], V[:, ::-1][:, :k].T
+        sv = np.sqrt(np.maximum(w, 0))
+        ev = sv ** 2 / (nt - 1)
+        gathered = [None] * world
+        dist.all_gather_object(gathered, X)
+        if rank == 0:
+            ref = O.restated_pca(np.concatenate(gathered), k, dtype=np.float64)
+            assert int(nt) == sum(g.shape[0] for g in gathered)
+            np.testing.assert_allclose(sv, ref.singular_values, rtol=1e-9)
+            np.testing.assert_allclose(ev, ref.explained_variance, rtol=1e-9)
+            np.testing.assert_allclose(ev / total_var, ref.explained_variance_ratio, rtol=1e-9)
+            np.testing.assert_allclose(mean, ref.mean, atol=1e-9)
+            (Cr,), (Co,) = O.svd_flip_v(ref.components), O.svd_flip_v(V)
+            assert O.max_principal_angle(Cr, Co) < 1e-6
+            print("MULTIRANK_CPU_OK", flush=True)
+        dist.barrier()
+        dist.destroy_process_group()
+        return
+
+    import dimreduce4gpu_b200 as pkg
+
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    ctx = pkg.DeviceContext(local)
+    ctx.init_comm_from_torch()
+    Xg = torch.from_numpy(X).cuda()
+    out = {}
+    for alg in ("cusolver", "power"):
+        res = ctx.fit(Xg, k, center=True, algorithm=alg, n_iter=60, random_state=3, tol=1e-9)
+        ctx.sync()
+        out[alg] = {kk: v.cpu().numpy() for kk, v in res.items() if v is not None}
+    Z = ctx.transform(Xg, res["components"], mean=res["mean"]).cpu().numpy()
+    # every rank must hold the same model (replicated eigensolve on identical all-reduced inputs)
+    mine = torch.from_numpy(out["cusolver"]["components"]).cuda()
+    ref0 = mine.clone()
+    dist.broadcast(ref0, src=0)
+    assert torch.equal(mine, ref0), "ranks disagree on components_"
+    gathered = [None] * world
+    dist.all_gather_object(gathered, X)
+    if rank == 0:
+        Xall = np.concatenate(gathered)
+        ref = O.RefLib().pca(Xall, k, "cusolver") if O.REF_SO.is_file() else O.restated_pca(Xall, k)
+        single = pkg.DeviceContext(local)
+        one = single.fit(torch.from_numpy(Xall).cuda(), k, center=True)
+        single.sync()
+        s1 = one["singular_values"].cpu().numpy()
+        for alg, tol in (("cusolver", 1e-4), ("power", 1e-3)):
+            s = out[alg]["singular_values"]
+            assert np.max(np.abs(s - ref.singular_values) / ref.singular_values) < tol, alg
+        np.testing.assert_allclose(out["cusolver"]["singular_values"], s1, rtol=2e-5)
+        np.testing.assert_allclose(out["cusolver"]["mean"], ref.mean, atol=1e-4)
+        (Cr,), (Co,) = O.svd_flip_v(ref.components), O.svd_flip_v(out["cusolver"]["components"])
+        assert O.max_principal_angle(Cr, Co) < 1e-2
+        # shard-local transform: rank 0's rows of the reference scores
+        Zr = (Xall[: X.shape[0]].astype(np.float64) - ref.mean) @ ref.components.T.astype(np.float64)
+        sgn = np.sign(np.sum(Zr * Z, axis=0))
+        assert np.max(np.abs(Zr - Z * sgn)) < 5e-3 * ref.singular_values[0] / np.sqrt(Xall.shape[0]) * 10
+        print("MULTIRANK_GPU_OK", flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
