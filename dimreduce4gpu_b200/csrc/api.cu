@@ -232,7 +232,7 @@ static void fit_impl(Ctx& c, const T* dX, long long n_local, int d, int k, int c
       void* slabs = c.arena.take(gram_tc_workspace_bytes(c, d));
       launch_gram_tc(c, Xf, n_local, d, reinterpret_cast<const float*>(shift_arg), G, s, q, slabs);
       used_tc = true;
-    } else if (c.gram_path == 2) {
+    } else if (c.gram_path >= 2) {
       fail("gram_path=2 (tcgen05) requested but the shape is not eligible: n=%lld d=%d", n_local, d);
     }
   }
@@ -241,7 +241,7 @@ static void fit_impl(Ctx& c, const T* dX, long long n_local, int d, int k, int c
     launch_gram_generic<T>(c, dX, n_local, d, shift_arg, G);
     launch_mirror_upper(c, G, d);
   }
-  c.last_gram_path = used_tc ? 2 : 1;
+  c.last_gram_path = used_tc ? (c.last_gram_kernel == 2 ? 3 : 2) : 1;
   launch_set_scalar(c, cnt, (double)n_local);
   mark(2);
 
@@ -547,9 +547,9 @@ int dr4g_gram_float(dr4g_ctx* ctx, const float* dX, long long n, int d, const fl
     ctx->arena.reserve(ws + 4096);
     ctx->arena.reset();
     launch_gram_tc(*ctx, dX, n, d, dshift, dG, nullptr, nullptr, ctx->arena.take(ws));
-    ctx->last_gram_path = 2;
+    ctx->last_gram_path = ctx->last_gram_kernel == 2 ? 3 : 2;
   } else {
-    if (ctx->gram_path == 2) fail("gram_path=2 (tcgen05) requested but the shape is not eligible: n=%lld d=%d", n, d);
+    if (ctx->gram_path >= 2) fail("gram_path=2 (tcgen05) requested but the shape is not eligible: n=%lld d=%d", n, d);
     launch_gram_generic<float>(*ctx, dX, n, d, dshift, dG);
     launch_mirror_upper(*ctx, dG, d);
     ctx->last_gram_path = 1;

@@ -72,7 +72,7 @@ struct Ctx {
   void* comm = nullptr;
   int rank = 0, world = 1;
   // options
-  int gram_path = 0;          // 0 auto, 1 generic, 2 tcgen05
+  int gram_path = 0;          // 0 auto, 1 generic, 2 tcgen05 (pair kernel where eligible), 3 tcgen05 single-CTA kernel only
   int flush_rows = 1024;      // rows between TMEM flushes in the tcgen05 Gram
   int pilot_rows = 4096;      // rows sampled for the pilot shift
   double jacobi_tol = 0.0;    // 0 -> per-dtype default
@@ -81,6 +81,7 @@ struct Ctx {
   int timing = 1;             // record per-stage events
   // telemetry
   int last_gram_path = 0;
+  int last_gram_kernel = 0;   // tcgen05 path: 1 single-CTA kernel (gram_tc.cu), 2 CTA-pair kernel (gram_tc2.cu)
   long long launches = 0;
   // tensor-map encoder (driver entry point fetched lazily)
   void* encode_tiled = nullptr;
@@ -105,6 +106,13 @@ bool gram_tc_eligible(const Ctx& c, const float* dX, long long n, int d);
 size_t gram_tc_workspace_bytes(const Ctx& c, int d);  // per-CTA fp32 partial-tile slabs
 void launch_gram_tc(Ctx& c, const float* dX, long long n, int d, const float* dshift, double* dG, double* dsum,
                     double* dsumsq, void* workspace);
+
+// CTA-pair variant (gram_tc2.cu): d > 128, d % 32 == 0.  Dispatched by launch_gram_tc.
+bool gram_pair_eligible(const Ctx& c, const float* dX, long long n, int d);
+size_t gram_pair_workspace_bytes(const Ctx& c, int d);
+void launch_gram_pair(Ctx& c, const float* dX, long long n, int d, const float* dshift, double* dG, double* dsum,
+                      double* dsumsq, void* workspace);
+void* tensor_map_encoder(Ctx& c);  // cuTensorMapEncodeTiled, fetched lazily through the runtime
 
 // K3: finalize.  packed = [G (d*d) | s (d) | q (d) | n (1)] doubles.
 // dsum_and_count = [column sums (d) | row count (1)] of the pilot sample (all-reduced across ranks)

@@ -36,6 +36,8 @@
 // 32-byte chunks (chunk ^= row % 4) exactly as TMA writes it (SWIZZLE_128B_ATOM_32B) and as the UMMA
 // descriptor reads it (SWIZZLE_128B_BASE32B, the only layout kind::tf32 takes for MN-major
 // operands; LBO = KT*128, SBO = 512).
+#include <cstdio>
+#include <cstdlib>
 #include <mutex>
 
 #include "common.cuh"
@@ -74,12 +76,20 @@ struct TcJobTable {
   TcJob job[kMaxJobs];
 };
 
+// Debug aid (DR4G_GRAM_TRACE=1): CTA 0 records clock64() at the pipeline hand-offs of its first
+// kTraceIts chunks: [it][0] TMA: stage free, [1] TMA issued, [2] conv: data landed, [3] conv: converted,
+// [4] conv: arrived, [5] MMA: operands ready, [6] MMA: issued + committed.
+constexpr int kTraceIts = 96;
+__device__ long long g_trace[kTraceIts * 8];
+#define DR4G_TRACE(ev) \
+  do { if (trace && blockIdx.x == 0 && it < kTraceIts) g_trace[it * 8 + (ev)] = clock64(); } while (0)
+
 __device__ __forceinline__ float clear13(float v) { return __uint_as_float(__float_as_uint(v) & 0xffffe000u); }
 
 __global__ void __launch_bounds__(kThreads, 1)
 gram_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ TcJobTable table, long long n, int d,
                const float* __restrict__ shift, float* __restrict__ slab, double* __restrict__ osum,
-               double* __restrict__ osq, int flush_rows) {
+               double* __restrict__ osq, int flush_rows, int trace) {
   // ---------------------------------------------------------------- which job / which chunks
   int ji = 0;
   while (ji + 1 < table.njobs && (int)blockIdx.x >= table.job[ji + 1].cta_begin) ++ji;
@@ -125,6 +135,7 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__
         const int s = it % kStages;
         const uint32_t ph = (uint32_t)(it / kStages) & 1u;
         ptx::mbar_wait(ptx::smem_u32(&bar_empty[s]), ph ^ 1u);
+        DR4G_TRACE(0);
         const long long row0 = ((long long)split + (long long)it * job.ncta) * kt;
         // boxes wholly outside the matrix are not loaded (the converters write zeros there)
         int boxes = 0;
@@ -146,6 +157,7 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__
               ptx::tma_load_2d(sx + (uint32_t)(((bi * 4 + sub) * kt + rc * kBoxRows) * 128), &tmap, full, col, (int)row);
             }
           }
+        DR4G_TRACE(1);
       }
     }
   } else if (warp == kConvWarps + 1) {
@@ -165,6 +177,7 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__
         }
         ptx::mbar_wait(ptx::smem_u32(&bar_conv[s]), ph);
         ptx::tc_fence_after_sync();
+        DR4G_TRACE(5);
         const uint32_t sx = smem_base + (uint32_t)s * kStageBytes;
         for (int ks = 0; ks < kt / 8; ++ks) {
           const uint32_t acc = (window_start && ks == 0) ? 0u : 1u;
@@ -182,6 +195,7 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__
           }
         }
         ptx::mma_commit(ptx::smem_u32(&bar_empty[s]));
+        DR4G_TRACE(6);
         const bool window_end = ((it + 1) % flush_chunks) == 0 || it == my_chunks - 1;
         if (window_end) {
           ptx::mma_commit(ptx::smem_u32(&bar_acc_full));
@@ -244,6 +258,7 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__
       const int s = it % kStages;
       const uint32_t ph = (uint32_t)(it / kStages) & 1u;
       ptx::mbar_wait(ptx::smem_u32(&bar_full[s]), ph);
+      if (tid == 0) DR4G_TRACE(2);
       const long long row0 = ((long long)split + (long long)it * job.ncta) * kt;
       const uint32_t sx = smem_base + (uint32_t)s * kStageBytes + q_off;
       if (has_block) {
@@ -272,9 +287,11 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__
           for (int j = 0; j < 4; ++j) { ds[j] += (double)fs[j]; dq[j] += (double)fq[j]; }
         }
       }
+      if (tid == 0) DR4G_TRACE(3);
       ptx::fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&bar_conv[s]));
+      if (tid == 0) DR4G_TRACE(4);
 
       const int e = it - kLookahead;
       if (e >= 0 && (e + 1) % flush_chunks == 0) epilogue(windows_done++);
@@ -331,7 +348,11 @@ using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t
                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
-EncodeTiledFn encode_tiled_fn(Ctx& c) {
+EncodeTiledFn encode_tiled_fn(Ctx& c) { return reinterpret_cast<EncodeTiledFn>(tensor_map_encoder(c)); }
+
+}  // namespace
+
+void* tensor_map_encoder(Ctx& c) {
   if (!c.encode_tiled) {
     void* fn = nullptr;
     cudaDriverEntryPointQueryResult qres;
@@ -339,8 +360,10 @@ EncodeTiledFn encode_tiled_fn(Ctx& c) {
     if (qres != cudaDriverEntryPointSuccess || !fn) fail("cuTensorMapEncodeTiled is not available in this driver");
     c.encode_tiled = fn;
   }
-  return reinterpret_cast<EncodeTiledFn>(c.encode_tiled);
+  return c.encode_tiled;
 }
+
+namespace {
 
 // Cut the block upper triangle into jobs: column blocks are paired into super-blocks of 256
 // columns; job (I, J), I <= J, owns the tiles between super-blocks I and J.
@@ -393,7 +416,12 @@ bool build_jobs(int d, int sm_count, TcJobTable& tab) {
 
 }  // namespace
 
+static bool use_pair(const Ctx& c, const float* dX, long long n, int d) {
+  return c.gram_path != 3 && gram_pair_eligible(c, dX, n, d);
+}
+
 bool gram_tc_eligible(const Ctx& c, const float* dX, long long n, int d) {
+  if (use_pair(c, dX, n, d)) return true;
   if (n < 1 || d < 4 || (d % 4) != 0) return false;                 // TMA: 16-byte row pitch
   if ((reinterpret_cast<uintptr_t>(dX) & 15) != 0) return false;    // TMA: 16-byte base
   if (n >= (1ll << 31)) return false;                               // TMA coordinates are int32
@@ -403,13 +431,23 @@ bool gram_tc_eligible(const Ctx& c, const float* dX, long long n, int d) {
 
 size_t gram_tc_workspace_bytes(const Ctx& c, int d) {
   TcJobTable tab;
-  if (!build_jobs(d, c.sm_count, tab)) return 0;
-  const int grid = tab.job[tab.njobs - 1].cta_begin + tab.job[tab.njobs - 1].ncta;
-  return (size_t)grid * 4 * kBlk * kBlk * sizeof(float);
+  size_t single = 0;
+  if (build_jobs(d, c.sm_count, tab)) {
+    const int grid = tab.job[tab.njobs - 1].cta_begin + tab.job[tab.njobs - 1].ncta;
+    single = (size_t)grid * 4 * kBlk * kBlk * sizeof(float);
+  }
+  const size_t pair = (d > kBlk && d % 32 == 0) ? gram_pair_workspace_bytes(c, d) : 0;
+  return single > pair ? single : pair;
 }
 
 void launch_gram_tc(Ctx& c, const float* dX, long long n, int d, const float* dshift, double* dG, double* dsum,
                     double* dsumsq, void* workspace) {
+  if (use_pair(c, dX, n, d)) {
+    launch_gram_pair(c, dX, n, d, dshift, dG, dsum, dsumsq, workspace);
+    c.last_gram_kernel = 2;
+    return;
+  }
+  c.last_gram_kernel = 1;
   TcJobTable tab;
   if (!build_jobs(d, c.sm_count, tab)) fail("gram_tc: d=%d needs more than %d jobs", d, kMaxJobs);
   CUtensorMap tmap;
@@ -433,9 +471,22 @@ void launch_gram_tc(Ctx& c, const float* dX, long long n, int d, const float* ds
   const int flush_rows = c.flush_rows > 0 ? c.flush_rows : 1024;
   const int grid = tab.job[tab.njobs - 1].cta_begin + tab.job[tab.njobs - 1].ncta;
   float* slab = static_cast<float*>(workspace);
-  gram_tc_kernel<<<grid, kThreads, smem, c.stream>>>(tmap, tab, n, d, dshift, slab, dsum, dsumsq, flush_rows);
+  static const bool trace = getenv("DR4G_GRAM_TRACE") != nullptr;
+  gram_tc_kernel<<<grid, kThreads, smem, c.stream>>>(tmap, tab, n, d, dshift, slab, dsum, dsumsq, flush_rows, trace ? 1 : 0);
   c.launches++;
   DR4G_CUDA(cudaGetLastError());
+  if (trace) {
+    static long long h[kTraceIts * 8];
+    DR4G_CUDA(cudaStreamSynchronize(c.stream));
+    DR4G_CUDA(cudaMemcpyFromSymbol(h, g_trace, sizeof(h)));
+    fprintf(stderr, "gram_tc trace (CTA 0, clocks relative to chunk 0 'stage free'; n=%lld d=%d)\n", n, d);
+    fprintf(stderr, "  it  tma_free tma_issued  landed converted  arrived  mma_ready mma_issued\n");
+    for (int it = 0; it < kTraceIts; ++it) {
+      fprintf(stderr, "%4d", it);
+      for (int e = 0; e < 7; ++e) fprintf(stderr, " %9lld", h[it * 8 + e] ? h[it * 8 + e] - h[0] : -1ll);
+      fprintf(stderr, "\n");
+    }
+  }
   int tiles = 0;
   for (int i = 0; i < tab.njobs; ++i) tiles += tab.job[i].ntile;
   reduce_slabs_kernel<<<dim3(tiles, kBlk), kBlk, 0, c.stream>>>(tab, slab, n, d, dG);

@@ -1,0 +1,523 @@
+// K2 (d > 128) - streamed Gram + column statistics on CTA PAIRS: tcgen05.mma cta_group::2, M = 256.
+//
+//   G = (X - 1 c^T)^T (X - 1 c^T),   s = sum_r (x_r - c),   q = sum_r (x_r - c)^2       (fp32 X, 3xTF32)
+//
+// Same contract as gram_tc.cu (which keeps d <= 128 and shapes whose d is not a multiple of 32);
+// replaces the reference's cublasSgemm Gram (src/tsvd.cu:324,358 via src/matrix.cu:95-127) and the
+// centring / variance sweeps around it (src/pca.cu:37-49, src/tsvd.cu:274-290).
+//
+// Why pairs.  Measured on B200 (tools/mma_probe.cu, profiles/r01_mma_probe_tf32_rates.txt): a
+// kind::tf32 MMA runs at its floor (N/2 cycles for M = 128 per CTA) from any operand placement, and
+// the tensor core has priority on shared memory; what is left for the converter warps (which split
+// every fp32 element into two tf32 numbers: 4 B TMA write + 4 B read + 8 B written per element) is
+// ~34 B/clk beside 128x128 MMAs, ~54 B/clk beside 128x256 and ~70 B/clk beside a 256x256 pair MMA,
+// because each CTA of a pair only supplies half of B.  In a pair every converted element feeds
+// 256 (A) or 256 (B) output rows/columns, so conversion stays under the MMA time for every d.
+//
+// Work decomposition.  Columns are cut into blocks of 128 (T blocks) and super-blocks of 256.  A
+// JOB is (row super-block I) x (one or two N-chunks of 256 columns at or right of the diagonal):
+// CTA rank r of the pair owns A block 2I + r (its 128 accumulator lanes) and, for every chunk,
+// B block cb + r (its half of the 256 columns).  The block upper triangle by 256 is covered, so
+// 2nd^2 * (S(S+1)/2) / S^2 flops are issued (S = ceil(d/256)) - 3/4 of the full product at d = 512.
+// A job's clusters split the rows (stage chunks it * ncl + split); partial accumulators go to per-CTA
+// fp32 slabs that reduce_pair_slabs_kernel sums in fp64 in a fixed order (deterministic).
+//
+// Shared-memory stage: 16-row x 128-column SLOTS of 8 KB, each written by ONE 3-D TMA box
+// (32 columns, 16 rows, 4 column groups) in the layout the MN-major tf32 descriptor needs
+// ([group][row][128 B], 32-byte chunks XOR row % 4 = SWIZZLE_128B_ATOM_32B; LBO = 2 KB between
+// groups, SBO = 512 B between 4-row atoms).  The first version issued 2 KB 2-D boxes and its
+// producer needed ~4100 cycles per 32-row stage (the whole pipeline ran at the TMA issue rate, see
+// the trace hook below); a stage is now 2-4 instructions.
+//
+// Warp roles (448 threads): 0-7 converters (+ column statistics), 8 TMA producer, 9 TMEM
+// allocation + MMA issue (leader CTA only), 10-13 epilogue (TMEM lane quadrant = warp % 4).
+// The fp32 accumulation of the tensor core truncates (about 1e-8 relative per accumulated row), so
+// the accumulators are flushed every `flush_rows` rows: the first window is stored, later ones are
+// RED-added (round to nearest, in L2) into the CTA's slab.  Jobs with one chunk use both halves
+// of TMEM alternately, so their flush overlaps the next window's MMAs; window boundaries are
+// staggered over the clusters so that the chip's flushes do not hit L2 at the same time.
+#include <cstdio>
+#include <cstdlib>
+#include <mutex>
+
+#include "common.cuh"
+#include "ptx_sm100.cuh"
+
+namespace dr4g {
+namespace {
+
+constexpr int kBlk = 128;
+constexpr int kSlotBytes = 8192;         // 16 rows x 128 columns x 4 B
+constexpr int kSlotRows = 16;
+constexpr int kRingBytes = 196608;       // stage ring (hi + lo halves)
+constexpr int kMaxStages = 4;
+constexpr int kConvWarps = 8;
+constexpr int kConvThreads = kConvWarps * 32;
+constexpr int kEpiWarps = 4;
+constexpr int kThreads = kConvThreads + 64 + kEpiWarps * 32;
+constexpr int kMaxPJobs = 40;
+constexpr uint32_t kTmemCols = 512;
+constexpr int kSlabFloats = 2 * kBlk * 256;  // per CTA: [chunk][lane][256 columns]
+
+struct PJob {
+  int I;            // row super-block: A block of rank r is 2 I + r
+  int nchunk;       // N-chunks of 256 columns (1 or 2)
+  int cb[2];        // first column block of each chunk (rank r supplies block cb + r)
+  int nlb;          // column blocks each CTA loads per 16 rows (1..3); local block 0 is the A block
+  int bb[3];        // first global block of local block lb (rank r loads bb + r)
+  int lb_of[2];     // local block holding a chunk's B half
+  int stats;        // 1: this job owns the column statistics of its A blocks
+  int cl_begin;     // first cluster of this job
+  int ncl;          // clusters (row splits)
+};
+
+struct PJobTable {
+  int njobs;
+  PJob job[kMaxPJobs];
+};
+
+constexpr int kTraceIts = 96;
+__device__ long long g_trace2[kTraceIts * 8];
+#define DR4G_TRACE2(ev) \
+  do { if (trace && blockIdx.x == 0 && it < kTraceIts) g_trace2[it * 8 + (ev)] = clock64(); } while (0)
+
+__device__ __forceinline__ float clear13(float v) { return __uint_as_float(__float_as_uint(v) & 0xffffe000u); }
+
+__global__ void __launch_bounds__(kThreads, 1)
+gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ PJobTable table, long long n, int d,
+                 const float* __restrict__ shift, float* __restrict__ slab, double* __restrict__ osum,
+                 double* __restrict__ osq, int flush_rows, int trace) {
+  // ---------------------------------------------------------------- which job / which chunks
+  const uint32_t rank = ptx::cluster_ctarank();
+  const int cluster = (int)blockIdx.x >> 1;
+  int ji = 0;
+  while (ji + 1 < table.njobs && cluster >= table.job[ji + 1].cl_begin) ++ji;
+  const PJob& job = table.job[ji];
+  const int split = cluster - job.cl_begin;
+  const int nlb = job.nlb, nchunk = job.nchunk;
+  const int cps = nlb == 1 ? 4 : (nlb == 2 ? 2 : 1);   // 16-row slots per local block per stage
+  const int kt = kSlotRows * cps;                        // rows per stage
+  const int slots = cps * nlb;
+  const uint32_t half_bytes = (uint32_t)slots * kSlotBytes;   // hi half, then lo half
+  const uint32_t stage_bytes = 2u * half_bytes;
+  const int nstages = (int)(kRingBytes / stage_bytes) < kMaxStages ? (int)(kRingBytes / stage_bytes) : kMaxStages;
+  const long long n_chunks = (n + kt - 1) / kt;
+  if (split >= job.ncl || split >= n_chunks) return;    // both CTAs of a pair take the same branch
+  const int my_chunks = (int)((n_chunks - split + job.ncl - 1) / job.ncl);
+  const int fc = flush_rows > kt ? flush_rows / kt : 1;          // stages per flush window
+  const int stagger = (split & 3) * (fc >> 2);                    // window phase of this cluster
+  const int nacc = nchunk == 1 ? 2 : 1;                           // accumulator sets in TMEM
+  const int T = (d + kBlk - 1) / kBlk;
+
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
+  __shared__ __align__(8) uint64_t bar_full[kMaxStages], bar_conv[kMaxStages], bar_empty[kMaxStages];
+  __shared__ __align__(8) uint64_t bar_acc_full[2], bar_acc_empty[2];
+  __shared__ uint32_t tmem_base_slot;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kMaxStages; ++s) {
+      ptx::mbar_init(ptx::smem_u32(&bar_full[s]), 1);
+      ptx::mbar_init(ptx::smem_u32(&bar_conv[s]), 2 * kConvWarps);   // used in the leader CTA only
+      ptx::mbar_init(ptx::smem_u32(&bar_empty[s]), 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      ptx::mbar_init(ptx::smem_u32(&bar_acc_full[a]), 1);
+      ptx::mbar_init(ptx::smem_u32(&bar_acc_empty[a]), 2 * kEpiWarps);  // leader CTA only
+    }
+    ptx::fence_barrier_init();
+  }
+  if (warp == kConvWarps + 1) {
+    ptx::tmem_alloc_pair(ptx::smem_u32(&tmem_base_slot), kTmemCols);
+    ptx::tmem_relinquish_pair();
+  }
+  ptx::tc_fence_before_sync();
+  __syncthreads();
+  ptx::cluster_sync();   // the peer's barriers exist before anything arrives on them
+  ptx::tc_fence_after_sync();
+  const uint32_t tmem_base = tmem_base_slot;
+
+  if (warp == kConvWarps) {
+    // ================================================================ TMA producer (each CTA its own blocks)
+    if (ptx::elect_one()) {
+      ptx::prefetch_tmap(&tmap);
+      int s = 0;
+      uint32_t ph = 0;
+      for (int it = 0; it < my_chunks; ++it) {
+        ptx::mbar_wait(ptx::smem_u32(&bar_empty[s]), ph ^ 1u);
+        DR4G_TRACE2(0);
+        const long long row0 = ((long long)split + (long long)it * job.ncl) * kt;
+        int boxes = 0;
+        for (int c = 0; c < cps; ++c)
+          if (row0 + c * kSlotRows < n)
+            for (int lb = 0; lb < nlb; ++lb)
+              if (job.bb[lb] + (int)rank < T) ++boxes;
+        const uint32_t full = ptx::smem_u32(&bar_full[s]);
+        ptx::mbar_arrive_expect_tx(full, (uint32_t)boxes * kSlotBytes);
+        const uint32_t sx = smem_base + (uint32_t)s * stage_bytes;
+        for (int c = 0; c < cps; ++c) {
+          const long long row = row0 + c * kSlotRows;
+          if (row >= n) continue;
+          for (int lb = 0; lb < nlb; ++lb) {
+            const int blk = job.bb[lb] + (int)rank;
+            if (blk >= T) continue;
+            ptx::tma_load_3d(sx + (uint32_t)(c * nlb + lb) * kSlotBytes, &tmap, full, 0, (int)row, blk * 4);
+          }
+        }
+        DR4G_TRACE2(1);
+        if (++s == nstages) { s = 0; ph ^= 1u; }
+      }
+    }
+  } else if (warp == kConvWarps + 1) {
+    // ================================================================ MMA issuer (leader CTA, one lane)
+    if (rank == 0 && ptx::elect_one()) {
+      constexpr uint32_t idesc = ptx::make_idesc_tf32(256, 256, true, true);
+      int s = 0, window = 0;
+      uint32_t ph = 0;
+      for (int it = 0; it < my_chunks; ++it) {
+        const bool window_start = it == 0 || (it + stagger) % fc == 0;
+        const int set = window % nacc;
+        if (window_start && window >= nacc) {
+          // the epilogue warps of both CTAs have drained this accumulator set
+          ptx::mbar_wait_cluster(ptx::smem_u32(&bar_acc_empty[set]), (uint32_t)(window / nacc - 1) & 1u);
+          ptx::tc_fence_after_sync();
+        }
+        ptx::mbar_wait_cluster(ptx::smem_u32(&bar_conv[s]), ph);
+        ptx::tc_fence_after_sync();
+        DR4G_TRACE2(5);
+        const uint32_t sx = smem_base + (uint32_t)s * stage_bytes;
+        for (int ks = 0; ks < kt / 8; ++ks) {
+          const uint32_t acc = (window_start && ks == 0) ? 0u : 1u;
+          const uint32_t row_off = (uint32_t)((ks >> 1) * nlb) * kSlotBytes + (uint32_t)(ks & 1) * 1024u;
+          const uint64_t a_hi = ptx::make_smem_desc(sx + row_off, 2048, 512, ptx::kLayoutSw128Base32);
+          const uint64_t a_lo = ptx::make_smem_desc(sx + half_bytes + row_off, 2048, 512, ptx::kLayoutSw128Base32);
+          for (int j = 0; j < nchunk; ++j) {
+            const uint32_t b_off = row_off + (uint32_t)job.lb_of[j] * kSlotBytes;
+            const uint64_t b_hi = ptx::make_smem_desc(sx + b_off, 2048, 512, ptx::kLayoutSw128Base32);
+            const uint64_t b_lo = ptx::make_smem_desc(sx + half_bytes + b_off, 2048, 512, ptx::kLayoutSw128Base32);
+            const uint32_t dcol = tmem_base + (uint32_t)(set + j) * 256u;
+            ptx::mma_tf32_ss_pair(dcol, a_hi, b_hi, idesc, acc);
+            ptx::mma_tf32_ss_pair(dcol, a_hi, b_lo, idesc, 1u);
+            ptx::mma_tf32_ss_pair(dcol, a_lo, b_hi, idesc, 1u);
+          }
+        }
+        ptx::mma_commit_pair(ptx::smem_u32(&bar_empty[s]), 3);   // stage free in both CTAs
+        DR4G_TRACE2(6);
+        const bool window_end = (it + stagger + 1) % fc == 0 || it == my_chunks - 1;
+        if (window_end) {
+          ptx::mma_commit_pair(ptx::smem_u32(&bar_acc_full[set]), 3);
+          ++window;
+        }
+        if (++s == nstages) { s = 0; ph ^= 1u; }
+      }
+    }
+  } else if (warp < kConvWarps) {
+    // ================================================================ converters (+ column statistics)
+    // thread -> fixed position inside a slot: 4 columns (group g, 16-byte chunk lc) and rows rg, rg + 8
+    const int tid = threadIdx.x;
+    const int lc = tid & 7, g = (tid >> 3) & 3, rg = tid >> 5;
+    const uint32_t conv_leader = ptx::mapa(ptx::smem_u32(&bar_conv[0]), 0);
+    float4 sh[3];
+    bool col_ok[3];
+    int col0[3];
+#pragma unroll
+    for (int lb = 0; lb < 3; ++lb) {
+      sh[lb] = make_float4(0.f, 0.f, 0.f, 0.f);
+      col0[lb] = lb < nlb ? (job.bb[lb] + (int)rank) * kBlk + g * 32 + lc * 4 : d;
+      col_ok[lb] = col0[lb] < d;
+      if (col_ok[lb] && shift) sh[lb] = *reinterpret_cast<const float4*>(shift + col0[lb]);
+    }
+    const bool stat_owner = job.stats && col_ok[0] && osum != nullptr;
+    double ds[4] = {0, 0, 0, 0}, dq[4] = {0, 0, 0, 0};
+    // 32-byte chunks XOR (row % 4): the BASE32B swizzle, as TMA (SWIZZLE_128B_ATOM_32B) laid it out
+    uint32_t toff[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int r = rg + 8 * h;
+      toff[h] = (uint32_t)g * 2048u + (uint32_t)r * 128u + (uint32_t)(((((lc >> 1) ^ (r & 3)) << 1) | (lc & 1)) << 4);
+    }
+    int s = 0;
+    uint32_t ph = 0;
+    for (int it = 0; it < my_chunks; ++it) {
+      ptx::mbar_wait(ptx::smem_u32(&bar_full[s]), ph);
+      if (tid == 0) DR4G_TRACE2(2);
+      const long long row0 = ((long long)split + (long long)it * job.ncl) * kt;
+      const uint32_t sx = smem_base + (uint32_t)s * stage_bytes;
+      float fs[4] = {0.f, 0.f, 0.f, 0.f}, fq[4] = {0.f, 0.f, 0.f, 0.f};
+      for (int c = 0; c < cps; ++c) {
+#pragma unroll
+        for (int lb = 0; lb < 3; ++lb) {
+          if (lb >= nlb) break;
+          const uint32_t slot = sx + (uint32_t)(c * nlb + lb) * kSlotBytes;
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const uint32_t a = slot + toff[h];
+            float4 hi = make_float4(0.f, 0.f, 0.f, 0.f), lo = hi;
+            if (col_ok[lb] && row0 + c * kSlotRows + rg + 8 * h < n) {
+              float4 x;
+              asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(x.x), "=f"(x.y), "=f"(x.z), "=f"(x.w) : "r"(a));
+              const float y0 = x.x - sh[lb].x, y1 = x.y - sh[lb].y, y2 = x.z - sh[lb].z, y3 = x.w - sh[lb].w;
+              if (lb == 0) {
+                fs[0] += y0; fs[1] += y1; fs[2] += y2; fs[3] += y3;
+                fq[0] = fmaf(y0, y0, fq[0]); fq[1] = fmaf(y1, y1, fq[1]);
+                fq[2] = fmaf(y2, y2, fq[2]); fq[3] = fmaf(y3, y3, fq[3]);
+              }
+              hi.x = clear13(y0); hi.y = clear13(y1); hi.z = clear13(y2); hi.w = clear13(y3);
+              lo.x = clear13(y0 - hi.x); lo.y = clear13(y1 - hi.y); lo.z = clear13(y2 - hi.z); lo.w = clear13(y3 - hi.w);
+            }
+            asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(a), "f"(hi.x), "f"(hi.y), "f"(hi.z), "f"(hi.w) : "memory");
+            asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(a + half_bytes), "f"(lo.x), "f"(lo.y), "f"(lo.z), "f"(lo.w) : "memory");
+          }
+        }
+      }
+      if (stat_owner) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { ds[j] += (double)fs[j]; dq[j] += (double)fq[j]; }
+      }
+      if (tid == 0) DR4G_TRACE2(3);
+      // the MMA that reads this stage is issued by the leader CTA: make the writes visible to the
+      // async proxy, then arrive (release at cluster scope) on the leader's barrier
+      ptx::fence_proxy_async_all();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive_cluster(conv_leader + (uint32_t)s * 8u);
+      if (tid == 0) DR4G_TRACE2(4);
+      if (++s == nstages) { s = 0; ph ^= 1u; }
+    }
+    if (stat_owner) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        atomicAdd(&osum[col0[0] + j], ds[j]);
+        atomicAdd(&osq[col0[0] + j], dq[j]);
+      }
+    }
+  } else {
+    // ================================================================ epilogue: TMEM -> this CTA's slab
+    // slab [chunk][accumulator lane m (128)][256 columns] fp32, L2 resident.  First window: store;
+    // later windows: vector RED (fire-and-forget, round-to-nearest adds in L2).
+    const int quadrant = warp & 3;
+    float* my_slab = slab + (size_t)blockIdx.x * kSlabFloats;
+    const uint32_t acc_empty_leader = ptx::mapa(ptx::smem_u32(&bar_acc_empty[0]), 0);
+    int window = 0;
+    for (int it = 0; it < my_chunks; ++it) {
+      const bool window_end = (it + stagger + 1) % fc == 0 || it == my_chunks - 1;
+      if (!window_end) continue;
+      const int set = window % nacc;
+      ptx::mbar_wait(ptx::smem_u32(&bar_acc_full[set]), (uint32_t)(window / nacc) & 1u);
+      ptx::tc_fence_after_sync();
+      for (int j = 0; j < nchunk; ++j) {
+        float* dst_row = my_slab + ((size_t)j * kBlk + quadrant * 32 + lane) * 256;
+        const uint32_t tbase = tmem_base + ((uint32_t)(quadrant * 32) << 16) + (uint32_t)(set + j) * 256u;
+#pragma unroll 1
+        for (int part = 0; part < 4; ++part) {
+          uint32_t v[32], w[32];
+          ptx::tmem_ld_32x32(tbase + (uint32_t)(part * 64), v);
+          ptx::tmem_ld_32x32(tbase + (uint32_t)(part * 64 + 32), w);
+          ptx::tmem_ld_wait();
+          float* dst = dst_row + part * 64;
+          if (window == 0) {
+#pragma unroll
+            for (int q = 0; q < 32; q += 4) {
+              asm volatile("st.global.v4.b32 [%0], {%1,%2,%3,%4};" ::"l"(dst + q), "r"(v[q]), "r"(v[q + 1]), "r"(v[q + 2]), "r"(v[q + 3]) : "memory");
+              asm volatile("st.global.v4.b32 [%0], {%1,%2,%3,%4};" ::"l"(dst + 32 + q), "r"(w[q]), "r"(w[q + 1]), "r"(w[q + 2]), "r"(w[q + 3]) : "memory");
+            }
+          } else {
+#pragma unroll
+            for (int q = 0; q < 32; q += 4) {
+              asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(dst + q), "f"(__uint_as_float(v[q])),
+                           "f"(__uint_as_float(v[q + 1])), "f"(__uint_as_float(v[q + 2])), "f"(__uint_as_float(v[q + 3])) : "memory");
+              asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(dst + 32 + q), "f"(__uint_as_float(w[q])),
+                           "f"(__uint_as_float(w[q + 1])), "f"(__uint_as_float(w[q + 2])), "f"(__uint_as_float(w[q + 3])) : "memory");
+            }
+          }
+        }
+      }
+      ptx::tc_fence_before_sync();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive_cluster(acc_empty_leader + (uint32_t)set * 8u);
+      ++window;
+    }
+  }
+
+  ptx::tc_fence_before_sync();
+  __syncthreads();
+  ptx::cluster_sync();   // no CTA of the pair leaves while the other may still signal it or read its smem
+  if (warp == kConvWarps + 1) ptx::tmem_dealloc_pair(tmem_base, kTmemCols);
+}
+
+// G (fp64, full symmetric) <- sum over a job's clusters of the slabs of CTA rank r, in a fixed
+// order (deterministic).  grid = (njobs * 4 [rank, chunk], 128 lanes m), block = 256 (column nn).
+__global__ void __launch_bounds__(256)
+reduce_pair_slabs_kernel(const __grid_constant__ PJobTable table, const float* __restrict__ slab, long long n, int d,
+                         double* __restrict__ G) {
+  const int ji = (int)blockIdx.x >> 2, r = ((int)blockIdx.x >> 1) & 1, j = (int)blockIdx.x & 1;
+  const PJob& job = table.job[ji];
+  if (j >= job.nchunk) return;
+  const int cps = job.nlb == 1 ? 4 : (job.nlb == 2 ? 2 : 1);
+  const long long n_chunks = (n + kSlotRows * cps - 1) / (kSlotRows * cps);
+  const int active = (int)(n_chunks < job.ncl ? n_chunks : job.ncl);
+  const int m = (int)blockIdx.y, nn = (int)threadIdx.x;
+  const int ga = (2 * job.I + r) * kBlk + m, gb = job.cb[j] * kBlk + nn;
+  if (ga >= d || gb >= d) return;
+  // the diagonal chunk holds both (a, b) and (b, a), accumulated in different orders: keep the
+  // upper one so that G is exactly symmetric
+  if (gb < ga) return;
+  const float* p = slab + ((size_t)(job.cl_begin * 2 + r)) * kSlabFloats + ((size_t)j * kBlk + m) * 256 + nn;
+  double acc = 0.0;
+  for (int c = 0; c < active; ++c) acc += (double)p[(size_t)c * 2 * kSlabFloats];
+  G[(size_t)ga * d + gb] = acc;
+  G[(size_t)gb * d + ga] = acc;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------- host side
+namespace {
+
+bool build_pair_jobs(int d, int sm_count, PJobTable& tab) {
+  const int T = (d + kBlk - 1) / kBlk;
+  const int S = (T + 1) / 2;
+  const int clusters = sm_count / 2;
+  tab.njobs = 0;
+  int total_cost = 0;
+  for (int I = 0; I < S; ++I)
+    for (int c0 = 2 * I; c0 < T; c0 += 4) {
+      if (tab.njobs == kMaxPJobs) return false;
+      PJob j{};
+      j.I = I;
+      j.nlb = 1;
+      j.bb[0] = 2 * I;
+      for (int cb = c0; cb < T && cb < c0 + 4; cb += 2) {
+        j.cb[j.nchunk] = cb;
+        if (cb == 2 * I) {
+          j.lb_of[j.nchunk] = 0;
+          j.stats = 1;
+        } else {
+          j.bb[j.nlb] = cb;
+          j.lb_of[j.nchunk] = j.nlb++;
+        }
+        ++j.nchunk;
+      }
+      tab.job[tab.njobs++] = j;
+      total_cost += j.nchunk;
+    }
+  if (tab.njobs > clusters) return false;
+  int given = 0;
+  for (int i = 0; i < tab.njobs; ++i) {
+    int m = (int)((long long)clusters * tab.job[i].nchunk / total_cost);
+    if (m < 1) m = 1;
+    tab.job[i].ncl = m;
+    given += m;
+  }
+  // hand the remaining clusters to the jobs with the most work per cluster
+  while (given < clusters) {
+    int best = 0;
+    double worst = -1.0;
+    for (int i = 0; i < tab.njobs; ++i) {
+      const double load = (double)tab.job[i].nchunk / tab.job[i].ncl;
+      if (load > worst) { worst = load; best = i; }
+    }
+    tab.job[best].ncl++;
+    given++;
+  }
+  while (given > clusters) {  // only when njobs is close to the cluster count
+    int best = -1;
+    double least = 1e30;
+    for (int i = 0; i < tab.njobs; ++i) {
+      if (tab.job[i].ncl <= 1) continue;
+      const double load = (double)tab.job[i].nchunk / (tab.job[i].ncl - 1);
+      if (load < least) { least = load; best = i; }
+    }
+    if (best < 0) return false;
+    tab.job[best].ncl--;
+    given--;
+  }
+  int begin = 0;
+  for (int i = 0; i < tab.njobs; ++i) {
+    tab.job[i].cl_begin = begin;
+    begin += tab.job[i].ncl;
+  }
+  return true;
+}
+
+using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+}  // namespace
+
+bool gram_pair_eligible(const Ctx& c, const float* dX, long long n, int d) {
+  if (n < 1 || d <= kBlk || (d % 32) != 0) return false;           // 3-D map: whole 32-column groups
+  if ((reinterpret_cast<uintptr_t>(dX) & 15) != 0) return false;    // TMA: 16-byte base
+  if (n >= (1ll << 31)) return false;                               // TMA coordinates are int32
+  if (c.sm_count < 2) return false;
+  PJobTable tab;
+  return build_pair_jobs(d, c.sm_count, tab);
+}
+
+size_t gram_pair_workspace_bytes(const Ctx& c, int d) {
+  return (size_t)(c.sm_count / 2) * 2 * kSlabFloats * sizeof(float);
+}
+
+void launch_gram_pair(Ctx& c, const float* dX, long long n, int d, const float* dshift, double* dG, double* dsum,
+                      double* dsumsq, void* workspace) {
+  PJobTable tab;
+  if (!build_pair_jobs(d, c.sm_count, tab)) fail("gram_pair: d=%d does not fit the job table", d);
+  // X as a 3-D tensor: (column within a 32-column group, row, column group); one box = 32 x 16 x 4
+  CUtensorMap tmap;
+  const cuuint64_t gdim[3] = {32, (cuuint64_t)n, (cuuint64_t)(d / 32)};
+  const cuuint64_t gstride[2] = {(cuuint64_t)d * sizeof(float), 32 * sizeof(float)};
+  const cuuint32_t box[3] = {32, (cuuint32_t)kSlotRows, 4};
+  const cuuint32_t estride[3] = {1, 1, 1};
+  CUresult r = reinterpret_cast<EncodeTiledFn>(tensor_map_encoder(c))(
+      &tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(dX), gdim, gstride, box, estride,
+      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) fail("cuTensorMapEncodeTiled (3-D) failed (%d) for n=%lld d=%d", (int)r, n, d);
+
+  static std::once_flag once;
+  static cudaError_t attr_err = cudaSuccess;
+  const int smem = kRingBytes + 1024;
+  std::call_once(once, [&] {
+    attr_err = cudaFuncSetAttribute(gram_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  });
+  DR4G_CUDA(attr_err);
+
+  static const bool trace = getenv("DR4G_GRAM_TRACE") != nullptr;
+  const int flush_rows = c.flush_rows > 0 ? c.flush_rows : 1024;
+  const int clusters = tab.job[tab.njobs - 1].cl_begin + tab.job[tab.njobs - 1].ncl;
+  float* slab = static_cast<float*>(workspace);
+  cudaLaunchConfig_t lc = {};
+  lc.gridDim = dim3(2 * clusters, 1, 1);
+  lc.blockDim = dim3(kThreads, 1, 1);
+  lc.dynamicSmemBytes = smem;
+  lc.stream = c.stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = 2;
+  at[0].val.clusterDim.y = 1;
+  at[0].val.clusterDim.z = 1;
+  lc.attrs = at;
+  lc.numAttrs = 1;
+  DR4G_CUDA(cudaLaunchKernelEx(&lc, gram_pair_kernel, tmap, tab, n, d, dshift, slab, dsum, dsumsq, flush_rows,
+                               trace ? 1 : 0));
+  c.launches++;
+  if (trace) {
+    static long long h[kTraceIts * 8];
+    DR4G_CUDA(cudaStreamSynchronize(c.stream));
+    DR4G_CUDA(cudaMemcpyFromSymbol(h, g_trace2, sizeof(h)));
+    fprintf(stderr, "gram_pair trace (CTA 0, clocks relative to chunk 0 'stage free'; n=%lld d=%d)\n", n, d);
+    fprintf(stderr, "  it  tma_free tma_issued  landed converted  arrived  mma_ready mma_issued\n");
+    for (int it = 0; it < kTraceIts; ++it) {
+      fprintf(stderr, "%4d", it);
+      for (int e = 0; e < 7; ++e) fprintf(stderr, " %9lld", h[it * 8 + e] ? h[it * 8 + e] - h[0] : -1ll);
+      fprintf(stderr, "\n");
+    }
+  }
+  reduce_pair_slabs_kernel<<<dim3(tab.njobs * 4, kBlk), 256, 0, c.stream>>>(tab, slab, n, d, dG);
+  c.launches++;
+  DR4G_CUDA(cudaGetLastError());
+}
+
+}  // namespace dr4g

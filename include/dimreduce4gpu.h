@@ -83,7 +83,7 @@ DR4G_EXPORT void dr4g_ctx_destroy(dr4g_ctx* ctx);
 DR4G_EXPORT int dr4g_ctx_set_stream(dr4g_ctx* ctx, void* cuda_stream);
 /* Block until everything enqueued on the context's stream is done; returns deferred errors. */
 DR4G_EXPORT int dr4g_sync(dr4g_ctx* ctx);
-/* Tunables / test hooks.  Keys: "gram_path" (0 auto, 1 generic DMMA kernel, 2 tcgen05 kernel),
+/* Tunables / test hooks.  Keys: "gram_path" (0 auto, 1 generic DMMA kernel, 2 tcgen05 kernels, 3 tcgen05 single-CTA kernel only),
  * "flush_rows" (rows between TMEM accumulator flushes), "pilot_rows", "jacobi_tol", "jacobi_sweeps",
  * "eig_solver" (exact path: 0 tridiagonal route for the top k, 1 blocked Jacobi), "timing". */
 DR4G_EXPORT int dr4g_set_option(dr4g_ctx* ctx, const char* key, double value);
@@ -142,7 +142,7 @@ DR4G_EXPORT int dr4g_eigh_topk_double(dr4g_ctx* ctx, double* dA, int d, int k, d
  * [3] eigensolve (Jacobi or subspace iteration), [4] sort/flip/outputs, [5] total.
  * Returns the number of entries written (<= n). */
 DR4G_EXPORT int dr4g_stage_times(dr4g_ctx* ctx, double* ms, int n);
-/* Which Gram kernel the last fit used (1 generic DMMA, 2 tcgen05), and launches it issued. */
+/* Which Gram kernel the last fit used (1 generic DMMA, 2 tcgen05 single-CTA, 3 tcgen05 CTA pairs), and launches it issued. */
 DR4G_EXPORT int dr4g_last_gram_path(dr4g_ctx* ctx);
 DR4G_EXPORT long long dr4g_launch_count(dr4g_ctx* ctx);
 

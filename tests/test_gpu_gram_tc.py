@@ -54,7 +54,7 @@ def test_gram_tc_matches_fp64(n, d, shifted):
     shift = X[: min(n, 4096)].mean(0).contiguous() if shifted else None
     G = ctx.gram(X, shift)
     ctx.sync()
-    assert ctx.last_gram_path == "tcgen05"
+    assert ctx.last_gram_path.startswith("tcgen05")
     Xd = X.double() - (shift.double() if shifted else 0.0)
     assert _rel_err(G, Xd) < GRAM_TOL
     assert float((G - G.T).abs().max()) == 0.0  # mirrored, exactly symmetric
@@ -78,7 +78,7 @@ def test_fused_column_statistics(n, d):
     X = _make(n, d, 3, offset=7.0)
     res = ctx.fit(X, min(8, d), center=True)
     ctx.sync()
-    assert ctx.last_gram_path == "tcgen05"
+    assert ctx.last_gram_path.startswith("tcgen05")
     Xd = X.double()
     assert float((res["mean"].double() - Xd.mean(0)).abs().max()) < 2e-6
     tot = float(Xd.var(0, unbiased=True).sum())
