@@ -29,8 +29,8 @@
 // producer needed ~4100 cycles per 32-row stage (the whole pipeline ran at the TMA issue rate, see
 // the trace hook below); a stage is now 2-4 instructions.
 //
-// Warp roles (448 threads): 0-7 converters (+ column statistics), 8 TMA producer, 9 TMEM
-// allocation + MMA issue (leader CTA only), 10-13 epilogue (TMEM lane quadrant = warp % 4).
+// Warp roles (512 threads): 0-7 converters (+ column statistics), 8-10 TMA producers, 11 TMEM
+// allocation + MMA issue (leader CTA only), 12-15 epilogue (TMEM lane quadrant = warp % 4).
 // The fp32 accumulation of the tensor core truncates (about 1e-8 relative per accumulated row), so
 // the accumulators are flushed every `flush_rows` rows: the first window is stored, later ones are
 // RED-added (round to nearest, in L2) into the CTA's slab.  Jobs with one chunk use both halves
@@ -39,6 +39,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <mutex>
+#include <type_traits>
 
 #include "common.cuh"
 #include "ptx_sm100.cuh"
@@ -50,11 +51,13 @@ constexpr int kBlk = 128;
 constexpr int kSlotBytes = 8192;         // 16 rows x 128 columns x 4 B
 constexpr int kSlotRows = 16;
 constexpr int kRingBytes = 196608;       // stage ring (hi + lo halves)
-constexpr int kMaxStages = 4;
+constexpr int kMaxStages = 6;
 constexpr int kConvWarps = 8;
 constexpr int kConvThreads = kConvWarps * 32;
 constexpr int kEpiWarps = 4;
-constexpr int kThreads = kConvThreads + 64 + kEpiWarps * 32;
+constexpr int kProducers = 3;            // TMA-issuing warps: one box costs its issuer ~700 cycles whatever its size
+constexpr int kMmaWarp = kConvWarps + kProducers;
+constexpr int kThreads = kConvThreads + (kProducers + 1 + kEpiWarps) * 32;
 constexpr int kMaxPJobs = 40;
 constexpr uint32_t kTmemCols = 512;
 constexpr int kSlabFloats = 2 * kBlk * 256;  // per CTA: [chunk][lane][256 columns]
@@ -79,7 +82,7 @@ struct PJobTable {
 constexpr int kTraceIts = 96;
 __device__ long long g_trace2[kTraceIts * 8];
 #define DR4G_TRACE2(ev) \
-  do { if (trace && blockIdx.x == 0 && it < kTraceIts) g_trace2[it * 8 + (ev)] = clock64(); } while (0)
+  do { if ((trace & 1) && (int)blockIdx.x == (trace >> 8) && it < kTraceIts) g_trace2[it * 8 + (ev)] = clock64(); } while (0)
 
 __device__ __forceinline__ float clear13(float v) { return __uint_as_float(__float_as_uint(v) & 0xffffe000u); }
 
@@ -95,7 +98,10 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
   const PJob& job = table.job[ji];
   const int split = cluster - job.cl_begin;
   const int nlb = job.nlb, nchunk = job.nchunk;
-  const int cps = nlb == 1 ? 4 : (nlb == 2 ? 2 : 1);   // 16-row slots per local block per stage
+  // 16-row slots per local block per stage: stages are kept small (32-48 KB) and the ring deep (4-6),
+  // because a stage's way round the ring (TMA issue ~1000 clk + landing ~1100 + conversion + store
+  // drain ~1000-1800 + MMA) is several times its MMA time
+  const int cps = nlb == 1 ? 2 : 1;
   const int kt = kSlotRows * cps;                        // rows per stage
   const int slots = cps * nlb;
   const uint32_t half_bytes = (uint32_t)slots * kSlotBytes;   // hi half, then lo half
@@ -119,8 +125,8 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kMaxStages; ++s) {
-      ptx::mbar_init(ptx::smem_u32(&bar_full[s]), 1);
-      ptx::mbar_init(ptx::smem_u32(&bar_conv[s]), 2 * kConvWarps);   // used in the leader CTA only
+      ptx::mbar_init(ptx::smem_u32(&bar_full[s]), kProducers);
+      ptx::mbar_init(ptx::smem_u32(&bar_conv[s]), kConvWarps);       // a group of 4 warps per CTA; leader CTA only
       ptx::mbar_init(ptx::smem_u32(&bar_empty[s]), 1);
     }
     for (int a = 0; a < 2; ++a) {
@@ -129,7 +135,7 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
     }
     ptx::fence_barrier_init();
   }
-  if (warp == kConvWarps + 1) {
+  if (warp == kMmaWarp) {
     ptx::tmem_alloc_pair(ptx::smem_u32(&tmem_base_slot), kTmemCols);
     ptx::tmem_relinquish_pair();
   }
@@ -139,38 +145,43 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
   ptx::tc_fence_after_sync();
   const uint32_t tmem_base = tmem_base_slot;
 
-  if (warp == kConvWarps) {
-    // ================================================================ TMA producer (each CTA its own blocks)
+  if (warp >= kConvWarps && warp < kMmaWarp) {
+    // ================================================================ TMA producers (each CTA its own blocks)
+    // Measured (tools/tma_probe.cu): a thread issues one box per ~700 cycles whatever the box size, so
+    // one issuer with 8 KB boxes streams 3.1 TB/s chip-wide and four issuers 6.5 TB/s.  The boxes of
+    // the stages are dealt round-robin to the kProducers warps; every producer arrives on every
+    // stage's barrier with the bytes it issued (possibly none).
     if (ptx::elect_one()) {
+      const int p = warp - kConvWarps;
       ptx::prefetch_tmap(&tmap);
       int s = 0;
       uint32_t ph = 0;
       for (int it = 0; it < my_chunks; ++it) {
         ptx::mbar_wait(ptx::smem_u32(&bar_empty[s]), ph ^ 1u);
-        DR4G_TRACE2(0);
+        if (p == 0) DR4G_TRACE2(0);
         const long long row0 = ((long long)split + (long long)it * job.ncl) * kt;
-        int boxes = 0;
-        for (int c = 0; c < cps; ++c)
-          if (row0 + c * kSlotRows < n)
-            for (int lb = 0; lb < nlb; ++lb)
-              if (job.bb[lb] + (int)rank < T) ++boxes;
         const uint32_t full = ptx::smem_u32(&bar_full[s]);
-        ptx::mbar_arrive_expect_tx(full, (uint32_t)boxes * kSlotBytes);
         const uint32_t sx = smem_base + (uint32_t)s * stage_bytes;
-        for (int c = 0; c < cps; ++c) {
-          const long long row = row0 + c * kSlotRows;
-          if (row >= n) continue;
-          for (int lb = 0; lb < nlb; ++lb) {
-            const int blk = job.bb[lb] + (int)rank;
-            if (blk >= T) continue;
-            ptx::tma_load_3d(sx + (uint32_t)(c * nlb + lb) * kSlotBytes, &tmap, full, 0, (int)row, blk * 4);
-          }
+        int mine = 0;
+        for (int sl = 0; sl < slots; ++sl) {
+          if ((it * slots + sl) % kProducers != p) continue;
+          const int c = sl / nlb, lb = sl - c * nlb;
+          if (row0 + c * kSlotRows < n && job.bb[lb] + (int)rank < T) ++mine;
         }
-        DR4G_TRACE2(1);
+        ptx::mbar_arrive_expect_tx(full, (uint32_t)mine * kSlotBytes);
+        for (int sl = 0; sl < slots; ++sl) {
+          if ((it * slots + sl) % kProducers != p) continue;
+          const int c = sl / nlb, lb = sl - c * nlb;
+          const long long row = row0 + c * kSlotRows;
+          const int blk = job.bb[lb] + (int)rank;
+          if (row >= n || blk >= T) continue;
+          ptx::tma_load_3d(sx + (uint32_t)sl * kSlotBytes, &tmap, full, 0, (int)row, blk * 4);
+        }
+        if (p == 0) DR4G_TRACE2(1);
         if (++s == nstages) { s = 0; ph ^= 1u; }
       }
     }
-  } else if (warp == kConvWarps + 1) {
+  } else if (warp == kMmaWarp) {
     // ================================================================ MMA issuer (leader CTA, one lane)
     if (rank == 0 && ptx::elect_one()) {
       constexpr uint32_t idesc = ptx::make_idesc_tf32(256, 256, true, true);
@@ -188,7 +199,7 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
         ptx::tc_fence_after_sync();
         DR4G_TRACE2(5);
         const uint32_t sx = smem_base + (uint32_t)s * stage_bytes;
-        for (int ks = 0; ks < kt / 8; ++ks) {
+        for (int ks = 0; ks < ((trace & 2) ? 0 : kt / 8); ++ks) {
           const uint32_t acc = (window_start && ks == 0) ? 0u : 1u;
           const uint32_t row_off = (uint32_t)((ks >> 1) * nlb) * kSlotBytes + (uint32_t)(ks & 1) * 1024u;
           const uint64_t a_hi = ptx::make_smem_desc(sx + row_off, 2048, 512, ptx::kLayoutSw128Base32);
@@ -215,9 +226,13 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
     }
   } else if (warp < kConvWarps) {
     // ================================================================ converters (+ column statistics)
-    // thread -> fixed position inside a slot: 4 columns (group g, 16-byte chunk lc) and rows rg, rg + 8
+    // Two groups of 4 warps convert alternate stages, so that one group's store drain (the proxy
+    // fence waits for the stores queued behind the MMA's operand reads, ~1000-2000 cycles) overlaps the
+    // other group's loads.  thread -> fixed position inside a slot: 4 columns (group g, 16-byte chunk
+    // lc) and rows rg + 4 h, h = 0..3
     const int tid = threadIdx.x;
-    const int lc = tid & 7, g = (tid >> 3) & 3, rg = tid >> 5;
+    const int grp = warp >> 2;
+    const int lc = tid & 7, g = (tid >> 3) & 3, rg = warp & 3;
     const uint32_t conv_leader = ptx::mapa(ptx::smem_u32(&bar_conv[0]), 0);
     float4 sh[3];
     bool col_ok[3];
@@ -232,57 +247,88 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
     const bool stat_owner = job.stats && col_ok[0] && osum != nullptr;
     double ds[4] = {0, 0, 0, 0}, dq[4] = {0, 0, 0, 0};
     // 32-byte chunks XOR (row % 4): the BASE32B swizzle, as TMA (SWIZZLE_128B_ATOM_32B) laid it out
-    uint32_t toff[2];
+    uint32_t toff[4];
 #pragma unroll
-    for (int h = 0; h < 2; ++h) {
-      const int r = rg + 8 * h;
+    for (int h = 0; h < 4; ++h) {
+      const int r = rg + 4 * h;
       toff[h] = (uint32_t)g * 2048u + (uint32_t)r * 128u + (uint32_t)(((((lc >> 1) ^ (r & 3)) << 1) | (lc & 1)) << 4);
     }
-    int s = 0;
+    int s = 0, pending = 0;
     uint32_t ph = 0;
+    float fs[4] = {0.f, 0.f, 0.f, 0.f}, fq[4] = {0.f, 0.f, 0.f, 0.f};
     for (int it = 0; it < my_chunks; ++it) {
+      if ((it & 1) != grp) {
+        if (++s == nstages) { s = 0; ph ^= 1u; }
+        continue;
+      }
       ptx::mbar_wait(ptx::smem_u32(&bar_full[s]), ph);
-      if (tid == 0) DR4G_TRACE2(2);
+      if (lane == 0 && rg == 0) DR4G_TRACE2(2);
       const long long row0 = ((long long)split + (long long)it * job.ncl) * kt;
       const uint32_t sx = smem_base + (uint32_t)s * stage_bytes;
-      float fs[4] = {0.f, 0.f, 0.f, 0.f}, fq[4] = {0.f, 0.f, 0.f, 0.f};
-      for (int c = 0; c < cps; ++c) {
+      // one stage = CPS x NLB slots, four float4 per slot and thread; all loads are issued before
+      // the first store so that the shared-memory latency (long beside the MMA's operand reads)
+      // is paid once per stage, not once per slot
+      auto convert = [&](auto nlb_c) {
+        constexpr int NLB = decltype(nlb_c)::value;
+        constexpr int CPS = NLB == 1 ? 2 : 1;
+        float4 x[CPS * NLB * 4];
+        bool ok[CPS * NLB * 4];
 #pragma unroll
-        for (int lb = 0; lb < 3; ++lb) {
-          if (lb >= nlb) break;
-          const uint32_t slot = sx + (uint32_t)(c * nlb + lb) * kSlotBytes;
+        for (int c = 0; c < CPS; ++c)
 #pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            const uint32_t a = slot + toff[h];
-            float4 hi = make_float4(0.f, 0.f, 0.f, 0.f), lo = hi;
-            if (col_ok[lb] && row0 + c * kSlotRows + rg + 8 * h < n) {
-              float4 x;
-              asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(x.x), "=f"(x.y), "=f"(x.z), "=f"(x.w) : "r"(a));
-              const float y0 = x.x - sh[lb].x, y1 = x.y - sh[lb].y, y2 = x.z - sh[lb].z, y3 = x.w - sh[lb].w;
-              if (lb == 0) {
-                fs[0] += y0; fs[1] += y1; fs[2] += y2; fs[3] += y3;
-                fq[0] = fmaf(y0, y0, fq[0]); fq[1] = fmaf(y1, y1, fq[1]);
-                fq[2] = fmaf(y2, y2, fq[2]); fq[3] = fmaf(y3, y3, fq[3]);
-              }
-              hi.x = clear13(y0); hi.y = clear13(y1); hi.z = clear13(y2); hi.w = clear13(y3);
-              lo.x = clear13(y0 - hi.x); lo.y = clear13(y1 - hi.y); lo.z = clear13(y2 - hi.z); lo.w = clear13(y3 - hi.w);
+          for (int lb = 0; lb < NLB; ++lb)
+#pragma unroll
+            for (int h = 0; h < 4; ++h) {
+              const int i = (c * NLB + lb) * 4 + h;
+              const uint32_t a = sx + (uint32_t)(c * NLB + lb) * kSlotBytes + toff[h];
+              ok[i] = col_ok[lb] && row0 + c * kSlotRows + rg + 4 * h < n;
+              asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(x[i].x), "=f"(x[i].y), "=f"(x[i].z), "=f"(x[i].w) : "r"(a));
             }
-            asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(a), "f"(hi.x), "f"(hi.y), "f"(hi.z), "f"(hi.w) : "memory");
-            asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(a + half_bytes), "f"(lo.x), "f"(lo.y), "f"(lo.z), "f"(lo.w) : "memory");
-          }
-        }
-      }
-      if (stat_owner) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) { ds[j] += (double)fs[j]; dq[j] += (double)fq[j]; }
+        for (int c = 0; c < CPS; ++c)
+#pragma unroll
+          for (int lb = 0; lb < NLB; ++lb)
+#pragma unroll
+            for (int h = 0; h < 4; ++h) {
+              const int i = (c * NLB + lb) * 4 + h;
+              const uint32_t a = sx + (uint32_t)(c * NLB + lb) * kSlotBytes + toff[h];
+              float4 hi = make_float4(0.f, 0.f, 0.f, 0.f), lo = hi;
+              if (ok[i]) {
+                const float y0 = x[i].x - sh[lb].x, y1 = x[i].y - sh[lb].y, y2 = x[i].z - sh[lb].z, y3 = x[i].w - sh[lb].w;
+                if (lb == 0) {
+                  fs[0] += y0; fs[1] += y1; fs[2] += y2; fs[3] += y3;
+                  fq[0] = fmaf(y0, y0, fq[0]); fq[1] = fmaf(y1, y1, fq[1]);
+                  fq[2] = fmaf(y2, y2, fq[2]); fq[3] = fmaf(y3, y3, fq[3]);
+                }
+                hi.x = clear13(y0); hi.y = clear13(y1); hi.z = clear13(y2); hi.w = clear13(y3);
+                lo.x = clear13(y0 - hi.x); lo.y = clear13(y1 - hi.y); lo.z = clear13(y2 - hi.z); lo.w = clear13(y3 - hi.w);
+              }
+              asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(a), "f"(hi.x), "f"(hi.y), "f"(hi.z), "f"(hi.w) : "memory");
+              asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(a + half_bytes), "f"(lo.x), "f"(lo.y), "f"(lo.z), "f"(lo.w) : "memory");
+            }
+      };
+      if (trace & 4) {
+      } else if (nlb == 1) convert(std::integral_constant<int, 1>{});
+      else if (nlb == 2) convert(std::integral_constant<int, 2>{});
+      else convert(std::integral_constant<int, 3>{});
+      // fp32 partial sums of at most 16 stages x 8 rows, then fp64 (fp64 conversions and adds are slow
+      // enough on B200 to double the conversion time when done per stage: measured)
+      if (stat_owner && (++pending == 16 || it + 2 >= my_chunks)) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          ds[j] += (double)fs[j]; dq[j] += (double)fq[j];
+          fs[j] = 0.f; fq[j] = 0.f;
+        }
+        pending = 0;
       }
-      if (tid == 0) DR4G_TRACE2(3);
-      // the MMA that reads this stage is issued by the leader CTA: make the writes visible to the
-      // async proxy, then arrive (release at cluster scope) on the leader's barrier
-      ptx::fence_proxy_async_all();
+      if (lane == 0 && rg == 0) DR4G_TRACE2(3);
+      // the MMA that reads this stage is issued by the leader CTA but reads THIS CTA's shared memory:
+      // make the writes visible to the async proxy (the fence also waits for the stores queued behind
+      // the MMA's operand reads), then arrive (release at cluster scope) on the leader's barrier
+      ptx::fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive_cluster(conv_leader + (uint32_t)s * 8u);
-      if (tid == 0) DR4G_TRACE2(4);
+      if (lane == 0 && rg == 0) DR4G_TRACE2(4);
       if (++s == nstages) { s = 0; ph ^= 1u; }
     }
     if (stat_owner) {
@@ -300,6 +346,8 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
     float* my_slab = slab + (size_t)blockIdx.x * kSlabFloats;
     const uint32_t acc_empty_leader = ptx::mapa(ptx::smem_u32(&bar_acc_empty[0]), 0);
     int window = 0;
+    // a window of fc stages lasts about fc * kt / 8 * nchunk * 384 cycles; spend ~1/3 of it draining
+    const unsigned pace_ns = (unsigned)(fc * kt * nchunk * 48 / 3 / 4 / 2);  // cycles -> ~ns at 2 GHz, per part
     for (int it = 0; it < my_chunks; ++it) {
       const bool window_end = (it + stagger + 1) % fc == 0 || it == my_chunks - 1;
       if (!window_end) continue;
@@ -311,6 +359,9 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
         const uint32_t tbase = tmem_base + ((uint32_t)(quadrant * 32) << 16) + (uint32_t)(set + j) * 256u;
 #pragma unroll 1
         for (int part = 0; part < 4; ++part) {
+          // With two accumulator sets the drain has a whole window to finish: pace it, so that the
+          // burst of global stores / REDs does not back up the LSU queues the converters share.
+          if (nacc == 2 && part) __nanosleep(pace_ns);
           uint32_t v[32], w[32];
           ptx::tmem_ld_32x32(tbase + (uint32_t)(part * 64), v);
           ptx::tmem_ld_32x32(tbase + (uint32_t)(part * 64 + 32), w);
@@ -343,7 +394,7 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
   ptx::tc_fence_before_sync();
   __syncthreads();
   ptx::cluster_sync();   // no CTA of the pair leaves while the other may still signal it or read its smem
-  if (warp == kConvWarps + 1) ptx::tmem_dealloc_pair(tmem_base, kTmemCols);
+  if (warp == kMmaWarp) ptx::tmem_dealloc_pair(tmem_base, kTmemCols);
 }
 
 // G (fp64, full symmetric) <- sum over a job's clusters of the slabs of CTA rank r, in a fixed
@@ -354,7 +405,7 @@ reduce_pair_slabs_kernel(const __grid_constant__ PJobTable table, const float* _
   const int ji = (int)blockIdx.x >> 2, r = ((int)blockIdx.x >> 1) & 1, j = (int)blockIdx.x & 1;
   const PJob& job = table.job[ji];
   if (j >= job.nchunk) return;
-  const int cps = job.nlb == 1 ? 4 : (job.nlb == 2 ? 2 : 1);
+  const int cps = job.nlb == 1 ? 2 : 1;
   const long long n_chunks = (n + kSlotRows * cps - 1) / (kSlotRows * cps);
   const int active = (int)(n_chunks < job.ncl ? n_chunks : job.ncl);
   const int m = (int)blockIdx.y, nn = (int)threadIdx.x;
@@ -484,7 +535,7 @@ void launch_gram_pair(Ctx& c, const float* dX, long long n, int d, const float* 
   });
   DR4G_CUDA(attr_err);
 
-  static const bool trace = getenv("DR4G_GRAM_TRACE") != nullptr;
+  static const int trace = getenv("DR4G_GRAM_TRACE") ? atoi(getenv("DR4G_GRAM_TRACE")) : 0;  // bit 0 trace (CTA = value >> 8), 2 no MMA, 4 no conversion
   const int flush_rows = c.flush_rows > 0 ? c.flush_rows : 1024;
   const int clusters = tab.job[tab.njobs - 1].cl_begin + tab.job[tab.njobs - 1].ncl;
   float* slab = static_cast<float*>(workspace);
@@ -501,9 +552,9 @@ void launch_gram_pair(Ctx& c, const float* dX, long long n, int d, const float* 
   lc.attrs = at;
   lc.numAttrs = 1;
   DR4G_CUDA(cudaLaunchKernelEx(&lc, gram_pair_kernel, tmap, tab, n, d, dshift, slab, dsum, dsumsq, flush_rows,
-                               trace ? 1 : 0));
+                               trace));
   c.launches++;
-  if (trace) {
+  if (trace & 1) {
     static long long h[kTraceIts * 8];
     DR4G_CUDA(cudaStreamSynchronize(c.stream));
     DR4G_CUDA(cudaMemcpyFromSymbol(h, g_trace2, sizeof(h)));
