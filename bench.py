@@ -323,7 +323,14 @@ def main() -> None:
                 for J in range(I, S):
                     na, nb = min(2, T - 2 * I), min(2, T - 2 * J)
                     tiles += na * (na + 1) // 2 if I == J else na * nb
-            issued_factor = 3.0 * tiles / (T * T) if ctx.last_gram_path == "tcgen05" else 0.0
+            if ctx.last_gram_path == "tcgen05_pair":
+                # CTA-pair kernel: 256-wide super-blocks, upper block triangle by 256, three tf32
+                # products each (csrc/gram_tc2.cu): issued = 3 * S(S+1)/2 * 256^2 / d^2 of 2nd^2
+                issued_factor = 3.0 * (S * (S + 1) // 2) * 65536.0 / (d * d)
+            elif ctx.last_gram_path == "tcgen05":
+                issued_factor = 3.0 * tiles / (T * T)
+            else:
+                issued_factor = 0.0
             bytes_alg, flops_alg = n * d * 4.0, 2.0 * n * d * d
             t_hbm = bytes_alg / (peaks["hbm_gbs"] * 1e9)
             t_tensor = issued_factor * flops_alg / (tf32_peak * 1e12)
@@ -341,6 +348,7 @@ def main() -> None:
             roof.update(kernel=f"gram ({ctx.last_gram_path})", kernel_ms=gram_ms, peak_source=peaks["source"],
                         arithmetic_intensity_flop_per_byte=d / 2.0,
                         achieved_tflops_algorithmic=flops_alg / sec / 1e12,
+                        frac_of_3xtf32_effective_peak=flops_alg / sec / 1e12 / (tf32_peak / 3.0),
                         achieved_gbs_algorithmic=bytes_alg / sec / 1e9,
                         hbm_frac=bytes_alg / sec / 1e9 / peaks["hbm_gbs"])
         cpu = None

@@ -154,28 +154,39 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
     if (ptx::elect_one()) {
       const int p = warp - kConvWarps;
       ptx::prefetch_tmap(&tmap);
-      int s = 0;
+      int s = 0, pown = 0;   // pown: owner of the next stage's first box
       uint32_t ph = 0;
+      int blk_of[3];
+#pragma unroll
+      for (int lb = 0; lb < 3; ++lb) blk_of[lb] = lb < nlb ? job.bb[lb] + (int)rank : T;
       for (int it = 0; it < my_chunks; ++it) {
         ptx::mbar_wait(ptx::smem_u32(&bar_empty[s]), ph ^ 1u);
         if (p == 0) DR4G_TRACE2(0);
         const long long row0 = ((long long)split + (long long)it * job.ncl) * kt;
         const uint32_t full = ptx::smem_u32(&bar_full[s]);
         const uint32_t sx = smem_base + (uint32_t)s * stage_bytes;
+        // boxes of this stage dealt round-robin: box index q = it * slots + sl, owner q % kProducers
         int mine = 0;
-        for (int sl = 0; sl < slots; ++sl) {
-          if ((it * slots + sl) % kProducers != p) continue;
-          const int c = sl / nlb, lb = sl - c * nlb;
-          if (row0 + c * kSlotRows < n && job.bb[lb] + (int)rank < T) ++mine;
+        {
+          int own = pown;
+          for (int c = 0, sl = 0; c < cps; ++c)
+            for (int lb = 0; lb < nlb; ++lb, ++sl) {
+              if (own == p && row0 + c * kSlotRows < n && blk_of[lb] < T) ++mine;
+              if (++own == kProducers) own = 0;
+            }
         }
         ptx::mbar_arrive_expect_tx(full, (uint32_t)mine * kSlotBytes);
-        for (int sl = 0; sl < slots; ++sl) {
-          if ((it * slots + sl) % kProducers != p) continue;
-          const int c = sl / nlb, lb = sl - c * nlb;
-          const long long row = row0 + c * kSlotRows;
-          const int blk = job.bb[lb] + (int)rank;
-          if (row >= n || blk >= T) continue;
-          ptx::tma_load_3d(sx + (uint32_t)sl * kSlotBytes, &tmap, full, 0, (int)row, blk * 4);
+        {
+          int own = pown;
+          for (int c = 0, sl = 0; c < cps; ++c)
+            for (int lb = 0; lb < nlb; ++lb, ++sl) {
+              const bool me = own == p;
+              if (++own == kProducers) own = 0;
+              const long long row = row0 + c * kSlotRows;
+              if (!me || row >= n || blk_of[lb] >= T) continue;
+              ptx::tma_load_3d(sx + (uint32_t)sl * kSlotBytes, &tmap, full, 0, (int)row, blk_of[lb] * 4);
+            }
+          pown = own;
         }
         if (p == 0) DR4G_TRACE2(1);
         if (++s == nstages) { s = 0; ph ^= 1u; }
@@ -184,44 +195,64 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
   } else if (warp == kMmaWarp) {
     // ================================================================ MMA issuer (leader CTA, one lane)
     if (rank == 0 && ptx::elect_one()) {
+      // One thread feeds the tensor pipe: no divisions, no constant-bank indexing inside the loop
+      // (a first version spent ~1900 cycles per 12-MMA stage on exactly that, measured).
       constexpr uint32_t idesc = ptx::make_idesc_tf32(256, 256, true, true);
-      int s = 0, window = 0;
+      const int nks = (trace & 2) ? 0 : kt / 8;
+      const uint32_t boff0 = (uint32_t)job.lb_of[0] * kSlotBytes, boff1 = (uint32_t)job.lb_of[1] * kSlotBytes;
+      const uint32_t slot_row_bytes = (uint32_t)nlb * kSlotBytes;   // next 16 rows of the same local block
+      const uint64_t desc0 = ptx::make_smem_desc(0, 2048, 512, ptx::kLayoutSw128Base32);  // address added below
+      int s = 0, window = 0, wpos = stagger, set = 0;
       uint32_t ph = 0;
+      uint32_t sx = smem_base;
+      bool window_start = true;
       for (int it = 0; it < my_chunks; ++it) {
-        const bool window_start = it == 0 || (it + stagger) % fc == 0;
-        const int set = window % nacc;
         if (window_start && window >= nacc) {
           // the epilogue warps of both CTAs have drained this accumulator set
-          ptx::mbar_wait_cluster(ptx::smem_u32(&bar_acc_empty[set]), (uint32_t)(window / nacc - 1) & 1u);
+          ptx::mbar_wait_cluster(ptx::smem_u32(&bar_acc_empty[set]), (uint32_t)(nacc == 2 ? (window - 2) >> 1 : window - 1) & 1u);
           ptx::tc_fence_after_sync();
         }
         ptx::mbar_wait_cluster(ptx::smem_u32(&bar_conv[s]), ph);
         ptx::tc_fence_after_sync();
         DR4G_TRACE2(5);
-        const uint32_t sx = smem_base + (uint32_t)s * stage_bytes;
-        for (int ks = 0; ks < ((trace & 2) ? 0 : kt / 8); ++ks) {
-          const uint32_t acc = (window_start && ks == 0) ? 0u : 1u;
-          const uint32_t row_off = (uint32_t)((ks >> 1) * nlb) * kSlotBytes + (uint32_t)(ks & 1) * 1024u;
-          const uint64_t a_hi = ptx::make_smem_desc(sx + row_off, 2048, 512, ptx::kLayoutSw128Base32);
-          const uint64_t a_lo = ptx::make_smem_desc(sx + half_bytes + row_off, 2048, 512, ptx::kLayoutSw128Base32);
-          for (int j = 0; j < nchunk; ++j) {
-            const uint32_t b_off = row_off + (uint32_t)job.lb_of[j] * kSlotBytes;
-            const uint64_t b_hi = ptx::make_smem_desc(sx + b_off, 2048, 512, ptx::kLayoutSw128Base32);
-            const uint64_t b_lo = ptx::make_smem_desc(sx + half_bytes + b_off, 2048, 512, ptx::kLayoutSw128Base32);
-            const uint32_t dcol = tmem_base + (uint32_t)(set + j) * 256u;
-            ptx::mma_tf32_ss_pair(dcol, a_hi, b_hi, idesc, acc);
-            ptx::mma_tf32_ss_pair(dcol, a_hi, b_lo, idesc, 1u);
-            ptx::mma_tf32_ss_pair(dcol, a_lo, b_hi, idesc, 1u);
+        const uint32_t d0 = tmem_base + (uint32_t)set * 256u;
+        uint32_t acc = window_start ? 0u : 1u;
+        uint32_t row = sx;
+#pragma unroll 1
+        for (int ks = 0; ks < nks; ks += 2) {
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const uint32_t r = row + (uint32_t)h * 1024u;
+            const uint64_t a_hi = desc0 | (uint64_t)((r >> 4) & 0x3FFF);
+            const uint64_t a_lo = desc0 | (uint64_t)(((r + half_bytes) >> 4) & 0x3FFF);
+            const uint64_t b_hi = desc0 | (uint64_t)(((r + boff0) >> 4) & 0x3FFF);
+            const uint64_t b_lo = desc0 | (uint64_t)(((r + boff0 + half_bytes) >> 4) & 0x3FFF);
+            ptx::mma_tf32_ss_pair(d0, a_hi, b_hi, idesc, acc);
+            ptx::mma_tf32_ss_pair(d0, a_hi, b_lo, idesc, 1u);
+            ptx::mma_tf32_ss_pair(d0, a_lo, b_hi, idesc, 1u);
+            if (nchunk == 2) {
+              const uint64_t c_hi = desc0 | (uint64_t)(((r + boff1) >> 4) & 0x3FFF);
+              const uint64_t c_lo = desc0 | (uint64_t)(((r + boff1 + half_bytes) >> 4) & 0x3FFF);
+              ptx::mma_tf32_ss_pair(d0 + 256u, a_hi, c_hi, idesc, acc);
+              ptx::mma_tf32_ss_pair(d0 + 256u, a_hi, c_lo, idesc, 1u);
+              ptx::mma_tf32_ss_pair(d0 + 256u, a_lo, c_hi, idesc, 1u);
+            }
+            acc = 1u;
           }
+          row += slot_row_bytes;
         }
         ptx::mma_commit_pair(ptx::smem_u32(&bar_empty[s]), 3);   // stage free in both CTAs
         DR4G_TRACE2(6);
-        const bool window_end = (it + stagger + 1) % fc == 0 || it == my_chunks - 1;
-        if (window_end) {
+        window_start = false;
+        if (++wpos == fc || it == my_chunks - 1) {              // window end
           ptx::mma_commit_pair(ptx::smem_u32(&bar_acc_full[set]), 3);
           ++window;
+          wpos = 0;
+          window_start = true;
+          if (nacc == 2) set ^= 1;
         }
-        if (++s == nstages) { s = 0; ph ^= 1u; }
+        sx += stage_bytes;
+        if (++s == nstages) { s = 0; ph ^= 1u; sx = smem_base; }
       }
     }
   } else if (warp < kConvWarps) {
@@ -348,11 +379,12 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
     int window = 0;
     // a window of fc stages lasts about fc * kt / 8 * nchunk * 384 cycles; spend ~1/3 of it draining
     const unsigned pace_ns = (unsigned)(fc * kt * nchunk * 48 / 3 / 4 / 2);  // cycles -> ~ns at 2 GHz, per part
+    int wpos = stagger;
     for (int it = 0; it < my_chunks; ++it) {
-      const bool window_end = (it + stagger + 1) % fc == 0 || it == my_chunks - 1;
-      if (!window_end) continue;
-      const int set = window % nacc;
-      ptx::mbar_wait(ptx::smem_u32(&bar_acc_full[set]), (uint32_t)(window / nacc) & 1u);
+      if (++wpos != fc && it != my_chunks - 1) continue;
+      wpos = 0;
+      const int set = nacc == 2 ? (window & 1) : 0;
+      ptx::mbar_wait(ptx::smem_u32(&bar_acc_full[set]), (uint32_t)(nacc == 2 ? window >> 1 : window) & 1u);
       ptx::tc_fence_after_sync();
       for (int j = 0; j < nchunk; ++j) {
         float* dst_row = my_slab + ((size_t)j * kBlk + quadrant * 32 + lane) * 256;
