@@ -324,9 +324,9 @@ def main() -> None:
                     na, nb = min(2, T - 2 * I), min(2, T - 2 * J)
                     tiles += na * (na + 1) // 2 if I == J else na * nb
             if ctx.last_gram_path == "tcgen05_pair":
-                # CTA-pair kernel: 256-wide super-blocks, upper block triangle by 256, three tf32
-                # products each (csrc/gram_tc2.cu): issued = 3 * S(S+1)/2 * 256^2 / d^2 of 2nd^2
-                issued_factor = 3.0 * (S * (S + 1) // 2) * 65536.0 / (d * d)
+                # CTA-pair kernel (csrc/gram_tc2.cu): 256-wide super-tiles, upper block triangle by 256;
+                # three tf32 products per off-diagonal super-tile, two per diagonal one (G = P + R + R^T)
+                issued_factor = (2.0 * S + 3.0 * (S * (S - 1) // 2)) * 65536.0 / (d * d)
             elif ctx.last_gram_path == "tcgen05":
                 issued_factor = 3.0 * tiles / (T * T)
             else:

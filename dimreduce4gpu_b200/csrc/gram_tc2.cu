@@ -15,10 +15,15 @@
 // 256 (A) or 256 (B) output rows/columns, so conversion stays under the MMA time for every d.
 //
 // Work decomposition.  Columns are cut into blocks of 128 (T blocks) and super-blocks of 256.  A
-// JOB is (row super-block I) x (one or two N-chunks of 256 columns at or right of the diagonal):
-// CTA rank r of the pair owns A block 2I + r (its 128 accumulator lanes) and, for every chunk,
-// B block cb + r (its half of the 256 columns).  The block upper triangle by 256 is covered, so
-// 2nd^2 * (S(S+1)/2) / S^2 flops are issued (S = ceil(d/256)) - 3/4 of the full product at d = 512.
+// JOB is (row super-block I) x (one or two N-chunks of 256 columns): CTA rank r of the pair owns A
+// block 2I + r (its 128 accumulator lanes) and, for every chunk, B block cb + r (its half of the 256
+// columns).  Only the block upper triangle by 256 is computed (S = ceil(d/256) diagonal super-tiles,
+// S(S-1)/2 off-diagonal ones).  An off-diagonal super-tile takes the three tf32 products
+// hi^T hi + hi^T lo + lo^T hi into one accumulator; a DIAGONAL super-tile (A and B are the same
+// columns) takes only two, P = hi^T hi and R = hi^T lo, into separate accumulators, because
+// lo^T hi = R^T: G = P + R + R^T is formed by reduce_pair_slabs_kernel.  Issued tensor flops are
+// (2 S + 3 S(S-1)/2) * 256^2 * 2n: 2.0x the algorithmic 2nd^2 at d = 256, 1.75x at d = 512, 1.63x at
+// d = 1024 (3.0 / 2.25 / 1.88 without the symmetric diagonal).
 // A job's clusters split the rows (stage chunks it * ncl + split); partial accumulators go to per-CTA
 // fp32 slabs that reduce_pair_slabs_kernel sums in fp64 in a fixed order (deterministic).
 //
@@ -70,6 +75,7 @@ struct PJob {
   int bb[3];        // first global block of local block lb (rank r loads bb + r)
   int lb_of[2];     // local block holding a chunk's B half
   int stats;        // 1: this job owns the column statistics of its A blocks
+  int diag;         // 1: diagonal super-tile, two accumulators P = hi^T hi and R = hi^T lo (G = P + R + R^T)
   int cl_begin;     // first cluster of this job
   int ncl;          // clusters (row splits)
 };
@@ -110,9 +116,13 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
   const long long n_chunks = (n + kt - 1) / kt;
   if (split >= job.ncl || split >= n_chunks) return;    // both CTAs of a pair take the same branch
   const int my_chunks = (int)((n_chunks - split + job.ncl - 1) / job.ncl);
-  const int fc = flush_rows > kt ? flush_rows / kt : 1;          // stages per flush window
+  // Stages per flush window.  `flush_rows` is calibrated for three accumulating MMAs per 8 rows; P of a
+  // diagonal job takes one (R, 2^-11 of P, is never flushed before the end), so its window is 4x longer.
+  const int diag = job.diag;
+  const int fc0 = flush_rows > kt ? flush_rows / kt : 1;
+  const int fc = diag ? 4 * fc0 : fc0;
   const int stagger = (split & 3) * (fc >> 2);                    // window phase of this cluster
-  const int nacc = nchunk == 1 ? 2 : 1;                           // accumulator sets in TMEM
+  const int nacc = (nchunk == 1 && !diag) ? 2 : 1;                // accumulator sets in TMEM
   const int T = (d + kBlk - 1) / kBlk;
 
   extern __shared__ uint8_t smem_raw[];
@@ -203,7 +213,7 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
       const uint32_t slot_row_bytes = (uint32_t)nlb * kSlotBytes;   // next 16 rows of the same local block
       const uint64_t desc0 = ptx::make_smem_desc(0, 2048, 512, ptx::kLayoutSw128Base32);  // address added below
       int s = 0, window = 0, wpos = stagger, set = 0;
-      uint32_t ph = 0;
+      uint32_t ph = 0, racc = 0u;
       uint32_t sx = smem_base;
       bool window_start = true;
       for (int it = 0; it < my_chunks; ++it) {
@@ -227,6 +237,15 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
             const uint64_t a_lo = desc0 | (uint64_t)(((r + half_bytes) >> 4) & 0x3FFF);
             const uint64_t b_hi = desc0 | (uint64_t)(((r + boff0) >> 4) & 0x3FFF);
             const uint64_t b_lo = desc0 | (uint64_t)(((r + boff0 + half_bytes) >> 4) & 0x3FFF);
+            if (diag) {
+              // P (columns 0-255) += hi^T hi, R (columns 256-511) += hi^T lo; lo^T hi = R^T is added by
+              // reduce_pair_slabs_kernel: 2 MMAs per 8 rows instead of 3
+              ptx::mma_tf32_ss_pair(d0, a_hi, b_hi, idesc, acc);
+              ptx::mma_tf32_ss_pair(d0 + 256u, a_hi, b_lo, idesc, racc);
+              racc = 1u;
+              acc = 1u;
+              continue;
+            }
             ptx::mma_tf32_ss_pair(d0, a_hi, b_hi, idesc, acc);
             ptx::mma_tf32_ss_pair(d0, a_hi, b_lo, idesc, 1u);
             ptx::mma_tf32_ss_pair(d0, a_lo, b_hi, idesc, 1u);
@@ -386,9 +405,14 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
       const int set = nacc == 2 ? (window & 1) : 0;
       ptx::mbar_wait(ptx::smem_u32(&bar_acc_full[set]), (uint32_t)(nacc == 2 ? window >> 1 : window) & 1u);
       ptx::tc_fence_after_sync();
-      for (int j = 0; j < nchunk; ++j) {
+      // accumulators to drain: the chunks of an ordinary job; P of a diagonal job and, at its very
+      // last window, R as well (stored once into the second slab plane)
+      const bool last = it == my_chunks - 1;
+      const int ndrain = diag ? (last ? 2 : 1) : nchunk;
+      for (int j = 0; j < ndrain; ++j) {
         float* dst_row = my_slab + ((size_t)j * kBlk + quadrant * 32 + lane) * 256;
         const uint32_t tbase = tmem_base + ((uint32_t)(quadrant * 32) << 16) + (uint32_t)(set + j) * 256u;
+        const bool store = window == 0 || (diag && j == 1);
 #pragma unroll 1
         for (int part = 0; part < 4; ++part) {
           // With two accumulator sets the drain has a whole window to finish: pace it, so that the
@@ -399,7 +423,7 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
           ptx::tmem_ld_32x32(tbase + (uint32_t)(part * 64 + 32), w);
           ptx::tmem_ld_wait();
           float* dst = dst_row + part * 64;
-          if (window == 0) {
+          if (store) {
 #pragma unroll
             for (int q = 0; q < 32; q += 4) {
               asm volatile("st.global.v4.b32 [%0], {%1,%2,%3,%4};" ::"l"(dst + q), "r"(v[q]), "r"(v[q + 1]), "r"(v[q + 2]), "r"(v[q + 3]) : "memory");
@@ -446,9 +470,19 @@ reduce_pair_slabs_kernel(const __grid_constant__ PJobTable table, const float* _
   // the diagonal chunk holds both (a, b) and (b, a), accumulated in different orders: keep the
   // upper one so that G is exactly symmetric
   if (gb < ga) return;
+  const size_t cta_stride = 2 * (size_t)kSlabFloats;   // next cluster, same rank
   const float* p = slab + ((size_t)(job.cl_begin * 2 + r)) * kSlabFloats + ((size_t)j * kBlk + m) * 256 + nn;
   double acc = 0.0;
-  for (int c = 0; c < active; ++c) acc += (double)p[(size_t)c * 2 * kSlabFloats];
+  for (int c = 0; c < active; ++c) acc += (double)p[(size_t)c * cta_stride];
+  if (job.diag) {
+    // plane 0 = P = hi^T hi (+ nothing else), plane 1 = R = hi^T lo:  G = P + R + R^T
+    const float* q = p + (size_t)kBlk * 256;   // R[a][b]
+    const int rb = nn >> 7, mb = nn & (kBlk - 1), na = r * kBlk + m;   // (b, a) inside the 256 x 256 super-tile
+    const float* qt = slab + ((size_t)(job.cl_begin * 2 + rb)) * kSlabFloats + ((size_t)kBlk + mb) * 256 + na;  // R[b][a]
+    double racc = 0.0;
+    for (int c = 0; c < active; ++c) racc += (double)q[(size_t)c * cta_stride] + (double)qt[(size_t)c * cta_stride];
+    acc += racc;
+  }
   G[(size_t)ga * d + gb] = acc;
   G[(size_t)gb * d + ga] = acc;
 }
@@ -458,37 +492,52 @@ reduce_pair_slabs_kernel(const __grid_constant__ PJobTable table, const float* _
 // ---------------------------------------------------------------- host side
 namespace {
 
+// cost of a job in MMA time per 8 rows (units of one 256 x 256 x 8 MMA)
+int job_cost(const PJob& j) { return j.diag ? 2 : 3 * j.nchunk; }
+
 bool build_pair_jobs(int d, int sm_count, PJobTable& tab) {
   const int T = (d + kBlk - 1) / kBlk;
   const int S = (T + 1) / 2;
   const int clusters = sm_count / 2;
   tab.njobs = 0;
   int total_cost = 0;
-  for (int I = 0; I < S; ++I)
-    for (int c0 = 2 * I; c0 < T; c0 += 4) {
-      if (tab.njobs == kMaxPJobs) return false;
+  auto push = [&](const PJob& j) {
+    if (tab.njobs == kMaxPJobs) return false;
+    tab.job[tab.njobs++] = j;
+    total_cost += job_cost(j);
+    return true;
+  };
+  for (int I = 0; I < S; ++I) {
+    // diagonal super-tile: A and B are the same blocks
+    PJob dj{};
+    dj.I = I;
+    dj.nchunk = 1;
+    dj.cb[0] = 2 * I;
+    dj.nlb = 1;
+    dj.bb[0] = 2 * I;
+    dj.lb_of[0] = 0;
+    dj.stats = 1;
+    dj.diag = 1;
+    if (!push(dj)) return false;
+    // super-tiles right of the diagonal, two per job
+    for (int c0 = 2 * I + 2; c0 < T; c0 += 4) {
       PJob j{};
       j.I = I;
       j.nlb = 1;
       j.bb[0] = 2 * I;
       for (int cb = c0; cb < T && cb < c0 + 4; cb += 2) {
         j.cb[j.nchunk] = cb;
-        if (cb == 2 * I) {
-          j.lb_of[j.nchunk] = 0;
-          j.stats = 1;
-        } else {
-          j.bb[j.nlb] = cb;
-          j.lb_of[j.nchunk] = j.nlb++;
-        }
+        j.bb[j.nlb] = cb;
+        j.lb_of[j.nchunk] = j.nlb++;
         ++j.nchunk;
       }
-      tab.job[tab.njobs++] = j;
-      total_cost += j.nchunk;
+      if (!push(j)) return false;
     }
+  }
   if (tab.njobs > clusters) return false;
   int given = 0;
   for (int i = 0; i < tab.njobs; ++i) {
-    int m = (int)((long long)clusters * tab.job[i].nchunk / total_cost);
+    int m = (int)((long long)clusters * job_cost(tab.job[i]) / total_cost);
     if (m < 1) m = 1;
     tab.job[i].ncl = m;
     given += m;
@@ -498,7 +547,7 @@ bool build_pair_jobs(int d, int sm_count, PJobTable& tab) {
     int best = 0;
     double worst = -1.0;
     for (int i = 0; i < tab.njobs; ++i) {
-      const double load = (double)tab.job[i].nchunk / tab.job[i].ncl;
+      const double load = (double)job_cost(tab.job[i]) / tab.job[i].ncl;
       if (load > worst) { worst = load; best = i; }
     }
     tab.job[best].ncl++;
@@ -509,7 +558,7 @@ bool build_pair_jobs(int d, int sm_count, PJobTable& tab) {
     double least = 1e30;
     for (int i = 0; i < tab.njobs; ++i) {
       if (tab.job[i].ncl <= 1) continue;
-      const double load = (double)tab.job[i].nchunk / (tab.job[i].ncl - 1);
+      const double load = (double)job_cost(tab.job[i]) / (tab.job[i].ncl - 1);
       if (load < least) { least = load; best = i; }
     }
     if (best < 0) return false;
