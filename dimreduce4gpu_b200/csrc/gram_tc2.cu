@@ -377,7 +377,10 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
       // the MMA's operand reads), then arrive (release at cluster scope) on the leader's barrier
       ptx::fence_proxy_async_smem();
       __syncwarp();
-      if (lane == 0) ptx::mbar_arrive_cluster(conv_leader + (uint32_t)s * 8u);
+      if (lane == 0) {
+        if (trace & 8) ptx::mbar_arrive_cluster(conv_leader + (uint32_t)s * 8u);
+        else ptx::mbar_arrive_cluster_relaxed(conv_leader + (uint32_t)s * 8u);
+      }
       if (lane == 0 && rg == 0) DR4G_TRACE2(4);
       if (++s == nstages) { s = 0; ph ^= 1u; }
     }
@@ -492,8 +495,13 @@ reduce_pair_slabs_kernel(const __grid_constant__ PJobTable table, const float* _
 // ---------------------------------------------------------------- host side
 namespace {
 
-// cost of a job in MMA time per 8 rows (units of one 256 x 256 x 8 MMA)
-int job_cost(const PJob& j) { return j.diag ? 2 : 3 * j.nchunk; }
+// Relative cost of a job per row (x10): MMA time is 2 : 3 per chunk, but an off-diagonal job converts
+// two blocks per 16 rows against a diagonal job's one per 16 rows, and conversion is not free.
+// DR4G_OCOST overrides the off-diagonal figure (tuning hook).
+int job_cost(const PJob& j) {
+  static const int ocost = getenv("DR4G_OCOST") ? atoi(getenv("DR4G_OCOST")) : 40;  // 26..42 swept on B200: 40 is best at d = 512 and 1024
+  return j.diag ? 20 : ocost * j.nchunk;
+}
 
 bool build_pair_jobs(int d, int sm_count, PJobTable& tab) {
   const int T = (d + kBlk - 1) / kBlk;
