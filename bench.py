@@ -345,6 +345,13 @@ def main() -> None:
                 ach = bytes_alg / sec / 1e9
                 roof = dict(bound="hbm", achieved=ach, peak=peaks["hbm_gbs"], unit="GB/s", frac=ach / peaks["hbm_gbs"],
                             traffic=None)
+            # dram bytes of this kernel from the committed ncu capture of the same workload (per launch), if any
+            tj = ROOT / "profiles" / "r01_ncu_traffic.json"
+            if tj.is_file():
+                t = json.loads(tj.read_text()).get(args.workload)
+                if t and ctx.last_gram_path == "tcgen05_pair":
+                    roof["traffic"] = t["traffic_bytes_per_launch"]
+                    roof["traffic_source"] = t["source"]
             roof.update(kernel=f"gram ({ctx.last_gram_path})", kernel_ms=gram_ms, peak_source=peaks["source"],
                         arithmetic_intensity_flop_per_byte=d / 2.0,
                         achieved_tflops_algorithmic=flops_alg / sec / 1e12,
