@@ -20,6 +20,7 @@
 // so the rank-2 update of one column and the matrix-vector product of the next share one sweep
 // over the rows and one barrier.
 #include <cfloat>
+#include <cstdlib>
 
 #include "common.cuh"
 
@@ -599,6 +600,56 @@ backtransform_kernel(const double* __restrict__ Vh, const double* __restrict__ t
   for (int i = tid; i < d; i += 256) Z[(size_t)j * d + i] = z[i];
 }
 
+// T4, d <= 512: one WARP per vector, z and the reflector row in registers (element i = lane + 32 u),
+// no block barrier on the dependent chain (the CTA-per-vector version needs two per reflector).
+// Four warps per CTA so that the fp64 work spreads over many SMs (fp64 issue is scarce on B200: a
+// 32-warp CTA with the reflectors staged in shared memory was slower, measured).  The next reflector
+// row and tau are fetched one step ahead.
+template <int PER>
+__global__ void __launch_bounds__(128)
+backtransform_warp_kernel(const double* __restrict__ Vh, const double* __restrict__ tau, int d, int k,
+                          double* __restrict__ Z) {
+  const int lane = threadIdx.x & 31, j = blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (j >= k) return;
+  double z[PER], nxt[PER];
+#pragma unroll
+  for (int u = 0; u < PER; ++u) {
+    const int i = lane + 32 * u;
+    z[u] = i < d ? Z[(size_t)j * d + i] : 0.0;
+    nxt[u] = 0.0;
+  }
+  auto fetch = [&](int s) {
+    const double* vr = Vh + (size_t)s * d;
+#pragma unroll
+    for (int u = 0; u < PER; ++u) {
+      const int i = lane + 32 * u;
+      nxt[u] = (i > s && i < d) ? __ldg(&vr[i]) : 0.0;
+    }
+  };
+  double tnext = 0.0;
+  if (d >= 3) { fetch(d - 3); tnext = __ldg(&tau[d - 3]); }
+  for (int s = d - 3; s >= 0; --s) {
+    double cur[PER];
+#pragma unroll
+    for (int u = 0; u < PER; ++u) cur[u] = nxt[u];
+    const double t = tnext;
+    if (s > 0) { fetch(s - 1); tnext = __ldg(&tau[s - 1]); }
+    double dot = 0.0;
+#pragma unroll
+    for (int u = 0; u < PER; ++u) dot = fma(cur[u], z[u], dot);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
+    dot *= t;
+#pragma unroll
+    for (int u = 0; u < PER; ++u) z[u] = fma(-dot, cur[u], z[u]);
+  }
+#pragma unroll
+  for (int u = 0; u < PER; ++u) {
+    const int i = lane + 32 * u;
+    if (i < d) Z[(size_t)j * d + i] = z[u];
+  }
+}
+
 }  // namespace
 
 // ---------------------------------------------------------------- host side
@@ -629,7 +680,8 @@ void launch_eigh_topk(Ctx& c, double* dA, int d, int k, double* dW, double* dVt,
   // T1: d <= 512 runs inside one thread-block cluster (hardware barrier, DSMEM exchange); larger d uses
   // the cooperative grid with an atomic barrier, rows in shared memory whenever they fit
   if (d <= 512 && c.eig_solver != 2) {
-    const int cs = d <= 128 ? 1 : (d <= 256 ? 8 : 16);
+    static const int cs_env = getenv("DR4G_TRI_CS") ? atoi(getenv("DR4G_TRI_CS")) : 0;  // tuning hook
+    const int cs = cs_env > 0 ? cs_env : (d <= 128 ? 1 : 16);  // 16 beats 8 at d = 256 (1.16 vs 1.28 ms, measured)
     const size_t smem = ((size_t)6 * d + (size_t)((d + cs - 1) / cs) * d) * sizeof(double);
     static size_t smem_set = 0;
     static bool nonportable_set = false;
@@ -690,7 +742,9 @@ void launch_eigh_topk(Ctx& c, double* dA, int d, int k, double* dW, double* dVt,
   invit_kernel<<<k, kInvThreads, iv_smem, c.stream>>>(diag, off, d, k, lam, info, dW, dVt);
   // T4
   const size_t bt_smem = (size_t)d * sizeof(double);
-  backtransform_kernel<<<k, 256, bt_smem, c.stream>>>(Vh, tau, d, k, dVt);
+  if (d <= 256) backtransform_warp_kernel<8><<<(k + 3) / 4, 128, 0, c.stream>>>(Vh, tau, d, k, dVt);
+  else if (d <= 512) backtransform_warp_kernel<16><<<(k + 3) / 4, 128, 0, c.stream>>>(Vh, tau, d, k, dVt);
+  else backtransform_kernel<<<k, 256, bt_smem, c.stream>>>(Vh, tau, d, k, dVt);
   c.launches += 4;
   DR4G_CUDA(cudaGetLastError());
 }
