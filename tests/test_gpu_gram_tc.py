@@ -1,5 +1,6 @@
-"""The tcgen05 Gram + column-statistics kernel (csrc/gram_tc.cu) through the C ABI (dr4g_gram_float,
-dr4g_fit_float with gram_path=2) against an fp64 product of the same inputs.
+"""The tcgen05 Gram + column-statistics kernels (csrc/gram_tc2.cu: CTA pairs, d > 128 and d % 32 == 0;
+csrc/gram_tc.cu: single CTA, the other shapes) through the C ABI (dr4g_gram_float, dr4g_fit_float
+with gram_path=2 / 3) against an fp64 product of the same inputs.
 
 Tolerance: 3xTF32 with 1024-row flush windows reproduces X^T X to about 2e-5 of sqrt(G_ii G_jj)
 (the tensor core truncates its fp32 accumulation, about 1.6e-8 relative per accumulated row); the
@@ -42,8 +43,11 @@ def _rel_err(G, Xd):
 
 # shapes: one/two/three/four/eight column blocks, ragged d (d % 128 != 0, d % 32 != 0), ragged n
 # (n % 64 != 0, n < one chunk, n < number of CTAs * chunk), and a long stream with many flush windows
+# pair kernel: fewer rows than one stage, odd number of 256-column super-blocks (768), a partial last block
+# (320, 384), several flush windows of the diagonal jobs (600000 x 256: 8108 rows per cluster, window 4096)
 SHAPES = [(1, 4), (3, 8), (64, 128), (200, 128), (4099, 100), (5000, 256), (3001, 320), (2500, 384),
-          (8192, 512), (3000, 516), (4096, 1024), (300000, 256), (70000, 512)]
+          (8192, 512), (3000, 516), (4096, 1024), (300000, 256), (70000, 512),
+          (10, 256), (33, 512), (1000, 768), (600000, 256), (20000, 2048)]
 
 
 @pytest.mark.parametrize("n,d", SHAPES)
@@ -58,6 +62,21 @@ def test_gram_tc_matches_fp64(n, d, shifted):
     Xd = X.double() - (shift.double() if shifted else 0.0)
     assert _rel_err(G, Xd) < GRAM_TOL
     assert float((G - G.T).abs().max()) == 0.0  # mirrored, exactly symmetric
+
+
+@pytest.mark.parametrize("n,d", [(5000, 256), (3001, 320), (9000, 512), (4096, 1024)])
+def test_pair_kernel_agrees_with_single_cta_kernel(n, d):
+    """gram_path=2 takes the CTA-pair kernel for these shapes, gram_path=3 forces the single-CTA one."""
+    import torch
+
+    X = _make(n, d, 17 * n + d)
+    cp, cs = _ctx(2), _ctx(3)
+    Gp = cp.gram(X).clone()
+    Gs = cs.gram(X).clone()
+    torch.cuda.synchronize()
+    assert cp.last_gram_path == "tcgen05_pair" and cs.last_gram_path == "tcgen05"
+    dg = torch.sqrt(torch.diag(Gs))
+    assert float(((Gp - Gs).abs() / (dg[:, None] * dg[None, :])).max()) < GRAM_TOL
 
 
 def test_gram_tc_agrees_with_generic_dmma_path():
