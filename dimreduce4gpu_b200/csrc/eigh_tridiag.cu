@@ -70,6 +70,20 @@ __device__ __forceinline__ double tri_block_sum(double v, double* red) {
   return t;
 }
 
+// one-barrier variant: partials go to alternating buffers, so a warp that races ahead into the next
+// reduction writes the other buffer (a third reduction cannot start before everyone passed the second)
+__device__ __forceinline__ double tri_block_sum1(double v, double (*red)[kTriWarps], int& par) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  if ((threadIdx.x & 31) == 0) red[par][threadIdx.x >> 5] = v;
+  __syncthreads();
+  double t = 0;
+#pragma unroll
+  for (int w = 0; w < kTriWarps; ++w) t += red[par][w];
+  par ^= 1;
+  return t;
+}
+
 // A: d x d symmetric, row-major, destroyed.  Out: diag[d], off[d] (off[s] couples s and s+1; off[d-1] = 0),
 // tau[d], Vh[d x d] (row s = reflector of column s, entries s+1.. with Vh[s][s+1] = 1).
 // xbuf: 4 x d doubles of exchange space: p' (two parities) and the published next row (two parities).
@@ -199,17 +213,23 @@ __device__ __forceinline__ void st_cluster_f64(double* local_ptr, unsigned cta, 
   asm volatile("st.shared::cluster.f64 [%0], %1;" ::"r"(ra), "d"(val) : "memory");
 }
 
+// Debug aid (DR4G_TRI_TRACE=1): clock64() of CTA 0, thread 0 at the phase boundaries of steps 100..103.
+__device__ long long g_tri_trace[4 * 8];
+#define TRI_TRACE(ev) \
+  do { if ((trace & 1) && rank == 0 && tid == 0 && s >= 100 && s < 104) g_tri_trace[(s - 100) * 8 + (ev)] = clock64(); } while (0)
+
 __global__ void __launch_bounds__(kTriThreads)
 tridiag_cluster_kernel(const double* __restrict__ A, int d, double* __restrict__ diag, double* __restrict__ off,
-                       double* __restrict__ tau, double* __restrict__ Vh, double* __restrict__ xbuf) {
-  extern __shared__ double tri_sm[];
+                       double* __restrict__ tau, double* __restrict__ Vh, double* __restrict__ xbuf, int trace) {
+  extern __shared__ __align__(16) double tri_sm[];
   double* v = tri_sm;
   double* w = v + d;
   double* vn = w + d;
   double* row = vn + d;
   double* pl = row + d;        // p, two parities (pushed into every CTA by the row owners)
   double* R = pl + 2 * (size_t)d;  // own rows: slot i / cs
-  __shared__ double red[kTriWarps];
+  __shared__ double red2[2][kTriWarps];
+  int par = 0;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int rank = (int)cluster_rank(), cs = (int)cluster_size();
   double* rbuf = xbuf + 2 * (size_t)d;  // published rows, two parities (global)
@@ -222,43 +242,51 @@ tridiag_cluster_kernel(const double* __restrict__ A, int d, double* __restrict__
   cluster_barrier();  // also orders the zero-initialisation of pl before any remote push
 
   double tprev = 0.0;
+  int qfirst = 0, owner = 0, oslot = 0;   // row s belongs to CTA `owner`, slot `oslot` (s = owner + cs oslot)
+  const int nslots = (d - rank + cs - 1) / cs;   // own rows: rank, rank + cs, ...
   for (int s = 0; s < d - 1; ++s) {
     const double* pcur = pl + (size_t)((s + 1) & 1) * d;  // parity (s-1)&1
+    TRI_TRACE(0);
     // row s: from own shared memory when this CTA owns it, else the copy its owner published
     if (s == 0) {
       for (int c = tid; c < d; c += kTriThreads) row[c] = A[c];
-    } else if (s % cs == rank) {
-      const double* Rs = R + (size_t)(s / cs) * d;
+    } else if (owner == rank) {
+      const double* Rs = R + (size_t)oslot * d;
       for (int c = s + tid; c < d; c += kTriThreads) row[c] = Rs[c];
     } else {
       const double* rp = rbuf + (size_t)(s & 1) * d;
       for (int c = s + tid; c < d; c += kTriThreads) row[c] = __ldcg(&rp[c]);
     }
+    TRI_TRACE(1);
     double pv = 0.0;
     for (int c = s + tid; c < d; c += kTriThreads) pv += pcur[c] * vn[c];
-    pv = tri_block_sum(pv, red);
+    pv = tri_block_sum1(pv, red2, par);
+    TRI_TRACE(2);
     const double kk = 0.5 * tprev * pv;
+    // v <- previous reflector, w = p - kk v, corrected row r = row - v_s w - w_s v: one sweep, every
+    // thread needs only its own column besides the scalars v_s and w_s
+    const double vs = vn[s], ws = pcur[s] - kk * vs;
+    double nrm2 = 0.0;
     for (int c = tid; c < d; c += kTriThreads) {
       const double vv = vn[c];
+      const double wc = c >= s ? pcur[c] - kk * vv : 0.0;
       v[c] = vv;
-      w[c] = c >= s ? pcur[c] - kk * vv : 0.0;
+      w[c] = wc;
+      if (c >= s) {
+        const double r = row[c] - vs * wc - ws * vv;
+        row[c] = r;
+        if (c > s + 1) nrm2 += r * r;
+      }
     }
-    __syncthreads();
-    const double vs = v[s], ws = w[s];
-    double nrm2 = 0.0;
-    for (int c = s + tid; c < d; c += kTriThreads) {
-      const double r = row[c] - vs * w[c] - ws * v[c];
-      row[c] = r;
-      if (c > s + 1) nrm2 += r * r;
-    }
-    nrm2 = tri_block_sum(nrm2, red);
+    nrm2 = tri_block_sum1(nrm2, red2, par);
+    TRI_TRACE(3);
     const double x0 = row[s + 1];
     double beta = x0, t = 0.0, scale = 0.0;
     if (nrm2 > 0.0 && s < d - 2) {
       const double nrm = sqrt(x0 * x0 + nrm2);
       beta = x0 >= 0.0 ? -nrm : nrm;
-      t = (beta - x0) / beta;
-      scale = 1.0 / (x0 - beta);
+      t = (beta - x0) * fast_rcp(beta);
+      scale = fast_rcp(x0 - beta);
     }
     for (int c = tid; c < d; c += kTriThreads) vn[c] = c > s + 1 ? row[c] * scale : (c == s + 1 ? 1.0 : 0.0);
     if (rank == 0) {
@@ -266,26 +294,63 @@ tridiag_cluster_kernel(const double* __restrict__ A, int d, double* __restrict__
       for (int c = tid; c < d; c += kTriThreads) Vh[(size_t)s * d + c] = c > s + 1 ? row[c] * scale : (c == s + 1 ? 1.0 : 0.0);
     }
     __syncthreads();
+    TRI_TRACE(4);
     // own rows i > s: rank-2 update fused with p'_i; push p'_i into every CTA; publish row s+1
     double* pnext = pl + (size_t)(s & 1) * d;
-    const int first = s + 1 + ((rank - (s + 1)) % cs + cs) % cs;  // first own row > s
-    for (int i = first + cs * warp; i < d; i += cs * kTriWarps) {
-      const double vi = v[i], wi = w[i];
-      double* Ri = R + (size_t)(i / cs) * d;
-      double* pub = (i == s + 1 && cs > 1) ? rbuf + (size_t)((s + 1) & 1) * d : nullptr;
-      double dot = 0.0;
-      for (int c = s + 1 + lane; c < d; c += 32) {
-        const double a = Ri[c] - vi * w[c] - wi * v[c];
-        Ri[c] = a;
-        if (pub) __stcg(&pub[c], a);
-        dot = fma(a, vn[c], dot);
+    // own slots q (row i = rank + cs q) with i > s; qfirst advances with s (no division in the loop)
+    while (rank + cs * qfirst <= s) ++qfirst;
+    const int cbeg = (s + 1) & ~63;          // lanes take aligned pairs of columns: c = cbeg + 2 lane + 64 j
+    // two own rows per pass (independent dot chains and shuffle trees; w, v, v' are loaded once)
+    for (int q = qfirst + warp; q < nslots; q += 2 * kTriWarps) {
+      const bool two = q + kTriWarps < nslots;
+      const int i0 = rank + cs * q, i1 = i0 + cs * kTriWarps;
+      const double vi0 = v[i0], wi0 = w[i0];
+      const double vi1 = two ? v[i1] : 0.0, wi1 = two ? w[i1] : 0.0;
+      double* R0 = R + (size_t)q * d;
+      double* R1 = two ? R0 + (size_t)kTriWarps * d : R0;
+      double* pub0 = (i0 == s + 1 && cs > 1) ? rbuf + (size_t)((s + 1) & 1) * d : nullptr;
+      double* pub1 = (two && i1 == s + 1 && cs > 1) ? rbuf + (size_t)((s + 1) & 1) * d : nullptr;
+      double dot0 = 0.0, dot1 = 0.0;
+      for (int c = cbeg + 2 * lane; c < d; c += 64) {
+        const double2 wv = *reinterpret_cast<const double2*>(w + c);
+        const double2 vv = *reinterpret_cast<const double2*>(v + c);
+        const double2 nv = *reinterpret_cast<const double2*>(vn + c);
+        double2 a = *reinterpret_cast<const double2*>(R0 + c);
+        double2 b = *reinterpret_cast<const double2*>(R1 + c);
+        if (c > s) {
+          a.x = a.x - vi0 * wv.x - wi0 * vv.x;
+          b.x = b.x - vi1 * wv.x - wi1 * vv.x;
+          dot0 = fma(a.x, nv.x, dot0);
+          dot1 = fma(b.x, nv.x, dot1);
+        }
+        if (c + 1 > s) {
+          a.y = a.y - vi0 * wv.y - wi0 * vv.y;
+          b.y = b.y - vi1 * wv.y - wi1 * vv.y;
+          dot0 = fma(a.y, nv.y, dot0);
+          dot1 = fma(b.y, nv.y, dot1);
+        }
+        *reinterpret_cast<double2*>(R0 + c) = a;
+        if (two) *reinterpret_cast<double2*>(R1 + c) = b;
+        if (pub0 && !(trace & 4)) __stcg(reinterpret_cast<double2*>(pub0 + c), a);
+        if (pub1 && !(trace & 4)) __stcg(reinterpret_cast<double2*>(pub1 + c), b);
       }
+      if (!(trace & 8)) {
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
-      if (lane < cs) st_cluster_f64(&pnext[i], (unsigned)lane, t * dot);
+      for (int o = 16; o > 0; o >>= 1) {
+        dot0 += __shfl_xor_sync(0xffffffffu, dot0, o);
+        dot1 += __shfl_xor_sync(0xffffffffu, dot1, o);
+      }
+      }
+      if (lane < cs && !(trace & 2)) {
+        st_cluster_f64(&pnext[i0], (unsigned)lane, t * dot0);
+        if (two) st_cluster_f64(&pnext[i1], (unsigned)lane, t * dot1);
+      }
     }
     tprev = t;
+    if (++owner == cs) { owner = 0; ++oslot; }
+    TRI_TRACE(5);
     cluster_barrier();
+    TRI_TRACE(6);
   }
   if (d == 1) {
     if (tid == 0) { diag[0] = A[0]; off[0] = 0.0; tau[0] = 0.0; }
@@ -679,7 +744,7 @@ void launch_eigh_topk(Ctx& c, double* dA, int d, int k, double* dW, double* dVt,
 
   // T1: d <= 512 runs inside one thread-block cluster (hardware barrier, DSMEM exchange); larger d uses
   // the cooperative grid with an atomic barrier, rows in shared memory whenever they fit
-  if (d <= 512 && c.eig_solver != 2) {
+  if (d <= 512 && d % 2 == 0 && c.eig_solver != 2) {   // the cluster kernel sweeps rows in aligned column pairs
     static const int cs_env = getenv("DR4G_TRI_CS") ? atoi(getenv("DR4G_TRI_CS")) : 0;  // tuning hook
     const int cs = cs_env > 0 ? cs_env : (d <= 128 ? 1 : 16);  // 16 beats 8 at d = 256 (1.16 vs 1.28 ms, measured)
     const size_t smem = ((size_t)6 * d + (size_t)((d + cs - 1) / cs) * d) * sizeof(double);
@@ -705,7 +770,20 @@ void launch_eigh_topk(Ctx& c, double* dA, int d, int k, double* dW, double* dVt,
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    DR4G_CUDA(cudaLaunchKernelEx(&cfg, tridiag_cluster_kernel, (const double*)dA, d, diag, off, tau, Vh, xbuf));
+    static const int tri_trace = getenv("DR4G_TRI_TRACE") ? atoi(getenv("DR4G_TRI_TRACE")) : 0;
+    DR4G_CUDA(cudaLaunchKernelEx(&cfg, tridiag_cluster_kernel, (const double*)dA, d, diag, off, tau, Vh, xbuf, tri_trace));
+    if (tri_trace & 1) {
+      long long h[32];
+      DR4G_CUDA(cudaStreamSynchronize(c.stream));
+      DR4G_CUDA(cudaMemcpyFromSymbol(h, g_tri_trace, sizeof(h)));
+      fprintf(stderr, "tridiag trace d=%d (cycles from step start): row_fetched pv_done nrm_done vn_done rows_done barrier_done\n", d);
+      for (int i = 0; i < 4; ++i) {
+        fprintf(stderr, "  step %d:", 100 + i);
+        for (int e = 1; e < 7; ++e) fprintf(stderr, " %6lld", h[i * 8 + e] - h[i * 8]);
+        if (i < 3) fprintf(stderr, "  | next step starts at %6lld", h[(i + 1) * 8] - h[i * 8]);
+        fprintf(stderr, "\n");
+      }
+    }
   } else {
     int grid = (d + 2 * kTriWarps - 1) / (2 * kTriWarps);
     if (grid > c.sm_count) grid = c.sm_count;
