@@ -102,12 +102,175 @@ rowgemm_kernel(const T* __restrict__ A, long long n, int lda, int tdim, const T*
   }
 }
 
+
+// ---------------------------------------------------------------- fp32 projection, k <= 64
+// Z = (X - mean) Q^T, U = Z / sigma.  The generic kernel above reached ~0.6 TB/s (scalar shared-memory
+// reads, synchronous staging, half of its 64 output columns idle at k = 32).  This one is a register-
+// tiled SIMT GEMM: 256 threads, RT = 8192 / KP rows per CTA (256 rows at KP = 32, 128 at KP = 64), thread
+// tile 8 rows x 4 outputs, contraction in chunks of 32 columns.  Shared tiles are stored contraction-
+// major (As[t][row], Bs[t][m]) so that a thread's 8 rows / 4 outputs are 128-bit loads; X is read with
+// coalesced float4 (a lane = row mapping ran at half the speed: 32 lines per load instruction) and
+// transposed into a row-swizzled tile with conflict-free scalar stores, the next chunk's
+// global loads are in flight while the current one is multiplied (register prefetch, two smem buffers,
+// one barrier per chunk).  AI = k/2 flop/B: at k = 32 the fp32 FMA pipe (~74 TF/s) and HBM need about
+// the same time, so this is the CUDA-core ceiling; a tensor-core version would need 3xTF32 again.
+template <int KP>
+__global__ void __launch_bounds__(256, 2)
+project_f32_kernel(const float* __restrict__ X, long long n, int d, int k, const float* __restrict__ mean,
+                   const float* __restrict__ Q, const float* __restrict__ sigma, float* __restrict__ Z,
+                   float* __restrict__ U) {
+  constexpr int RT = 8192 / KP;        // rows per CTA
+  constexpr int TC = 32;               // contraction chunk
+  constexpr int XF = RT * TC / 256 / 4;  // float4 of X per thread and chunk (8 at KP = 32, 4 at KP = 64)
+  extern __shared__ __align__(16) float psm[];
+  float* As = psm;                       // [2][TC][RT]
+  float* Bs = psm + 2 * TC * RT;         // [2][TC][KP]
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tx = tid % (KP / 4), ty = tid / (KP / 4);
+  const long long row0 = (long long)blockIdx.x * RT;
+
+  // staging: a warp instruction reads 4 rows x 128 B (lane = (row r4 = lane / 8, float4 c4 = lane % 8)), the
+  // values go to As[t][row] transposed; rows are XOR-swizzled in groups of 4 by (t / 4) % 8 so that these
+  // scalar stores hit 32 distinct banks while a thread's 8 rows stay two aligned float4
+  constexpr int WR = RT / 8;             // rows per warp
+  const int c4 = lane & 7, r4 = lane >> 3;
+  const int srow0 = warp * WR + r4;      // + 4 j
+  const int swz = c4 << 2;               // ((4 c4 + e) / 4) % 8 = c4
+  // Q chunk: thread (m = tid % KP, quarter q = tid / KP) loads TC * KP / 256 floats
+  constexpr int BF = TC * KP / 256;      // 4 at KP = 32, 8 at KP = 64
+  const int bm = tid % KP, bt0 = (tid / KP) * BF;
+  const bool full_rows = row0 + RT <= n;
+
+  float4 xa[XF], mu4;
+  float bq[BF];
+  auto fetch = [&](int t0) {
+    const int t = t0 + 4 * c4;
+    const bool tin = t + 3 < d;          // d % 4 == 0: a float4 is inside or outside as a whole
+#pragma unroll
+    for (int j = 0; j < XF; ++j) {
+      const long long r = row0 + srow0 + 4 * j;
+      xa[j] = (tin && (full_rows || r < n)) ? __ldg(reinterpret_cast<const float4*>(X + r * (long long)d + t))
+                                            : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    mu4 = (mean && tin) ? __ldg(reinterpret_cast<const float4*>(mean + t)) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int j = 0; j < BF; ++j) {
+      const int tq = t0 + bt0 + j;
+      bq[j] = (bm < k && tq < d) ? __ldg(Q + (long long)bm * d + tq) : 0.f;
+    }
+  };
+  auto stash = [&](int buf, int t0) {
+    float* Ab = As + buf * TC * RT + (4 * c4) * RT;
+    float* Bb = Bs + buf * TC * KP;
+    const bool tin = t0 + 4 * c4 + 3 < d;
+#pragma unroll
+    for (int j = 0; j < XF; ++j) {
+      const int rl = srow0 + 4 * j;
+      const bool in = tin && (full_rows || row0 + rl < n);  // rows past n and columns past d contribute 0
+      const int pr = rl ^ swz;
+      Ab[0 * RT + pr] = in ? xa[j].x - mu4.x : 0.f;
+      Ab[1 * RT + pr] = in ? xa[j].y - mu4.y : 0.f;
+      Ab[2 * RT + pr] = in ? xa[j].z - mu4.z : 0.f;
+      Ab[3 * RT + pr] = in ? xa[j].w - mu4.w : 0.f;
+    }
+#pragma unroll
+    for (int j = 0; j < BF; ++j) Bb[(bt0 + j) * KP + bm] = bq[j];
+  };
+
+  float acc[8][4];
+#pragma unroll
+  for (int i = 0; i < 8; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+  fetch(0);
+  stash(0, 0);
+  __syncthreads();
+  int buf = 0;
+  for (int t0 = 0; t0 < d; t0 += TC) {
+    const bool more = t0 + TC < d;
+    if (more) fetch(t0 + TC);
+    const float* Ab = As + buf * TC * RT;
+    const float* Bb = Bs + buf * TC * KP + tx * 4;
+#pragma unroll 8
+    for (int t = 0; t < TC; ++t) {
+      const int g = ((t >> 2) & 7) << 2;
+      const float4 a0 = *reinterpret_cast<const float4*>(Ab + t * RT + ((ty * 8) ^ g));
+      const float4 a1 = *reinterpret_cast<const float4*>(Ab + t * RT + ((ty * 8 + 4) ^ g));
+      const float4 b = *reinterpret_cast<const float4*>(Bb + t * KP);
+      const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+      const float bb[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], bb[j], acc[i][j]);
+    }
+    if (more) stash(buf ^ 1, t0 + TC);
+    __syncthreads();
+    buf ^= 1;
+  }
+  // epilogue: 4 consecutive outputs per thread and row
+  float inv[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int m = tx * 4 + j;
+    const float sg = (U && sigma && m < k) ? __ldg(sigma + m) : 0.f;
+    inv[j] = sg != 0.f ? 1.f / sg : 0.f;
+  }
+  const bool vec = (k % 4) == 0;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const long long r = row0 + ty * 8 + i;
+    if (r >= n) continue;
+    const int m0 = tx * 4;
+    if (vec && m0 + 3 < k) {
+      *reinterpret_cast<float4*>(Z + r * k + m0) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+      if (U) *reinterpret_cast<float4*>(U + r * k + m0) =
+          make_float4(acc[i][0] * inv[0], acc[i][1] * inv[1], acc[i][2] * inv[2], acc[i][3] * inv[3]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (m0 + j < k) {
+          Z[r * k + m0 + j] = acc[i][j];
+          if (U) U[r * k + m0 + j] = acc[i][j] * inv[j];
+        }
+    }
+  }
+}
+
+template <int KP>
+void launch_project_f32(Ctx& c, const float* dX, long long n, int d, int k, const float* dQ, const float* dmean,
+                        const float* dw, float* dZ, float* dU) {
+  constexpr int RT = 8192 / KP;
+  const size_t smem = (size_t)2 * 32 * (RT + KP) * sizeof(float);
+  static bool set = false;
+  if (!set) {
+    DR4G_CUDA(cudaFuncSetAttribute(project_f32_kernel<KP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    set = true;
+  }
+  const long long blocks = (n + RT - 1) / RT;
+  project_f32_kernel<KP><<<(unsigned)blocks, 256, smem, c.stream>>>(dX, n, d, k, dmean, dQ, (dU && dw) ? dw : nullptr,
+                                                                   dZ, (dU && dw) ? dU : nullptr);
+}
+
 }  // namespace
 
 template <typename T>
 void launch_project(Ctx& c, const T* dX, long long n, int d, int k, const T* dQ, const T* dmean, const T* dw,
                     T* dZ, T* dU) {
   if (n <= 0) return;
+  if constexpr (sizeof(T) == 4) {
+    // 16-byte aligned rows (float4 loads of X, float4 stores of Z when k % 4 == 0)
+    const bool aligned = (reinterpret_cast<uintptr_t>(dX) & 15) == 0 && (d % 4) == 0 &&
+                         (reinterpret_cast<uintptr_t>(dZ) & 15) == 0 && (!dU || (reinterpret_cast<uintptr_t>(dU) & 15) == 0);
+    if (aligned && k <= 64) {
+      if (k <= 32) launch_project_f32<32>(c, dX, n, d, k, dQ, dmean, dw, dZ, dU);
+      else launch_project_f32<64>(c, dX, n, d, k, dQ, dmean, dw, dZ, dU);
+      c.launches++;
+      DR4G_CUDA(cudaGetLastError());
+      return;
+    }
+  }
   const long long blocks = (n + RT - 1) / RT;
   rowgemm_kernel<T><<<(unsigned)blocks, 256, 0, c.stream>>>(dX, n, d, d, dmean, dQ, (long long)d, 1LL, k, nullptr,
                                                             dw, dZ, (dU && dw) ? dU : nullptr, k);
