@@ -12,66 +12,109 @@
 // parity oracle is the CPU backend).
 //
 //   Q0 = orth(randn(d, l));  repeat: Y = C Q;  theta_j = q_j . y_j;  Q = orth(Y)
-//   B = Q^T C Q;  B = W diag(lambda) W^T (K4 Jacobi);  Ritz vectors = Q W
+//   B = Q^T C Q;  B = W diag(lambda) W^T (K4 tridiagonal solver, all l pairs);  Ritz vectors = Q W
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace dr4g {
 namespace {
 
 // ---- small fp64 GEMM with arbitrary strides: C(m,n) = sum_k A(m,k) B(k,n) -----------------
-constexpr int GT = 64, GK = 16;
+// Everything here is a few MFLOP on matrices that live in L2, so the kernels are latency-bound:
+// TM = 32 tiles when 64 x 64 tiles would leave most SMs idle, the next k-step's operands are
+// fetched into registers while the current one is multiplied (one barrier per step, two shared
+// buffers), and a long contraction with a tiny output (S = Y^T Y) is split over blockIdx.z into
+// partial products that the consumer (chol_inv_kernel) adds up in a fixed order.
+constexpr int GK = 16;
 
+template <int TM>
 __global__ void __launch_bounds__(256)
 dgemm_kernel(int M, int N, int K, const double* __restrict__ A, long long sa_m, long long sa_k,
              const double* __restrict__ B, long long sb_k, long long sb_n, double* __restrict__ C,
-             long long sc_m, long long sc_n, const int* __restrict__ done) {
+             long long sc_m, long long sc_n, const int* __restrict__ done, int kchunk, long long split_stride) {
   if (done && *done) return;
-  __shared__ double As[GK][GT + 1];
-  __shared__ double Bs[GK][GT + 1];
+  constexpr int PT = TM / 16;          // thread tile PT x PT
+  constexpr int NL = TM * GK / 256;    // operand elements per thread and k-step
+  __shared__ double As[2][GK][TM + 1];
+  __shared__ double Bs[2][GK][TM + 1];
   const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
-  const int m0 = blockIdx.y * GT, n0 = blockIdx.x * GT;
-  double acc[4][4] = {};
-  for (int k0 = 0; k0 < K; k0 += GK) {
-    for (int e = tid; e < GK * GT; e += 256) {
-      int kk, mm;
-      if (sa_k == 1) { kk = e % GK; mm = e / GK; } else { mm = e % GT; kk = e / GT; }
-      const int m = m0 + mm, k = k0 + kk;
-      As[kk][mm] = (m < M && k < K) ? A[m * sa_m + k * sa_k] : 0.0;
+  const int m0 = blockIdx.y * TM, n0 = blockIdx.x * TM;
+  const int kbeg = blockIdx.z * kchunk, kend = min(K, kbeg + kchunk);
+  C += (long long)blockIdx.z * split_stride;
+  // element e of a GK x TM operand tile: the fast index follows the unit stride of the operand
+  int akk[NL], amm[NL], bkk[NL], bnn[NL];
+#pragma unroll
+  for (int i = 0; i < NL; ++i) {
+    const int e = tid + 256 * i;
+    if (sa_k == 1) { akk[i] = e % GK; amm[i] = e / GK; } else { amm[i] = e % TM; akk[i] = e / TM; }
+    if (sb_k == 1) { bkk[i] = e % GK; bnn[i] = e / GK; } else { bnn[i] = e % TM; bkk[i] = e / TM; }
+  }
+  double ra[NL], rb[NL];
+  auto fetch = [&](int k0) {
+#pragma unroll
+    for (int i = 0; i < NL; ++i) {
+      const int m = m0 + amm[i], ka = k0 + akk[i];
+      ra[i] = (m < M && ka < kend) ? A[m * sa_m + ka * sa_k] : 0.0;
+      const int n = n0 + bnn[i], kb = k0 + bkk[i];
+      rb[i] = (n < N && kb < kend) ? B[kb * sb_k + n * sb_n] : 0.0;
     }
-    for (int e = tid; e < GK * GT; e += 256) {
-      int kk, nn;
-      if (sb_k == 1) { kk = e % GK; nn = e / GK; } else { nn = e % GT; kk = e / GT; }
-      const int n = n0 + nn, k = k0 + kk;
-      Bs[kk][nn] = (n < N && k < K) ? B[k * sb_k + n * sb_n] : 0.0;
+  };
+  auto stash = [&](int buf) {
+#pragma unroll
+    for (int i = 0; i < NL; ++i) {
+      As[buf][akk[i]][amm[i]] = ra[i];
+      Bs[buf][bkk[i]][bnn[i]] = rb[i];
     }
-    __syncthreads();
+  };
+  double acc[PT][PT] = {};
+  fetch(kbeg);
+  stash(0);
+  __syncthreads();
+  int buf = 0;
+  for (int k0 = kbeg; k0 < kend; k0 += GK) {
+    const bool more = k0 + GK < kend;
+    if (more) fetch(k0 + GK);
 #pragma unroll
     for (int kk = 0; kk < GK; ++kk) {
-      double a[4], b[4];
+      double a[PT], b[PT];
 #pragma unroll
-      for (int i = 0; i < 4; ++i) a[i] = As[kk][ty + 16 * i];
+      for (int i = 0; i < PT; ++i) a[i] = As[buf][kk][ty + 16 * i];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) b[j] = Bs[kk][tx + 16 * j];
+      for (int j = 0; j < PT; ++j) b[j] = Bs[buf][kk][tx + 16 * j];
 #pragma unroll
-      for (int i = 0; i < 4; ++i)
+      for (int i = 0; i < PT; ++i)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j] = fma(a[i], b[j], acc[i][j]);
+        for (int j = 0; j < PT; ++j) acc[i][j] = fma(a[i], b[j], acc[i][j]);
     }
+    if (more) stash(buf ^ 1);
     __syncthreads();
+    buf ^= 1;
   }
 #pragma unroll
-  for (int i = 0; i < 4; ++i)
+  for (int i = 0; i < PT; ++i)
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
+    for (int j = 0; j < PT; ++j) {
       const int m = m0 + ty + 16 * i, n = n0 + tx + 16 * j;
       if (m < M && n < N) C[m * sc_m + n * sc_n] = acc[i][j];
     }
 }
 
+// splits > 1: C is an array of `splits` partial products (split_stride doubles apart)
 void dgemm(Ctx& c, int M, int N, int K, const double* A, long long sa_m, long long sa_k, const double* B,
-           long long sb_k, long long sb_n, double* C, long long sc_m, long long sc_n, const int* done) {
-  dim3 grid(ceil_div(N, GT), ceil_div(M, GT));
-  dgemm_kernel<<<grid, 256, 0, c.stream>>>(M, N, K, A, sa_m, sa_k, B, sb_k, sb_n, C, sc_m, sc_n, done);
+           long long sb_k, long long sb_n, double* C, long long sc_m, long long sc_n, const int* done,
+           int splits = 1, long long split_stride = 0) {
+  const int kchunk = ceil_div(ceil_div(K, splits), GK) * GK;
+  const bool small = (long long)ceil_div(N, 64) * ceil_div(M, 64) * splits < c.sm_count;
+  if (small) {
+    dim3 grid(ceil_div(N, 32), ceil_div(M, 32), splits);
+    dgemm_kernel<32><<<grid, 256, 0, c.stream>>>(M, N, K, A, sa_m, sa_k, B, sb_k, sb_n, C, sc_m, sc_n, done, kchunk,
+                                                 split_stride);
+  } else {
+    dim3 grid(ceil_div(N, 64), ceil_div(M, 64), splits);
+    dgemm_kernel<64><<<grid, 256, 0, c.stream>>>(M, N, K, A, sa_m, sa_k, B, sb_k, sb_n, C, sc_m, sc_n, done, kchunk,
+                                                 split_stride);
+  }
   c.launches++;
 }
 
@@ -96,52 +139,73 @@ __global__ void randn_kernel(double* __restrict__ Y, long long count, unsigned l
 // ---- Cholesky of the l x l Gram of the block and inverse of the factor (one CTA) -----------
 // S = R^T R (R upper).  Rinv = R^-1 so that Q = Y Rinv.  Pivots that have collapsed (columns of Y
 // linearly dependent on earlier ones: rank-deficient data) give a zero column in Rinv, i.e. the
-// direction is dropped instead of amplified.
-__global__ void __launch_bounds__(256)
-chol_inv_kernel(double* __restrict__ S, int l, double* __restrict__ Rinv, const int* __restrict__ done) {
+// direction is dropped instead of amplified.  S arrives as `splits` partial products, is summed in
+// a fixed order into shared memory (row stride l + 1), factored there, and R^-1 is built row by row
+// from the bottom (one warp per column, lanes over the inner sum).
+constexpr int kCholThreads = 256;
+
+__global__ void __launch_bounds__(kCholThreads)
+chol_inv_kernel(const double* __restrict__ Sparts, int splits, int l, double* __restrict__ Rinv,
+                const int* __restrict__ done, double* __restrict__ scratch /* used when 2 l (l+1) doubles exceed smem */) {
   if (done && *done) return;
-  const int tid = threadIdx.x;
+  extern __shared__ double csm[];
+  const int ld = l + 1;
+  double* S = scratch ? scratch : csm;   // l x ld
+  double* Ri = S + (size_t)l * ld;       // l x ld
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   __shared__ double piv;
   __shared__ double maxdiag;
-  if (tid == 0) {
+  for (int e = tid; e < l * l; e += kCholThreads) {
+    double v = 0.0;
+    for (int z = 0; z < splits; ++z) v += Sparts[(size_t)z * l * l + e];
+    const int r = e / l, cc = e - r * l;
+    S[r * ld + cc] = v;
+    Ri[r * ld + cc] = 0.0;
+  }
+  __syncthreads();
+  if (warp == 0) {
     double m = 0;
-    for (int i = 0; i < l; ++i) m = fmax(m, S[(size_t)i * l + i]);
-    maxdiag = m;
+    for (int i = lane; i < l; i += 32) m = fmax(m, S[i * ld + i]);
+    for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if (lane == 0) maxdiag = m;
   }
   __syncthreads();
   // right-looking Cholesky, upper factor stored in place (row j holds R[j][j..])
   for (int j = 0; j < l; ++j) {
     if (tid == 0) {
-      const double p = S[(size_t)j * l + j];
+      const double p = S[j * ld + j];
       piv = (p > 1e-26 * maxdiag && p > 0) ? sqrt(p) : 0.0;
     }
     __syncthreads();
     const double rjj = piv;
-    for (int c = j + tid; c < l; c += 256) S[(size_t)j * l + c] = (rjj > 0) ? S[(size_t)j * l + c] / rjj : 0.0;
-    __syncthreads();
+    const double rinv = rjj > 0 ? 1.0 / rjj : 0.0;
+    // scaled row j is needed by the update: each thread scales the entries it reads (no extra barrier),
+    // the row itself is rewritten by the threads of the first update row after the barrier below
     if (rjj > 0) {
-      const int rem = l - j - 1;
-      for (int e = tid; e < rem * rem; e += 256) {
-        const int r = j + 1 + e / rem, c = j + 1 + e % rem;
-        if (c >= r) S[(size_t)r * l + c] -= S[(size_t)j * l + r] * S[(size_t)j * l + c];
+      for (int r = j + 1 + warp; r < l; r += kCholThreads / 32) {
+        const double srj = S[j * ld + r] * rinv;
+        for (int cc = r + lane; cc < l; cc += 32) S[r * ld + cc] -= srj * (S[j * ld + cc] * rinv);
       }
+    }
+    __syncthreads();
+    for (int cc = j + tid; cc < l; cc += kCholThreads) S[j * ld + cc] = rjj > 0 ? S[j * ld + cc] * rinv : 0.0;
+  }
+  __syncthreads();
+  // R^-1 (upper), rows from the bottom: Ri[r][c] = (delta_rc - sum_{t=r+1..c} R[r][t] Ri[t][c]) / R[r][r]
+  for (int r = l - 1; r >= 0; --r) {
+    const double rrr = S[r * ld + r];
+    const double inv = rrr > 0 ? 1.0 / rrr : 0.0;
+    for (int cc = r + warp; cc < l; cc += kCholThreads / 32) {
+      double acc = 0.0;
+      for (int t = r + 1 + lane; t <= cc; t += 32) acc += S[r * ld + t] * Ri[t * ld + cc];
+      for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+      if (lane == 0) Ri[r * ld + cc] = ((r == cc ? 1.0 : 0.0) - acc) * inv;
     }
     __syncthreads();
   }
-  // Rinv (upper): column c solved independently by back substitution R x = e_c
-  for (int c = tid; c < l; c += 256) {
-    for (int r = l - 1; r >= 0; --r) {
-      double v = 0.0;
-      if (r <= c) {
-        const double rrr = S[(size_t)r * l + r];
-        if (rrr > 0) {
-          double acc = (r == c) ? 1.0 : 0.0;
-          for (int t = r + 1; t <= c; ++t) acc -= S[(size_t)r * l + t] * Rinv[(size_t)t * l + c];
-          v = acc / rrr;
-        }
-      }
-      Rinv[(size_t)r * l + c] = v;
-    }
+  for (int e = tid; e < l * l; e += kCholThreads) {
+    const int r = e / l, cc = e - r * l;
+    Rinv[e] = Ri[r * ld + cc];
   }
 }
 
@@ -150,21 +214,24 @@ __global__ void __launch_bounds__(256)
 ritz_check_kernel(const double* __restrict__ Q, const double* __restrict__ Y, int d, int l, int k,
                   double* __restrict__ theta_prev, double tol, int* __restrict__ done, int iter) {
   if (*done) return;
-  __shared__ double red[256];
   __shared__ int bad;
   if (threadIdx.x == 0) bad = 0;
   __syncthreads();
-  for (int j = 0; j < k; ++j) {
+  // a thread walks one column (consecutive threads: consecutive columns, coalesced), 256 / kc row slices
+  const int kc = k <= 32 ? 32 : (k <= 64 ? 64 : (k <= 128 ? 128 : 256));
+  const int slices = 256 / kc;
+  __shared__ double part[256];
+  for (int j0 = 0; j0 < k; j0 += kc) {
+    const int j = j0 + (int)(threadIdx.x % kc), sl = threadIdx.x / kc;
     double acc = 0;
-    for (int r = threadIdx.x; r < d; r += 256) acc += Q[(size_t)r * l + j] * Y[(size_t)r * l + j];
-    red[threadIdx.x] = acc;
+    if (j < k)
+      for (int r = sl; r < d; r += slices) acc += Q[(size_t)r * l + j] * Y[(size_t)r * l + j];
+    part[threadIdx.x] = acc;
     __syncthreads();
-    for (int o = 128; o > 0; o >>= 1) {
-      if (threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o];
-      __syncthreads();
-    }
-    if (threadIdx.x == 0) {
-      const double th = red[0], pr = theta_prev[j];
+    if (sl == 0 && j < k) {
+      double th = 0;
+      for (int q = 0; q < slices; ++q) th += part[q * kc + (threadIdx.x % kc)];
+      const double pr = theta_prev[j];
       if (iter == 0 || !(fabs(th - pr) <= tol * fabs(pr))) bad = 1;
       theta_prev[j] = th;
     }
@@ -175,61 +242,72 @@ ritz_check_kernel(const double* __restrict__ Q, const double* __restrict__ Y, in
 
 }  // namespace
 
+constexpr int kSplits = 16;                      // partial products of S = Y^T Y
+constexpr size_t kCholSmemMax = 200 * 1024;
+
 struct PowerWs {
-  double *Y, *Z, *Q, *S, *Rinv, *theta, *jac_A, *jac_V;
-  void* jac_ws;
+  double *Y, *Z, *Q, *S, *Rinv, *theta, *chol_scratch, *B, *Wl, *Vl;
+  void* eig_ws;
   int* done;
-  int lp;
 };
 
 static size_t r256(size_t b) { return (b + 255) / 256 * 256; }
+static size_t chol_bytes(int l) { return (size_t)2 * l * (l + 1) * 8; }
 
 static PowerWs carve(void* workspace, int d, int l) {
   PowerWs w;
   char* p = static_cast<char*>(workspace);
   auto take = [&](size_t bytes) { void* r = p; p += r256(bytes); return r; };
-  w.lp = jacobi_padded_dim(l);
   w.Y = (double*)take((size_t)d * l * 8);
   w.Z = (double*)take((size_t)d * l * 8);
   w.Q = (double*)take((size_t)d * l * 8);
-  w.S = (double*)take((size_t)l * l * 8);
+  w.S = (double*)take((size_t)kSplits * l * l * 8);
   w.Rinv = (double*)take((size_t)l * l * 8);
   w.theta = (double*)take((size_t)l * 8);
-  w.jac_A = (double*)take((size_t)w.lp * w.lp * 8);
-  w.jac_V = (double*)take((size_t)w.lp * w.lp * 8);
-  w.jac_ws = take(jacobi_workspace_bytes(w.lp));
+  w.chol_scratch = chol_bytes(l) > kCholSmemMax ? (double*)take(chol_bytes(l)) : nullptr;
+  w.B = (double*)take((size_t)l * l * 8);
+  w.Wl = (double*)take((size_t)l * 8);
+  w.Vl = (double*)take((size_t)l * l * 8);
+  w.eig_ws = take(eigh_topk_workspace_bytes(l, l));
   w.done = (int*)take(256);
   return w;
 }
 
 size_t power_workspace_bytes(int d, int l) {
-  const int lp = jacobi_padded_dim(l);
-  return 3 * r256((size_t)d * l * 8) + 2 * r256((size_t)l * l * 8) + r256((size_t)l * 8) +
-         2 * r256((size_t)lp * lp * 8) + r256(jacobi_workspace_bytes(lp)) + 256 + 256;
+  return 3 * r256((size_t)d * l * 8) + r256((size_t)kSplits * l * l * 8) + 3 * r256((size_t)l * l * 8) +
+         2 * r256((size_t)l * 8) + (chol_bytes(l) > kCholSmemMax ? r256(chol_bytes(l)) : 0) +
+         r256(eigh_topk_workspace_bytes(l, l)) + 256 + 256;
 }
 
-int power_padded_block(int l) { return jacobi_padded_dim(l); }
+int power_padded_block(int l) { return l; }
 
 // Q = orth(Y) by CholeskyQR2: Y -> Z -> Q.  Every launch is guarded by `done` (may be null).
 static void cholqr2(Ctx& c, PowerWs& w, int d, int l, const int* done) {
+  const size_t smem = w.chol_scratch ? 0 : chol_bytes(l);
+  static size_t smem_set = 0;
+  if (smem > 48 * 1024 && smem > smem_set) {
+    DR4G_CUDA(cudaFuncSetAttribute(chol_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    smem_set = smem;
+  }
+  const int splits = std::max(1, std::min(kSplits, d / 64));
   for (int pass = 0; pass < 2; ++pass) {
     const double* src = pass == 0 ? w.Y : w.Z;
     double* dst = pass == 0 ? w.Z : w.Q;
-    dgemm(c, l, l, d, src, 1, l, src, l, 1, w.S, l, 1, done);      // S = src^T src
-    chol_inv_kernel<<<1, 256, 0, c.stream>>>(w.S, l, w.Rinv, done);
+    dgemm(c, l, l, d, src, 1, l, src, l, 1, w.S, l, 1, done, splits, (long long)l * l);  // S = src^T src (partials)
+    chol_inv_kernel<<<1, kCholThreads, smem, c.stream>>>(w.S, splits, l, w.Rinv, done, w.chol_scratch);
     c.launches++;
     dgemm(c, d, l, l, src, l, 1, w.Rinv, l, 1, dst, l, 1, done);   // dst = src Rinv
   }
 }
 
-__global__ void symmetrize_pad_kernel(const double* __restrict__ B, int l, double* __restrict__ A, int lp) {
+__global__ void symmetrize_kernel(const double* __restrict__ B, int l, double* __restrict__ A) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y;
-  if (c >= lp) return;
-  A[(size_t)r * lp + c] = (r < l && c < l) ? 0.5 * (B[(size_t)r * l + c] + B[(size_t)c * l + r]) : 0.0;
+  if (c >= l) return;
+  A[(size_t)r * l + c] = 0.5 * (B[(size_t)r * l + c] + B[(size_t)c * l + r]);
 }
 
 void launch_power(Ctx& c, const double* dC, int d, int k, int l, int n_iter, double tol, int seed,
-                  double* dW_out /* lp */, double* dVt_out /* lp x d */, void* workspace) {
+                  double* dW_out /* l */, double* dVt_out /* l x d */, void* workspace) {
   PowerWs w = carve(workspace, d, l);
   DR4G_CUDA(cudaMemsetAsync(w.done, 0, 256, c.stream));
   DR4G_CUDA(cudaMemsetAsync(w.theta, 0, (size_t)l * 8, c.stream));
@@ -244,17 +322,17 @@ void launch_power(Ctx& c, const double* dC, int d, int k, int l, int n_iter, dou
     c.launches++;
     cholqr2(c, w, d, l, w.done);                                 // Q = orth(Y) unless converged
   }
-  // Rayleigh-Ritz on span(Q)
+  // Rayleigh-Ritz on span(Q): B = Q^T C Q (l x l), all l eigenpairs by the tridiagonal solver (K4)
   dgemm(c, d, l, d, dC, d, 1, w.Q, l, 1, w.Y, l, 1, nullptr);      // Y = C Q
   dgemm(c, l, l, d, w.Q, 1, l, w.Y, l, 1, w.S, l, 1, nullptr);     // S = Q^T Y
   {
-    dim3 grid(ceil_div(w.lp, 128), w.lp);
-    symmetrize_pad_kernel<<<grid, 128, 0, c.stream>>>(w.S, l, w.jac_A, w.lp);
+    dim3 grid(ceil_div(l, 128), l);
+    symmetrize_kernel<<<grid, 128, 0, c.stream>>>(w.S, l, w.B);
     c.launches++;
   }
-  launch_jacobi(c, w.jac_A, w.jac_V, w.lp, dW_out, w.jac_ws, 1e-14, 30);
-  // Ritz vectors as rows: Vt[j][col] = sum_i Vl[i][j] Q[col][i]
-  dgemm(c, w.lp, d, l, w.jac_V, 1, w.lp, w.Q, 1, l, dVt_out, d, 1, nullptr);
+  launch_eigh_topk(c, w.B, l, l, dW_out, w.Vl, w.eig_ws);          // Vl rows = eigenvectors of B, descending
+  // Ritz vectors as rows: Vt[j][col] = sum_i Vl[j][i] Q[col][i]
+  dgemm(c, l, d, l, w.Vl, l, 1, w.Q, 1, l, dVt_out, d, 1, nullptr);
   DR4G_CUDA(cudaGetLastError());
 }
 
