@@ -20,19 +20,21 @@ namespace {
 // key_j = lambda_j, or -DBL_MAX for eigenvectors that live in the zero padding
 __global__ void keys_kernel(const double* __restrict__ W, int nw, const double* __restrict__ V, int ldv,
                             bool vectors_in_rows, bool check_mass, int d, double* __restrict__ keys) {
-  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  // one warp per eigenpair
+  const int j = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (j >= nw) return;
   double key = W[j];
   if (check_mass) {
     double mass = 0;
-    for (int r = 0; r < d; ++r) {
+    for (int r = lane; r < d; r += 32) {
       const double v = vectors_in_rows ? V[(size_t)j * ldv + r] : V[(size_t)r * ldv + j];
       mass += v * v;
     }
+    for (int o = 16; o > 0; o >>= 1) mass += __shfl_xor_sync(0xffffffffu, mass, o);
     if (mass < 0.5) key = -DBL_MAX;
   }
   if (!(key == key)) key = -DBL_MAX;  // NaN guard
-  keys[j] = key;
+  if (lane == 0) keys[j] = key;
 }
 
 __global__ void rank_kernel(const double* __restrict__ keys, int nw, int k, int* __restrict__ sel) {
@@ -105,7 +107,7 @@ void launch_postproc(Ctx& c, const double* dW, int nw, const double* dV, int ldv
                      T* dQ, T* dw, T* dev, T* devr, T* dmean) {
   double* keys = c.arena.take_n<double>(nw);
   int* sel = c.arena.take_n<int>(k);
-  keys_kernel<<<ceil_div(nw, 128), 128, 0, c.stream>>>(dW, nw, dV, ldv, vectors_in_rows, check_mass, d, keys);
+  keys_kernel<<<ceil_div(nw, 4), 128, 0, c.stream>>>(dW, nw, dV, ldv, vectors_in_rows, check_mass, d, keys);
   rank_kernel<<<ceil_div(nw, 128), 128, 0, c.stream>>>(keys, nw, k, sel);
   gather_kernel<T><<<k, 256, 0, c.stream>>>(keys, sel, dV, ldv, vectors_in_rows, d, k, packed_n, dtotal_var,
                                             dmean_d, dQ, dw, dev, devr, dmean);

@@ -14,6 +14,7 @@
 //   Q0 = orth(randn(d, l));  repeat: Y = C Q;  theta_j = q_j . y_j;  Q = orth(Y)
 //   B = Q^T C Q;  B = W diag(lambda) W^T (K4 tridiagonal solver, all l pairs);  Ritz vectors = Q W
 #include <algorithm>
+#include <cstdlib>
 
 #include "common.cuh"
 
@@ -27,6 +28,7 @@ namespace {
 // buffers), and a long contraction with a tiny output (S = Y^T Y) is split over blockIdx.z into
 // partial products that the consumer (chol_inv_kernel) adds up in a fixed order.
 constexpr int GK = 16;
+constexpr int kSplits = 16;  // partial products of S = Y^T Y (split contraction)
 
 template <int TM>
 __global__ void __launch_bounds__(256)
@@ -209,18 +211,183 @@ chol_inv_kernel(const double* __restrict__ Sparts, int splits, int l, double* __
   }
 }
 
-// theta_j = q_j . y_j ; convergence of the leading k Ritz estimates against the previous iteration
+// 1 / sqrt(p) for normal positive p: exponent folded to [1, 4), fp32 estimate, two Newton steps in fp64
+// (~9 dependent fp64 operations instead of the ~60 of sqrt() followed by a division; dependent fp64
+// latency is what the factorisation's pivot chain is made of).  Relative error ~2e-16.
+__device__ __forceinline__ double fast_rsqrt(double p) {
+  const long long bits = __double_as_longlong(p);
+  const int e2 = (int)(((bits >> 52) & 0x7ff) - 1023) & ~1;          // even, <= exponent
+  const double m = __longlong_as_double(bits - ((long long)e2 << 52));  // [1, 4)
+  double y = (double)rsqrtf((float)m);
+  const double hm = 0.5 * m;
+  y = y * fma(-hm * y, y, 1.5);
+  y = y * fma(-hm * y, y, 1.5);
+  return y * __longlong_as_double((long long)(1023 - e2 / 2) << 52);
+}
+
+__device__ long long g_chol_trace[16];  // DR4G_CHOL_TRACE=1: phase time stamps of thread 0
+
+// sum of the split-contraction partial products (many CTAs: all loads of an element in flight at once)
 __global__ void __launch_bounds__(256)
+sum_partials_kernel(const double* __restrict__ parts, int splits, int count, double* __restrict__ out,
+                    const int* __restrict__ done) {
+  if (done && *done) return;
+  const int e = blockIdx.x * 256 + threadIdx.x;
+  if (e >= count) return;
+  double part[kSplits];
+#pragma unroll
+  for (int z = 0; z < kSplits; ++z) part[z] = z < splits ? parts[(size_t)z * count + e] : 0.0;
+  double acc = 0.0;
+#pragma unroll
+  for (int z = 0; z < kSplits; ++z) acc += part[z];
+  out[e] = acc;
+}
+
+// Register-resident variant for l <= min(8 P, 32 Q): thread (warp w, lane) keeps the elements (w + 8 p, lane + 32 q)
+// of the trailing matrix in registers for the whole factorisation; only the pivot row goes through shared memory
+// (two buffers, one barrier per step).  Row tests are warp-uniform (real branches, finished rows cost nothing),
+// column tests are predicates, indices are compile-time offsets: ~60 instructions per warp and step.  (A first
+// version with a flat element map spent 1100 instructions per step on index unpacking and selects, and one with
+// a branch per element 3300 cycles of exposed latency; the shared-memory kernel above ~250 us at l = 74.)
+// R^-1 is then solved two lanes per column, columns private to their lanes (no block barriers).
+template <int P, int Q>
+__global__ void __launch_bounds__(kCholThreads)
+chol_inv_reg_kernel(const double* __restrict__ S, int l, double* __restrict__ Rinv, const int* __restrict__ done,
+                    int trace) {
+  if (done && *done) return;
+  extern __shared__ double csm[];
+  const int ld = l + 1;
+  double* R = csm;                        // l x ld, upper factor
+  double* Ri = R + (size_t)l * ld;        // l x ld, upper inverse
+  double* rowj = Ri + (size_t)l * ld;     // 2 x 32 Q pivot-row buffers (zero beyond l)
+  double* rinvs = rowj + 2 * 32 * Q;      // l reciprocal pivots
+  __shared__ double maxdiag_s;
+  __shared__ double pivs[2];              // reciprocal pivot per row buffer
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const bool tr = trace && tid == 0;
+  if (tr) g_chol_trace[0] = clock64();
+  double v[P][Q];
+  double dmax = 0.0;
+  for (int e = tid; e < 2 * 32 * Q; e += kCholThreads) rowj[e] = 0.0;
+#pragma unroll
+  for (int p = 0; p < P; ++p)
+#pragma unroll
+    for (int q = 0; q < Q; ++q) {
+      const int r = warp + 8 * p, cc = lane + 32 * q;
+      const bool in = r < l && cc < l;
+      v[p][q] = (in && cc >= r) ? S[r * l + cc] : 0.0;   // only the upper triangle is used
+      if (in && cc == r) dmax = fmax(dmax, v[p][q]);
+      if (in && cc < r) Rinv[r * l + cc] = 0.0;          // the inverse is upper triangular
+    }
+  for (int o = 16; o > 0; o >>= 1) dmax = fmax(dmax, __shfl_xor_sync(0xffffffffu, dmax, o));
+  if (tid == 0) maxdiag_s = 0.0;
+  __syncthreads();
+  if (lane == 0 && dmax > 0) atomicMax(reinterpret_cast<unsigned long long*>(&maxdiag_s), (unsigned long long)__double_as_longlong(dmax));
+  __syncthreads();
+  if (tr) g_chol_trace[1] = clock64();
+  const double thr = 1e-26 * maxdiag_s;
+  auto publish_pivot = [&](int buf, double pv) { pivs[buf] = (pv > thr && pv > 1e-290) ? fast_rsqrt(pv) : 0.0; };
+  if (warp == 0) {
+#pragma unroll
+    for (int q = 0; q < Q; ++q) {
+      const int cc = lane + 32 * q;
+      if (cc < l) rowj[cc] = v[0][q];
+    }
+    if (lane == 0) publish_pivot(0, v[0][0]);
+  }
+  __syncthreads();
+  // step j: R[j][j..] = S[j][j..] / r_jj, trailing S[r][c] -= R[j][r] R[j][c].  The step is a latency chain
+  // (barrier -> pivot row -> update of row j+1 -> its rsqrt -> barrier): all shared-memory operands are
+  // fetched up front, row j+1 is updated and published first, the other rows follow branch-free.
+  // Measured at l = 74 (B200, trace hook): 1460 cycles per step = ~200 dependent instructions of one warp
+  // (operands 190, row update through the unrolled owner test 600, rsqrt + publication 520, barrier 100);
+  // a panel-blocked factorisation (one barrier per 8 columns) is the next step if this ever matters.
+  for (int j = 0; j < l; ++j) {
+    const double* rj = rowj + (j & 1) * (32 * Q);
+    double* rnext = rowj + ((j + 1) & 1) * (32 * Q);
+    const double rinv = pivs[j & 1];
+    double b[Q], a[P];
+#pragma unroll
+    for (int q = 0; q < Q; ++q) b[q] = rj[lane + 32 * q] * rinv;   // entries below j are stale but finite and unused
+#pragma unroll
+    for (int p = 0; p < P; ++p) a[p] = rj[warp + 8 * p] * rinv;     // zero beyond l
+    // row j+1 (one warp, warp-uniform test)
+    if (((j + 1) & 7) == warp && j + 1 < l) {
+      double nx[Q];
+#pragma unroll
+      for (int p = 0; p < P; ++p)
+        if (warp + 8 * p == j + 1) {
+#pragma unroll
+          for (int q = 0; q < Q; ++q) {
+            if (lane + 32 * q >= j + 1) v[p][q] = fma(-a[p], b[q], v[p][q]);
+            nx[q] = v[p][q];
+          }
+        }
+#pragma unroll
+      for (int q = 0; q < Q; ++q) {
+        const int cc = lane + 32 * q;
+        if (cc >= j + 1 && cc < l) rnext[cc] = nx[q];
+        if (cc == j + 1) publish_pivot((j + 1) & 1, nx[q]);
+      }
+    }
+    // rows below j+1
+#pragma unroll
+    for (int p = 0; p < P; ++p) {
+      const int r = warp + 8 * p;
+      const bool act = r > j + 1;
+#pragma unroll
+      for (int q = 0; q < Q; ++q) {
+        const double nv = fma(-a[p], b[q], v[p][q]);
+        v[p][q] = (act && lane + 32 * q >= r) ? nv : v[p][q];
+      }
+    }
+    // row j of the factor
+    if ((j & 7) == warp) {
+#pragma unroll
+      for (int q = 0; q < Q; ++q) {
+        const int cc = lane + 32 * q;
+        if (cc >= j && cc < l) R[j * ld + cc] = b[q];
+        if (cc == j) rinvs[j] = rinv;
+      }
+    }
+    __syncthreads();
+  }
+  if (tr) g_chol_trace[2] = clock64();
+  // R^-1 (upper): two lanes per column cc, from the diagonal upwards:
+  // Ri[r][c] = (delta_rc - sum_{t=r+1..c} R[r][t] Ri[t][c]) / R[r][r], with 1 / R[r][r] kept from the factorisation.
+  // All lanes of a warp walk the same rows (those above their column idle) so that the shuffles are warp-uniform.
+  if ((tid & ~31) < 2 * l) {
+    const int cc = tid < 2 * l ? tid >> 1 : -1, h = tid & 1;
+    const int rtop = min(l - 1, ((tid & ~31) + 31) >> 1);
+    for (int r = rtop; r >= 0; --r) {
+      double acc = 0.0;
+      for (int t = r + 1 + h; t <= cc; t += 2) acc = fma(R[r * ld + t], Ri[t * ld + cc], acc);
+      acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+      if (h == 0 && r <= cc) {
+        const double val = ((r == cc ? 1.0 : 0.0) - acc) * rinvs[r];   // rinvs[r] = 0 for a dropped pivot
+        Ri[r * ld + cc] = val;
+        Rinv[r * l + cc] = val;
+      }
+      __syncwarp();
+    }
+  }
+  if (tr) g_chol_trace[3] = clock64();
+}
+
+// theta_j = q_j . y_j ; convergence of the leading k Ritz estimates against the previous iteration
+constexpr int kRitzThreads = 1024;
+
+__global__ void __launch_bounds__(kRitzThreads)
 ritz_check_kernel(const double* __restrict__ Q, const double* __restrict__ Y, int d, int l, int k,
                   double* __restrict__ theta_prev, double tol, int* __restrict__ done, int iter) {
   if (*done) return;
   __shared__ int bad;
   if (threadIdx.x == 0) bad = 0;
   __syncthreads();
-  // a thread walks one column (consecutive threads: consecutive columns, coalesced), 256 / kc row slices
+  // a thread walks one column (consecutive threads: consecutive columns, coalesced), kRitzThreads / kc row slices
   const int kc = k <= 32 ? 32 : (k <= 64 ? 64 : (k <= 128 ? 128 : 256));
-  const int slices = 256 / kc;
-  __shared__ double part[256];
+  const int slices = kRitzThreads / kc;
+  __shared__ double part[kRitzThreads];
   for (int j0 = 0; j0 < k; j0 += kc) {
     const int j = j0 + (int)(threadIdx.x % kc), sl = threadIdx.x / kc;
     double acc = 0;
@@ -242,11 +409,10 @@ ritz_check_kernel(const double* __restrict__ Q, const double* __restrict__ Y, in
 
 }  // namespace
 
-constexpr int kSplits = 16;                      // partial products of S = Y^T Y
 constexpr size_t kCholSmemMax = 200 * 1024;
 
 struct PowerWs {
-  double *Y, *Z, *Q, *S, *Rinv, *theta, *chol_scratch, *B, *Wl, *Vl;
+  double *Y, *Z, *Q, *S, *Ssum, *Rinv, *theta, *chol_scratch, *B, *Wl, *Vl;
   void* eig_ws;
   int* done;
 };
@@ -262,6 +428,7 @@ static PowerWs carve(void* workspace, int d, int l) {
   w.Z = (double*)take((size_t)d * l * 8);
   w.Q = (double*)take((size_t)d * l * 8);
   w.S = (double*)take((size_t)kSplits * l * l * 8);
+  w.Ssum = (double*)take((size_t)l * l * 8);
   w.Rinv = (double*)take((size_t)l * l * 8);
   w.theta = (double*)take((size_t)l * 8);
   w.chol_scratch = chol_bytes(l) > kCholSmemMax ? (double*)take(chol_bytes(l)) : nullptr;
@@ -274,7 +441,7 @@ static PowerWs carve(void* workspace, int d, int l) {
 }
 
 size_t power_workspace_bytes(int d, int l) {
-  return 3 * r256((size_t)d * l * 8) + r256((size_t)kSplits * l * l * 8) + 3 * r256((size_t)l * l * 8) +
+  return 3 * r256((size_t)d * l * 8) + r256((size_t)kSplits * l * l * 8) + 4 * r256((size_t)l * l * 8) +
          2 * r256((size_t)l * 8) + (chol_bytes(l) > kCholSmemMax ? r256(chol_bytes(l)) : 0) +
          r256(eigh_topk_workspace_bytes(l, l)) + 256 + 256;
 }
@@ -283,18 +450,36 @@ int power_padded_block(int l) { return l; }
 
 // Q = orth(Y) by CholeskyQR2: Y -> Z -> Q.  Every launch is guarded by `done` (may be null).
 static void cholqr2(Ctx& c, PowerWs& w, int d, int l, const int* done) {
-  const size_t smem = w.chol_scratch ? 0 : chol_bytes(l);
-  static size_t smem_set = 0;
-  if (smem > 48 * 1024 && smem > smem_set) {
-    DR4G_CUDA(cudaFuncSetAttribute(chol_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    smem_set = smem;
+  constexpr int kRegP = 10, kRegQ = 3;           // register-resident factorisation up to l = 80
+  const bool reg = l <= 8 * kRegP && l <= 32 * kRegQ;
+  const size_t smem = reg ? chol_bytes(l) + (size_t)(2 * 32 * kRegQ + l) * 8 : (w.chol_scratch ? 0 : chol_bytes(l));
+  static size_t smem_set[2] = {0, 0};
+  if (smem > 48 * 1024 && smem > smem_set[reg]) {
+    if (reg) DR4G_CUDA(cudaFuncSetAttribute(chol_inv_reg_kernel<kRegP, kRegQ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    else DR4G_CUDA(cudaFuncSetAttribute(chol_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    smem_set[reg] = smem;
   }
   const int splits = std::max(1, std::min(kSplits, d / 64));
   for (int pass = 0; pass < 2; ++pass) {
     const double* src = pass == 0 ? w.Y : w.Z;
     double* dst = pass == 0 ? w.Z : w.Q;
     dgemm(c, l, l, d, src, 1, l, src, l, 1, w.S, l, 1, done, splits, (long long)l * l);  // S = src^T src (partials)
-    chol_inv_kernel<<<1, kCholThreads, smem, c.stream>>>(w.S, splits, l, w.Rinv, done, w.chol_scratch);
+    static const int trace = getenv("DR4G_CHOL_TRACE") ? atoi(getenv("DR4G_CHOL_TRACE")) : 0;
+    if (reg) {
+      sum_partials_kernel<<<ceil_div(l * l, 256), 256, 0, c.stream>>>(w.S, splits, l * l, w.Ssum, done);
+      c.launches++;
+      chol_inv_reg_kernel<kRegP, kRegQ><<<1, kCholThreads, smem, c.stream>>>(w.Ssum, l, w.Rinv, done, trace);
+      static int printed = 0;
+      if (trace && printed < 4) {
+        long long h[16];
+        DR4G_CUDA(cudaStreamSynchronize(c.stream));
+        DR4G_CUDA(cudaMemcpyFromSymbol(h, g_chol_trace, sizeof(h)));
+        fprintf(stderr, "chol trace l=%d (cycles, thread 0): load %lld, factor %lld, inverse (column 0 only) %lld\n", l,
+                h[1] - h[0], h[2] - h[1], h[3] - h[2]);
+        ++printed;
+      }
+    }
+    else chol_inv_kernel<<<1, kCholThreads, smem, c.stream>>>(w.S, splits, l, w.Rinv, done, w.chol_scratch);
     c.launches++;
     dgemm(c, d, l, l, src, l, 1, w.Rinv, l, 1, dst, l, 1, done);   // dst = src Rinv
   }
@@ -318,7 +503,7 @@ void launch_power(Ctx& c, const double* dC, int d, int k, int l, int n_iter, dou
   if (n_iter < 1) n_iter = 1;
   for (int it = 0; it < n_iter; ++it) {
     dgemm(c, d, l, d, dC, d, 1, w.Q, l, 1, w.Y, l, 1, w.done);   // Y = C Q
-    ritz_check_kernel<<<1, 256, 0, c.stream>>>(w.Q, w.Y, d, l, k, w.theta, tol, w.done, it);
+    ritz_check_kernel<<<1, kRitzThreads, 0, c.stream>>>(w.Q, w.Y, d, l, k, w.theta, tol, w.done, it);
     c.launches++;
     cholqr2(c, w, d, l, w.done);                                 // Q = orth(Y) unless converged
   }
