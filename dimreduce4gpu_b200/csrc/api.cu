@@ -89,9 +89,30 @@ struct DeviceGuard {
   }
 };
 
+// Streaming (out-of-core) fit, SURVEY 8f-1: [G | s | q | n] of (x - shift) accumulated over row chunks.
+// The shift is fixed by the first chunk (it has to be the same for every chunk and every rank).
+struct StreamFit {
+  double* acc = nullptr;      // packed accumulators, d*d + 2d + 1 doubles
+  double* shift_d = nullptr;  // d doubles
+  void* shift_t = nullptr;    // d elements of the input type
+  int d = 0, center = 0, elem = 0;
+  long long rows = 0;         // rows accumulated on this rank
+  void release() {
+    if (acc) cudaFree(acc);
+    if (shift_d) cudaFree(shift_d);
+    if (shift_t) cudaFree(shift_t);
+    acc = shift_d = nullptr;
+    shift_t = nullptr;
+    d = center = elem = 0;
+    rows = 0;
+  }
+};
+
 struct CtxFull : Ctx {
   std::mutex mu;
   Arena io;  // device copies of inputs/outputs for the legacy host-pointer symbols
+  StreamFit sf;
+  cudaStream_t copy_stream = nullptr, out_stream = nullptr;  // H2D / D2H of the out-of-core legacy path
 };
 
 static CtxFull* ctx_new(int device) {
@@ -123,6 +144,9 @@ static void ctx_delete(CtxFull* c) {
   for (auto& ev : c->stage_ev) if (ev) cudaEventDestroy(ev);
   c->arena.release();
   c->io.release();
+  c->sf.release();
+  if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+  if (c->out_stream) cudaStreamDestroy(c->out_stream);
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
   delete c;
 }
@@ -157,7 +181,9 @@ constexpr int kOversample = 10;  // same block oversampling as the CPU backend's
 
 template <typename T>
 static void fit_impl(Ctx& c, const T* dX, long long n_local, int d, int k, int center, const params& p, T* dQ,
-                     T* dw, T* dev, T* devr, T* dmean) {
+                     T* dw, T* dev, T* devr, T* dmean, StreamFit* sf = nullptr, int phase = 0) {
+  // phase 0: whole fit.  phase 1 (sf): pilot shift on the first chunk, pass over this chunk, sf->acc += result.
+  // phase 2 (sf): no pass, the accumulated [G|s|q|n] goes through the exchange, eigensolve and outputs.
   if (d <= 0 || k <= 0 || n_local < 0) fail("fit: bad shape n_local=%lld d=%d k=%d", n_local, d, k);
   if (k > d) k = d;
   const bool exact = is_exact(p);
@@ -194,6 +220,10 @@ static void fit_impl(Ctx& c, const T* dX, long long n_local, int d, int k, int c
   double* pilot = c.arena.take_n<double>((size_t)d + 1);
   double* shift_d = c.arena.take_n<double>(d);
   T* shift_t = c.arena.take_n<T>(d);
+  if (sf) {
+    shift_d = sf->shift_d;
+    shift_t = static_cast<T*>(sf->shift_t);
+  }
   double* mean_d = c.arena.take_n<double>(d);
   double* total_var = c.arena.take_n<double>(1);
 
@@ -206,7 +236,12 @@ static void fit_impl(Ctx& c, const T* dX, long long n_local, int d, int k, int c
   // ranks, hence the (d+1)-element allreduce before the pass.
   const T* shift_arg = nullptr;
   const double* shift_d_arg = nullptr;
-  if (center) {
+  if (center && sf && !(phase == 1 && sf->rows == 0)) {
+    // streaming: the shift of the first chunk stays in force
+    if constexpr (sizeof(T) == 8) shift_arg = reinterpret_cast<const T*>(shift_d);
+    else shift_arg = shift_t;
+    shift_d_arg = shift_d;
+  } else if (center) {
     long long rows = n_local < c.pilot_rows ? n_local : c.pilot_rows;
     DR4G_CUDA(cudaMemsetAsync(pilot, 0, ((size_t)d + 1) * 8, c.stream));
     DR4G_CUDA(cudaMemsetAsync(shift_d, 0, (size_t)d * 8, c.stream));
@@ -224,6 +259,9 @@ static void fit_impl(Ctx& c, const T* dX, long long n_local, int d, int k, int c
   mark(1);
 
   // [1] the streamed pass
+  if (phase == 2) {
+    DR4G_CUDA(cudaMemcpyAsync(packed, sf->acc, packed_count * 8, cudaMemcpyDeviceToDevice, c.stream));
+  } else {
   DR4G_CUDA(cudaMemsetAsync(packed, 0, packed_count * 8, c.stream));
   bool used_tc = false;
   if constexpr (sizeof(T) == 4) {
@@ -243,6 +281,12 @@ static void fit_impl(Ctx& c, const T* dX, long long n_local, int d, int k, int c
   }
   c.last_gram_path = used_tc ? (c.last_gram_kernel == 2 ? 3 : 2) : 1;
   launch_set_scalar(c, cnt, (double)n_local);
+  }
+  if (phase == 1) {
+    launch_add_f64(c, sf->acc, packed, packed_count);
+    sf->rows += n_local;
+    return;
+  }
   mark(2);
 
   // [2] combine ranks, centre
@@ -286,6 +330,132 @@ static void fit_impl(Ctx& c, const T* dX, long long n_local, int d, int k, int c
   c.stage_valid = timing;
 }
 
+// ---------------------------------------------------------------- streaming fit
+template <typename T>
+static void partial_fit_impl(CtxFull& c, const T* dX, long long n, int d, int center) {
+  if (d <= 0 || n < 0) fail("partial_fit: bad shape n=%lld d=%d", n, d);
+  StreamFit& sf = c.sf;
+  if (!sf.acc) {
+    const size_t count = (size_t)d * d + 2 * (size_t)d + 1;
+    DR4G_CUDA(cudaMalloc(&sf.acc, count * 8));
+    DR4G_CUDA(cudaMalloc(&sf.shift_d, (size_t)d * 8));
+    DR4G_CUDA(cudaMalloc(&sf.shift_t, (size_t)d * 8));
+    DR4G_CUDA(cudaMemsetAsync(sf.acc, 0, count * 8, c.stream));
+    DR4G_CUDA(cudaMemsetAsync(sf.shift_d, 0, (size_t)d * 8, c.stream));
+    DR4G_CUDA(cudaMemsetAsync(sf.shift_t, 0, (size_t)d * 8, c.stream));
+    sf.d = d;
+    sf.center = center;
+    sf.elem = (int)sizeof(T);
+    sf.rows = 0;
+  } else if (sf.d != d || sf.center != center || sf.elem != (int)sizeof(T)) {
+    fail("partial_fit: chunk (d=%d center=%d %d-byte elements) does not match the accumulated state (d=%d center=%d %d-byte); "
+         "call dr4g_partial_fit_reset first", d, center, (int)sizeof(T), sf.d, sf.center, sf.elem);
+  }
+  if (n == 0) return;
+  params p{};
+  p.algorithm = const_cast<char*>("cusolver");
+  fit_impl<T>(c, dX, n, d, 1, center, p, nullptr, nullptr, nullptr, nullptr, nullptr, &sf, 1);
+}
+
+template <typename T>
+static void partial_fit_finalize_impl(CtxFull& c, int k, const params& p, T* dQ, T* dw, T* dev, T* devr, T* dmean) {
+  StreamFit& sf = c.sf;
+  if (!sf.acc || sf.elem != (int)sizeof(T)) fail("partial_fit_finalize: nothing accumulated for this element type");
+  if (sf.rows <= 0 && c.world <= 1) fail("partial_fit_finalize: no rows accumulated");
+  fit_impl<T>(c, nullptr, sf.rows, sf.d, k, sf.center, p, dQ, dw, dev, devr, dmean, &sf, 2);
+}
+
+// Two sweeps over a host-resident X in row chunks: [1] H2D (copy stream) overlapped with the chunk's Gram pass
+// (partial fit), then the eigensolve; [2] H2D again, projection, D2H of the scores (third stream), all three
+// overlapped through two chunk buffers.  Device footprint: 2 chunks of X and of the two score matrices.
+template <typename T>
+static void legacy_out_of_core(CtxFull& c, bool is_pca, const T* X, long long n, int d, int k, long long chunk,
+                               const params& p, T* Q, T* w, T* U, T* Xt, T* ev, T* evr, T* mean) {
+  if (!c.copy_stream) DR4G_CUDA(cudaStreamCreateWithFlags(&c.copy_stream, cudaStreamNonBlocking));
+  if (!c.out_stream) DR4G_CUDA(cudaStreamCreateWithFlags(&c.out_stream, cudaStreamNonBlocking));
+  const size_t cx = (size_t)chunk * d * sizeof(T), cz = (size_t)chunk * k * sizeof(T);
+  c.io.reserve(2 * up256(cx) + 4 * up256(cz) + up256((size_t)k * d * sizeof(T)) + 3 * up256((size_t)k * sizeof(T)) +
+               up256((size_t)d * sizeof(T)) + 4096);
+  c.io.reset();
+  T* dQ = c.io.take_n<T>((size_t)k * d);
+  T* dw = c.io.take_n<T>(k);
+  T* dev = c.io.take_n<T>(k);
+  T* devr = c.io.take_n<T>(k);
+  T* dmean = c.io.take_n<T>(d);
+  T* xb[2] = {c.io.take_n<T>((size_t)chunk * d), c.io.take_n<T>((size_t)chunk * d)};
+  T* zb[2] = {c.io.take_n<T>((size_t)chunk * k), c.io.take_n<T>((size_t)chunk * k)};
+  T* ub[2] = {c.io.take_n<T>((size_t)chunk * k), c.io.take_n<T>((size_t)chunk * k)};
+  cudaEvent_t loaded[2], xfree[2], projected[2], zfree[2];
+  for (int b = 0; b < 2; ++b) {
+    DR4G_CUDA(cudaEventCreateWithFlags(&loaded[b], cudaEventDisableTiming));
+    DR4G_CUDA(cudaEventCreateWithFlags(&xfree[b], cudaEventDisableTiming));
+    DR4G_CUDA(cudaEventCreateWithFlags(&projected[b], cudaEventDisableTiming));
+    DR4G_CUDA(cudaEventCreateWithFlags(&zfree[b], cudaEventDisableTiming));
+  }
+  auto cleanup = [&]() {
+    for (int b = 0; b < 2; ++b) {
+      cudaEventDestroy(loaded[b]);
+      cudaEventDestroy(xfree[b]);
+      cudaEventDestroy(projected[b]);
+      cudaEventDestroy(zfree[b]);
+    }
+  };
+  try {
+    DR4G_CUDA(cudaStreamSynchronize(c.stream));
+    c.sf.release();
+    const long long nchunks = (n + chunk - 1) / chunk;
+    // [1] fit
+    for (long long i = 0; i < nchunks; ++i) {
+      const int b = (int)(i & 1);
+      const long long r0 = i * chunk, rows = n - r0 < chunk ? n - r0 : chunk;
+      if (i >= 2) DR4G_CUDA(cudaStreamWaitEvent(c.copy_stream, xfree[b], 0));
+      DR4G_CUDA(cudaMemcpyAsync(xb[b], X + (size_t)r0 * d, (size_t)rows * d * sizeof(T), cudaMemcpyDefault, c.copy_stream));
+      DR4G_CUDA(cudaEventRecord(loaded[b], c.copy_stream));
+      DR4G_CUDA(cudaStreamWaitEvent(c.stream, loaded[b], 0));
+      partial_fit_impl<T>(c, xb[b], rows, d, is_pca ? 1 : 0);
+      DR4G_CUDA(cudaEventRecord(xfree[b], c.stream));
+    }
+    partial_fit_finalize_impl<T>(c, k, p, dQ, dw, dev, devr, dmean);
+    // [2] scores
+    for (long long i = 0; i < nchunks; ++i) {
+      const int b = (int)(i & 1);
+      const long long r0 = i * chunk, rows = n - r0 < chunk ? n - r0 : chunk;
+      DR4G_CUDA(cudaStreamWaitEvent(c.copy_stream, xfree[b], 0));   // last reader: the pass or the projection of chunk i-2
+      DR4G_CUDA(cudaMemcpyAsync(xb[b], X + (size_t)r0 * d, (size_t)rows * d * sizeof(T), cudaMemcpyDefault, c.copy_stream));
+      DR4G_CUDA(cudaEventRecord(loaded[b], c.copy_stream));
+      DR4G_CUDA(cudaStreamWaitEvent(c.stream, loaded[b], 0));
+      if (i >= 2) DR4G_CUDA(cudaStreamWaitEvent(c.stream, zfree[b], 0));
+      launch_project<T>(c, xb[b], rows, d, k, dQ, is_pca ? dmean : nullptr, dw, zb[b], ub[b]);
+      DR4G_CUDA(cudaEventRecord(projected[b], c.stream));
+      DR4G_CUDA(cudaEventRecord(xfree[b], c.stream));
+      DR4G_CUDA(cudaStreamWaitEvent(c.out_stream, projected[b], 0));
+      DR4G_CUDA(cudaMemcpyAsync(Xt + (size_t)r0 * k, zb[b], (size_t)rows * k * sizeof(T), cudaMemcpyDefault, c.out_stream));
+      DR4G_CUDA(cudaMemcpyAsync(U + (size_t)r0 * k, ub[b], (size_t)rows * k * sizeof(T), cudaMemcpyDefault, c.out_stream));
+      DR4G_CUDA(cudaEventRecord(zfree[b], c.out_stream));
+    }
+    auto out = [&](T* dst, const T* src, size_t count) {
+      if (dst) DR4G_CUDA(cudaMemcpyAsync(dst, src, count * sizeof(T), cudaMemcpyDefault, c.stream));
+    };
+    out(Q, dQ, (size_t)k * d);
+    out(w, dw, k);
+    out(ev, dev, k);
+    out(evr, devr, k);
+    if (is_pca) out(mean, dmean, d);
+    DR4G_CUDA(cudaStreamSynchronize(c.copy_stream));
+    DR4G_CUDA(cudaStreamSynchronize(c.stream));
+    DR4G_CUDA(cudaStreamSynchronize(c.out_stream));
+    c.sf.release();
+  } catch (...) {
+    cudaStreamSynchronize(c.copy_stream);
+    cudaStreamSynchronize(c.stream);
+    cudaStreamSynchronize(c.out_stream);
+    c.sf.release();
+    cleanup();
+    throw;
+  }
+  cleanup();
+}
+
 // ---------------------------------------------------------------- legacy host-pointer entry points
 static bool is_device_pointer(const void* p) {
   cudaPointerAttributes a;
@@ -321,6 +491,21 @@ static void legacy_entry(bool is_pca, const T* X, T* Q, T* w, T* U, T* Xt, T* ev
     const size_t xbytes = (size_t)n * d * sizeof(T);
     const size_t zbytes = (size_t)n * k * sizeof(T);
     const bool x_on_device = is_device_pointer(X);
+    // Out of core: X and its scores do not fit beside each other on the device (or
+    // DR4G_STREAM_ROWS forces a chunk size): two streamed sweeps over the host copy of X.
+    {
+      size_t free_b = 0, total_b = 0;
+      DR4G_CUDA(cudaMemGetInfo(&free_b, &total_b));
+      const char* env = getenv("DR4G_STREAM_ROWS");
+      const long long forced = env ? atoll(env) : 0;
+      if (!x_on_device && (forced > 0 || (double)xbytes + 2.0 * (double)zbytes > 0.8 * (double)total_b)) {
+        long long chunk = forced > 0 ? forced : (long long)(((size_t)256 << 20) / ((size_t)d * sizeof(T)));
+        if (chunk < 1024 && forced <= 0) chunk = 1024;
+        if (chunk > n) chunk = n;
+        legacy_out_of_core<T>(*c, is_pca, X, n, d, k, chunk, p, Q, w, U, Xt, ev, evr, mean);
+        return;
+      }
+    }
     size_t need = 2 * up256(zbytes) + up256((size_t)k * d * sizeof(T)) + 3 * up256((size_t)k * sizeof(T)) +
                   up256((size_t)d * sizeof(T)) + 4096;
     if (!x_on_device) need += up256(xbytes);
@@ -497,6 +682,39 @@ int dr4g_comm_world(dr4g_ctx* ctx) { return ctx ? ctx->world : 0; }
   }
 DR4G_FIT(dr4g_fit_float, float)
 DR4G_FIT(dr4g_fit_double, double)
+
+// ---- streaming fit ----------------------------------------------------------------
+int dr4g_partial_fit_reset(dr4g_ctx* ctx) {
+  DR4G_API_BEGIN
+  if (!ctx) fail("null context");
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  DeviceGuard g(ctx->device);
+  DR4G_CUDA(cudaStreamSynchronize(ctx->stream));
+  ctx->sf.release();
+  DR4G_API_END
+}
+
+long long dr4g_partial_fit_rows(dr4g_ctx* ctx) { return ctx ? ctx->sf.rows : -1; }
+
+#define DR4G_PARTIAL(NAME, FNAME, T)                                                                        \
+  int NAME(dr4g_ctx* ctx, const T* dX, long long n, int d, int center) {                                    \
+    DR4G_API_BEGIN                                                                                          \
+    if (!ctx || (!dX && n > 0)) fail(#NAME ": null argument");                                              \
+    std::lock_guard<std::mutex> lk(ctx->mu);                                                                \
+    DeviceGuard g(ctx->device);                                                                             \
+    partial_fit_impl<T>(*ctx, dX, n, d, center);                                                            \
+    DR4G_API_END                                                                                            \
+  }                                                                                                         \
+  int FNAME(dr4g_ctx* ctx, int k, params p, T* dQ, T* dw, T* dev, T* devr, T* dmean) {                      \
+    DR4G_API_BEGIN                                                                                          \
+    if (!ctx || !dQ || !dw) fail(#FNAME ": null argument");                                                 \
+    std::lock_guard<std::mutex> lk(ctx->mu);                                                                \
+    DeviceGuard g(ctx->device);                                                                             \
+    partial_fit_finalize_impl<T>(*ctx, k, p, dQ, dw, dev, devr, dmean);                                     \
+    DR4G_API_END                                                                                            \
+  }
+DR4G_PARTIAL(dr4g_partial_fit_float, dr4g_partial_fit_finalize_float, float)
+DR4G_PARTIAL(dr4g_partial_fit_double, dr4g_partial_fit_finalize_double, double)
 
 #define DR4G_TRANSFORM(NAME, T)                                                                            \
   int NAME(dr4g_ctx* ctx, const T* dX, long long n, int d, int k, const T* dQ, const T* dmean, const T* dw, \

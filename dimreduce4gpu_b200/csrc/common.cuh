@@ -118,6 +118,7 @@ void* tensor_map_encoder(Ctx& c);  // cuTensorMapEncodeTiled, fetched lazily thr
 // dsum_and_count = [column sums (d) | row count (1)] of the pilot sample (all-reduced across ranks)
 void launch_pilot_finish(Ctx& c, const double* dsum_and_count, int d, float* shift_f, double* shift_d);
 void launch_set_scalar(Ctx& c, double* dst, double value);
+void launch_add_f64(Ctx& c, double* acc, const double* x, size_t count);  // acc += x (streaming fit)
 void launch_center(Ctx& c, const double* packed, int d, int center, const double* shift_d,
                    double* dC /* d x d, may alias packed G */, double* dmean, double* dtotal_var);
 

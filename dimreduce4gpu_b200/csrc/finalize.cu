@@ -85,6 +85,17 @@ void launch_pilot_finish(Ctx& c, const double* dsum_and_count, int d, float* shi
   DR4G_CUDA(cudaGetLastError());
 }
 
+__global__ void add_f64_kernel(double* __restrict__ acc, const double* __restrict__ x, size_t count) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < count) acc[i] += x[i];
+}
+
+void launch_add_f64(Ctx& c, double* acc, const double* x, size_t count) {
+  add_f64_kernel<<<(unsigned)((count + 255) / 256), 256, 0, c.stream>>>(acc, x, count);
+  c.launches++;
+  DR4G_CUDA(cudaGetLastError());
+}
+
 void launch_set_scalar(Ctx& c, double* dst, double value) {
   set_scalar_kernel<<<1, 1, 0, c.stream>>>(dst, value);
   c.launches++;

@@ -140,6 +140,53 @@ class DeviceContext:
         _check(rc, f"dr4g_fit_{sfx}")
         return out
 
+    # ------------------------------------------------------------------ streaming fit
+    def partial_fit(self, X, center: bool) -> None:
+        """Accumulate one device-resident row chunk (n, d) into the context's [G|s|q|n]; asynchronous on the
+        current torch stream (keep X alive until later work on that stream has finished)."""
+        _need_cuda_contig(X, "X", self.device)
+        if X.dim() != 2:
+            raise ValueError("X must be 2-D (n_samples, n_features)")
+        n, d = X.shape
+        sfx = _suffix(X)
+        self._on_torch_stream()
+        rc = getattr(self._lib, f"dr4g_partial_fit_{sfx}")(self._h, X.data_ptr(), n, d, 1 if center else 0)
+        _check(rc, f"dr4g_partial_fit_{sfx}")
+
+    def partial_fit_rows(self) -> int:
+        return int(self._lib.dr4g_partial_fit_rows(self._h))
+
+    def partial_fit_reset(self) -> None:
+        _check(self._lib.dr4g_partial_fit_reset(self._h), "dr4g_partial_fit_reset")
+
+    def partial_fit_finalize(self, n_features: int, n_components: int, center: bool, dtype, algorithm: str = "cusolver",
+                             n_iter: int = 5, random_state: int = 0, tol: float = 1e-5, verbose: bool = False) -> dict:
+        """Eigensolve + outputs from the accumulated chunks; same result dictionary as fit()."""
+        import torch
+
+        d = int(n_features)
+        rows = self.partial_fit_rows()
+        if rows <= 0 and self.world <= 1:
+            raise RuntimeError("partial_fit_finalize: nothing accumulated (call partial_fit first)")
+        k = min(int(n_components), d) if self.world > 1 else min(int(n_components), rows, d)
+        dev = torch.device("cuda", self.device)
+        z = lambda *s: torch.empty(*s, dtype=dtype, device=dev)  # noqa: E731
+        out = dict(components=z(k, d), singular_values=z(k), explained_variance=z(k),
+                   explained_variance_ratio=z(k), mean=z(d) if center else None)
+        sfx = "float" if dtype == torch.float32 else "double"
+        p = params()
+        p.X_n, p.X_m, p.k = min(rows, 2**31 - 1), d, k
+        p.algorithm = algorithm.encode("utf-8")
+        p.n_iter, p.random_state, p.tol = int(n_iter), int(random_state) & 0x7FFFFFFF, float(tol)
+        p.verbose, p.gpu_id, p.whiten = int(bool(verbose)), self.device, False
+        self._on_torch_stream()
+        rc = getattr(self._lib, f"dr4g_partial_fit_finalize_{sfx}")(
+            self._h, k, p, out["components"].data_ptr(), out["singular_values"].data_ptr(),
+            out["explained_variance"].data_ptr(), out["explained_variance_ratio"].data_ptr(),
+            out["mean"].data_ptr() if center else None)
+        _check(rc, f"dr4g_partial_fit_finalize_{sfx}")
+        return out
+
     def transform(self, X, components, mean=None, singular_values=None, want_u: bool = False, out=None, out_u=None):
         """Z = (X - mean) @ components.T on this rank's rows (no communication); optionally U = Z / sigma."""
         import torch

@@ -37,6 +37,10 @@ def _bind(lib: ctypes.CDLL) -> None:
         # device-pointer API: pointers are passed as integers (tensor.data_ptr())
         f = getattr(lib, f"dr4g_fit_{name}")
         f.argtypes, f.restype = [vp, vp, ll, ci, ci, ci, params, vp, vp, vp, vp, vp], ci
+        f = getattr(lib, f"dr4g_partial_fit_{name}")
+        f.argtypes, f.restype = [vp, vp, ll, ci, ci], ci
+        f = getattr(lib, f"dr4g_partial_fit_finalize_{name}")
+        f.argtypes, f.restype = [vp, ci, params, vp, vp, vp, vp, vp], ci
         f = getattr(lib, f"dr4g_transform_{name}")
         f.argtypes, f.restype = [vp, vp, ll, ci, ci, vp, vp, vp, vp, vp], ci
         f = getattr(lib, f"dr4g_inverse_transform_{name}")
@@ -60,6 +64,8 @@ def _bind(lib: ctypes.CDLL) -> None:
     lib.dr4g_stage_times.argtypes, lib.dr4g_stage_times.restype = [vp, c_double_p, ci], ci
     lib.dr4g_last_gram_path.argtypes, lib.dr4g_last_gram_path.restype = [vp], ci
     lib.dr4g_launch_count.argtypes, lib.dr4g_launch_count.restype = [vp], ll
+    lib.dr4g_partial_fit_reset.argtypes, lib.dr4g_partial_fit_reset.restype = [vp], ci
+    lib.dr4g_partial_fit_rows.argtypes, lib.dr4g_partial_fit_rows.restype = [vp], ll
 
 
 # every symbol include/dimreduce4gpu.h declares (checked by tests/test_abi.py with `nm -D` semantics)
@@ -71,6 +77,8 @@ EXPORTED_SYMBOLS = (
     "dr4g_inverse_transform_float", "dr4g_inverse_transform_double", "dr4g_colstats_float",
     "dr4g_colstats_double", "dr4g_gram_float", "dr4g_gram_double", "dr4g_eigh_double", "dr4g_eigh_topk_double", "dr4g_stage_times",
     "dr4g_last_gram_path", "dr4g_launch_count",
+    "dr4g_partial_fit_float", "dr4g_partial_fit_double", "dr4g_partial_fit_finalize_float",
+    "dr4g_partial_fit_finalize_double", "dr4g_partial_fit_reset", "dr4g_partial_fit_rows",
 )
 
 

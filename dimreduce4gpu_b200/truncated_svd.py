@@ -76,12 +76,16 @@ class TruncatedSVD:
     # ------------------------------------------------------------------ attributes
     @property
     def components_(self):
+        if getattr(self, "_stream_dirty", False):
+            self.finalize_fit()
         if self._Q is None:
             raise AttributeError("components_ is not available before fit/fit_transform.")
         return self._Q
 
     @property
     def singular_values_(self):
+        if getattr(self, "_stream_dirty", False):
+            self.finalize_fit()
         if self._w is None:
             raise AttributeError("singular_values_ is not available before fit/fit_transform.")
         return self._w
@@ -154,6 +158,62 @@ class TruncatedSVD:
         self.mean_ = res["mean"].cpu().numpy() if self._center else None
         self._U = None
         return Z
+
+    # ------------------------------------------------------------------ streaming fit
+    def partial_fit(self, X, y=None):
+        """Accumulate a chunk of rows (numpy array or torch CUDA tensor, (n_chunk, n_features)) into the
+        fit's sufficient statistics on the GPU.  X as a whole never has to fit in device memory; call
+        ``finalize_fit()`` (or read ``components_`` through ``transform``) after the last chunk.  Not in the
+        reference, whose entry points copy all of X to the device (src/tsvd.cu:427-452)."""
+        import torch
+
+        select_backend(self.backend)
+        tdt = torch.float32 if self.dtype == np.float32 else torch.float64
+        Xd, _ = self._to_device(X, tdt)
+        if Xd.dim() != 2:
+            raise ValueError("X must be 2-D (n_samples, n_features)")
+        if getattr(self, "_sctx", None) is None:
+            from .device import DeviceContext
+
+            self._sctx = DeviceContext(Xd.device.index)   # the accumulators live in this private context
+            self._stream_d = None
+        if self._stream_d is None:
+            self._sctx.partial_fit_reset()
+            self._stream_d = int(Xd.shape[1])
+        elif Xd.shape[1] != self._stream_d:
+            raise ValueError(f"chunk has {Xd.shape[1]} features, earlier chunks had {self._stream_d}")
+        with torch.cuda.device(Xd.device):
+            self._sctx.partial_fit(Xd, center=self._center)
+        self._stream_dirty = True
+        return self
+
+    def finalize_fit(self):
+        """Eigensolve + outputs from the chunks accumulated by partial_fit (more chunks may follow)."""
+        import torch
+
+        if getattr(self, "_sctx", None) is None or self._stream_d is None:
+            raise RuntimeError("finalize_fit() needs at least one partial_fit() call")
+        tdt = torch.float32 if self.dtype == np.float32 else torch.float64
+        with torch.cuda.device(self._sctx.device):
+            res = self._sctx.partial_fit_finalize(self._stream_d, self.n_components, self._center, tdt,
+                                                  algorithm=self.algorithm, n_iter=self.n_iter,
+                                                  random_state=self.random_state, tol=self.tol, verbose=self.verbose)
+            self._sctx.sync()
+        self._Q = res["components"].cpu().numpy()
+        self._w = res["singular_values"].cpu().numpy()
+        self.explained_variance_ = res["explained_variance"].cpu().numpy()
+        self.explained_variance_ratio_ = res["explained_variance_ratio"].cpu().numpy()
+        self.mean_ = res["mean"].cpu().numpy() if self._center else None
+        self._U = None
+        self._stream_dirty = False
+        return self
+
+    def reset_partial_fit(self):
+        if getattr(self, "_sctx", None) is not None:
+            self._sctx.partial_fit_reset()
+            self._stream_d = None
+        self._stream_dirty = False
+        return self
 
     # ------------------------------------------------------------------ transform / inverse
     def _to_device(self, A, dtype):

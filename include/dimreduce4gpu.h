@@ -105,6 +105,26 @@ DR4G_EXPORT int dr4g_fit_float(dr4g_ctx* ctx, const float* dX, long long n_local
 DR4G_EXPORT int dr4g_fit_double(dr4g_ctx* ctx, const double* dX, long long n_local, int d, int k, int center,
                     params p, double* dQ, double* dw, double* dev, double* devr, double* dmean);
 
+/* Streaming (out-of-core) fit, SURVEY 8f-1: the packed accumulators [G | s | q | n] of the fit are summed
+ * over row chunks, so X never has to be device-resident as a whole (the reference's host-pointer symbols,
+ * truncated_svd.py:98-107 / src/tsvd.cu:427-452, copy all of X to the device first).
+ *   dr4g_partial_fit_*          one pass over a device-resident chunk (n x d); the first chunk fixes d, center,
+ *                               the element type and, for center=1, the pilot shift (all-reduced when a
+ *                               communicator is set: every rank must then make its first call together).
+ *   dr4g_partial_fit_finalize_* exchange + eigensolve + outputs, exactly as dr4g_fit_* after its pass
+ *                               (one all-reduce of the packed accumulators when a communicator is set);
+ *                               the accumulated state stays valid (more chunks may follow).
+ *   dr4g_partial_fit_reset      drop the accumulated state;  dr4g_partial_fit_rows: rows accumulated so far.
+ * Asynchronous on ctx's stream: a chunk buffer may be reused once work queued after the call has completed. */
+DR4G_EXPORT int dr4g_partial_fit_float(dr4g_ctx* ctx, const float* dX, long long n, int d, int center);
+DR4G_EXPORT int dr4g_partial_fit_double(dr4g_ctx* ctx, const double* dX, long long n, int d, int center);
+DR4G_EXPORT int dr4g_partial_fit_finalize_float(dr4g_ctx* ctx, int k, params p, float* dQ, float* dw, float* dev,
+                                    float* devr, float* dmean);
+DR4G_EXPORT int dr4g_partial_fit_finalize_double(dr4g_ctx* ctx, int k, params p, double* dQ, double* dw, double* dev,
+                                     double* devr, double* dmean);
+DR4G_EXPORT int dr4g_partial_fit_reset(dr4g_ctx* ctx);
+DR4G_EXPORT long long dr4g_partial_fit_rows(dr4g_ctx* ctx);
+
 /* transform on a device-resident row shard (no communication):
  *   dZ[n x k] = (dX - dmean) * dQ^T   (dmean NULL -> no centring, the reference's transform,
  *                                      dimreduce4gpu/truncated_svd.py:116-118)

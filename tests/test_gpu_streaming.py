@@ -1,0 +1,136 @@
+"""Streaming / out-of-core fit, B200 only (`-m gpu`): dr4g_partial_fit_* through DeviceContext and
+the estimators, and the chunked two-sweep path of the legacy host-pointer symbols (DR4G_STREAM_ROWS), checked
+against the reference's CPU backend (live oracle) and against the one-pass fit of the same data.
+
+Tolerances: BASELINE.json's 1e-4 relative (fp32) / 1e-10 (fp64) against the oracle; chunked vs one-pass fit of
+the same rows differ only by summation order (1e-5 / 1e-12 relative on singular values)."""
+from __future__ import annotations
+
+import os
+
+import numpy as np
+import pytest
+
+from oracle import cpu_oracle as O
+from test_gpu_parity import TOL32, _check_against, _rel
+
+pytestmark = pytest.mark.gpu
+
+
+def _data(n, d, seed, dtype=np.float32, offset=True):
+    rng = np.random.default_rng(seed)
+    X = rng.standard_normal((n, d)) * np.linspace(1.0, 3.0, d)
+    if offset:
+        X += np.linspace(-5.0, 5.0, d)
+    return np.ascontiguousarray(X.astype(dtype))
+
+
+def _ref(kind, X, k):
+    if O.REF_SO.is_file():
+        return (O.RefLib().pca if kind == "pca" else O.RefLib().tsvd)(X, k, "cusolver")
+    return (O.restated_pca if kind == "pca" else O.restated_tsvd)(X, k)
+
+
+@pytest.mark.parametrize("kind,n,d,k,cuts", [("pca", 20000, 256, 32, (7000, 7001, 19999)), ("tsvd", 9000, 100, 10, (1, 4500)),
+                                              ("pca", 3000, 320, 8, (1000, 2000)), ("pca", 600, 33, 5, (599,))])
+def test_partial_fit_context_matches_one_pass_fit(kind, n, d, k, cuts):
+    """Ragged chunks (a 1-row chunk, a chunk below the pilot size) through dr4g_partial_fit_float."""
+    import torch
+
+    import dimreduce4gpu_b200 as pkg
+
+    X = torch.from_numpy(_data(n, d, 5 + n)).cuda()
+    center = kind == "pca"
+    ctx = pkg.DeviceContext(0)
+    whole = ctx.fit(X, k, center=center, algorithm="cusolver")
+    ctx.partial_fit_reset()
+    edges = (0,) + tuple(cuts) + (n,)
+    for a, b in zip(edges[:-1], edges[1:]):
+        ctx.partial_fit(X[a:b].contiguous(), center=center)
+    assert ctx.partial_fit_rows() == n
+    part = ctx.partial_fit_finalize(d, k, center, torch.float32, algorithm="cusolver")
+    ctx.sync()
+    assert _rel(part["singular_values"].cpu().numpy(), whole["singular_values"].cpu().numpy()) < 1e-5
+    assert _rel(part["explained_variance_ratio"].cpu().numpy(), whole["explained_variance_ratio"].cpu().numpy()) < 1e-5
+    if center:
+        assert float((part["mean"] - whole["mean"]).abs().max()) < 1e-5
+    ang = O.max_principal_angle(part["components"].cpu().numpy(), whole["components"].cpu().numpy())
+    assert ang < 1e-3
+    # the state survives finalize: more chunks may follow
+    ctx.partial_fit(X[:100].contiguous(), center=center)
+    assert ctx.partial_fit_rows() == n + 100
+    ctx.partial_fit_reset()
+    assert ctx.partial_fit_rows() == 0
+
+
+def test_partial_fit_rejects_mismatched_chunks():
+    import torch
+
+    import dimreduce4gpu_b200 as pkg
+
+    ctx = pkg.DeviceContext(0)
+    ctx.partial_fit_reset()
+    ctx.partial_fit(torch.randn(100, 64, device="cuda"), center=True)
+    with pytest.raises(RuntimeError, match="does not match"):
+        ctx.partial_fit(torch.randn(100, 65, device="cuda"), center=True)
+    with pytest.raises(RuntimeError, match="does not match"):
+        ctx.partial_fit(torch.randn(100, 64, device="cuda", dtype=torch.float64), center=True)
+    ctx.partial_fit_reset()
+    with pytest.raises(RuntimeError, match="nothing accumulated"):
+        ctx.partial_fit_finalize(64, 4, True, torch.float32)
+
+
+@pytest.mark.parametrize("kind,n,d,k", [("pca", 12000, 256, 16), ("tsvd", 8000, 130, 7)])
+def test_estimator_partial_fit_matches_oracle(kind, n, d, k):
+    """numpy chunks through PCA.partial_fit / TruncatedSVD.partial_fit vs the reference CPU backend on all rows."""
+    import dimreduce4gpu_b200 as pkg
+
+    X = _data(n, d, 31 + n)
+    ref = _ref(kind, X, k)
+    cls = pkg.PCA if kind == "pca" else pkg.TruncatedSVD
+    est = cls(n_components=k, algorithm="cusolver", random_state=42, backend="gpu")
+    for a in range(0, n, 2500):
+        est.partial_fit(X[a:a + 2500])
+    Z = est.transform(X, center=kind == "pca")   # finalises lazily
+    _check_against(est, Z, ref.components, ref.singular_values, ref.explained_variance, ref.explained_variance_ratio,
+                   ref.mean, ref.X_transformed, TOL32, n)
+
+
+def test_estimator_partial_fit_fp64():
+    import dimreduce4gpu_b200 as pkg
+
+    n, d, k = 5000, 96, 12
+    X = _data(n, d, 77, dtype=np.float64)
+    ref = O.restated_pca(X, k, dtype=np.float64)
+    est = pkg.PCA(n_components=k, backend="gpu", dtype="float64")
+    for a in range(0, n, 1234):
+        est.partial_fit(X[a:a + 1234])
+    est.finalize_fit()
+    assert est.components_.dtype == np.float64
+    assert _rel(est.singular_values_, ref.singular_values) < 1e-10
+    np.testing.assert_allclose(est.mean_, ref.mean, rtol=0, atol=1e-12)
+
+
+@pytest.mark.parametrize("kind,n,d,k,rows", [("pca", 20000, 256, 32, 3000), ("tsvd", 10000, 100, 10, 4096), ("pca", 5000, 64, 6, 5000)])
+def test_legacy_symbols_out_of_core(kind, n, d, k, rows, monkeypatch):
+    """pca_float / truncated_svd_float with DR4G_STREAM_ROWS: two chunked sweeps over the host X (H2D, pass /
+    projection and D2H overlapped on three streams) give the reference's outputs, including U and X_transformed."""
+    import dimreduce4gpu_b200 as pkg
+
+    X = _data(n, d, 900 + n)
+    ref = _ref(kind, X, k)
+    monkeypatch.setenv("DR4G_STREAM_ROWS", str(rows))
+    cls = pkg.PCA if kind == "pca" else pkg.TruncatedSVD
+    est = cls(n_components=k, algorithm="cusolver", random_state=42, backend="gpu")
+    Z = est.fit_transform(X)
+    monkeypatch.delenv("DR4G_STREAM_ROWS")
+    _check_against(est, Z, ref.components, ref.singular_values, ref.explained_variance, ref.explained_variance_ratio,
+                   ref.mean, ref.X_transformed, TOL32, n)
+    # U = X_transformed / sigma, as the reference's get_tsvd_attr (src/tsvd.cu:171-175)
+    np.testing.assert_allclose(est._U * est.singular_values_[None, :], Z, rtol=1e-5, atol=1e-4)
+    # and the resident path gives the same scores
+    est2 = cls(n_components=k, algorithm="cusolver", random_state=42, backend="gpu")
+    Z2 = est2.fit_transform(X)
+    assert _rel(est2.singular_values_, est.singular_values_) < 1e-5
+    assert float(np.max(np.abs(np.abs(Z2) - np.abs(Z)))) < 1e-3 * float(est.singular_values_[0])
+    assert os.environ.get("DR4G_STREAM_ROWS") is None
