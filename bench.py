@@ -56,7 +56,7 @@ class ClockSampler:
     def start(self) -> None:
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE,
+                                          "-lms", "20", "-i", str(self.index)], stdout=subprocess.PIPE,
                                          stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._pump, daemon=True).start()
         except OSError:
@@ -66,14 +66,23 @@ class ClockSampler:
         for ln in self.proc.stdout:
             self.lines.append(ln)
 
-    def stop(self) -> dict:
+    def wait_first(self, timeout: float = 5.0) -> None:
+        """nvidia-smi needs a few hundred ms to come up: block until its first line so that a short timed
+        region is not over before the first sample."""
+        t0 = time.time()
+        while self.proc is not None and not self.lines and time.time() - t0 < timeout:
+            time.sleep(0.01)
+
+    def mark(self) -> int:
+        return len(self.lines)
+
+    def stop(self, first: int = 0) -> dict:
         if self.proc is None:
             return dict(sm_mhz=None, sm_max_mhz=None, reasons=["nvidia-smi unavailable"])
-        time.sleep(0.15)
         self.proc.terminate()
         sm, mx, reasons = [], [], set()
         names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
-        for ln in self.lines:
+        for ln in self.lines[first:]:
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 9:
                 continue
@@ -269,12 +278,15 @@ def main() -> None:
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(args.warmup):
-        step()
-    barrier()
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    if rank == 0:
+        sampler.wait_first()
+    mark = sampler.mark()
     launches0 = ctx.launch_count
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
@@ -285,19 +297,29 @@ def main() -> None:
     barrier()
     ms_total = e0.elapsed_time(e1)
     launches = ctx.launch_count - launches0
-    # per-kernel share: same steps again, synchronising each one to read the library's stage events
+    t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total = float(t.item())
+    # per-kernel share: same steps again, synchronising each one to read the library's stage events; enough of
+    # them (same count on every rank: the step contains collectives) for the clock sampler to see >= 0.2 s of load
     stage_acc: dict = {}
-    for _ in range(min(args.steps, 10)):
+    replay = max(min(args.steps, 10), min(400, int(200.0 / max(ms_total / max(args.steps, 1), 0.05))))
+    for _ in range(replay):
         step()
         torch.cuda.synchronize()
         st = ctx.stage_times()
         for kk, v in (st or {}).items():
             stage_acc.setdefault(kk, []).append(v)
-    clocks = sampler.stop() if rank == 0 else None
-    t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_total = float(t.item())
+    # a 30 ms timed region is shorter than nvidia-smi's sampling period: keep the same steps running (untimed)
+    # until the sampler has seen the load at least 5 times, at most 1 s
+    t_end = time.time() + 1.0
+    while rank == 0 and world == 1 and sampler.proc is not None and sampler.mark() - mark < 5 and time.time() < t_end:
+        step()
+        torch.cuda.synchronize()
+    clocks = sampler.stop(mark) if rank == 0 else None
+    if clocks is not None:
+        clocks["window"] = "timed steps + the same steps replayed untimed (stage events)"
     value = n * world * args.steps / (ms_total * 1e-3)
 
     # ---- end to end through the public API with HOST buffers (pinned), copies inside the timed region

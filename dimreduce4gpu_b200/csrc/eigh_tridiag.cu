@@ -46,6 +46,18 @@ __device__ __forceinline__ double fast_rcp(double x) {
   return r;
 }
 
+// sqrt(x) for normal positive x the same way: rsqrt.approx.ftz.f64 seed + two Newton steps, sqrt = x * rsqrt
+// (the IEEE sqrt is another call-like sequence on the per-step critical path of the tridiagonalisation).
+__device__ __forceinline__ double fast_sqrt(double x) {
+  double y;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+  const double hx = 0.5 * x;
+  y = y * fma(-hx * y, y, 1.5);
+  y = y * fma(-hx * y, y, 1.5);
+  const double r = x * y;
+  return fma(fma(-r, r, x), 0.5 * y, r);   // one correction step on the root itself
+}
+
 __device__ __forceinline__ void tri_grid_barrier(TriCtrl* ctrl, unsigned int& target) {
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -225,16 +237,20 @@ tridiag_cluster_kernel(const double* __restrict__ A, int d, double* __restrict__
   double* v = tri_sm;
   double* w = v + d;
   double* vn = w + d;
-  double* row = vn + d;
-  double* pl = row + d;        // p, two parities (pushed into every CTA by the row owners)
+  double* rowp = vn + d;       // row s, two parities (pushed into every CTA by the row's owner through DSMEM)
+  double* pl = rowp + 2 * (size_t)d;  // p, two parities (pushed into every CTA by the row owners)
   double* R = pl + 2 * (size_t)d;  // own rows: slot i / cs
   __shared__ double red2[2][kTriWarps];
   int par = 0;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int rank = (int)cluster_rank(), cs = (int)cluster_size();
-  double* rbuf = xbuf + 2 * (size_t)d;  // published rows, two parities (global)
+  (void)xbuf;
 
-  for (int c = tid; c < d; c += kTriThreads) { v[c] = 0.0; w[c] = 0.0; vn[c] = 0.0; pl[c] = 0.0; pl[d + c] = 0.0; }
+  for (int c = tid; c < d; c += kTriThreads) {
+    v[c] = 0.0; w[c] = 0.0; vn[c] = 0.0; pl[c] = 0.0; pl[d + c] = 0.0;
+    rowp[c] = A[c];            // row 0
+    rowp[d + c] = 0.0;
+  }
   for (int i = rank + cs * warp; i < d; i += cs * kTriWarps) {
     double* Ri = R + (size_t)(i / cs) * d;
     for (int c = lane; c < d; c += 32) Ri[c] = A[(size_t)i * d + c];
@@ -247,16 +263,9 @@ tridiag_cluster_kernel(const double* __restrict__ A, int d, double* __restrict__
   for (int s = 0; s < d - 1; ++s) {
     const double* pcur = pl + (size_t)((s + 1) & 1) * d;  // parity (s-1)&1
     TRI_TRACE(0);
-    // row s: from own shared memory when this CTA owns it, else the copy its owner published
-    if (s == 0) {
-      for (int c = tid; c < d; c += kTriThreads) row[c] = A[c];
-    } else if (owner == rank) {
-      const double* Rs = R + (size_t)oslot * d;
-      for (int c = s + tid; c < d; c += kTriThreads) row[c] = Rs[c];
-    } else {
-      const double* rp = rbuf + (size_t)(s & 1) * d;
-      for (int c = s + tid; c < d; c += kTriThreads) row[c] = __ldcg(&rp[c]);
-    }
+    // row s arrived in this CTA's shared memory before the last cluster barrier (an L2 round trip through a
+    // published global copy cost ~1100 cycles per step here)
+    double* row = rowp + (size_t)(s & 1) * d;
     TRI_TRACE(1);
     double pv = 0.0;
     for (int c = s + tid; c < d; c += kTriThreads) pv += pcur[c] * vn[c];
@@ -283,7 +292,8 @@ tridiag_cluster_kernel(const double* __restrict__ A, int d, double* __restrict__
     const double x0 = row[s + 1];
     double beta = x0, t = 0.0, scale = 0.0;
     if (nrm2 > 0.0 && s < d - 2) {
-      const double nrm = sqrt(x0 * x0 + nrm2);
+      const double y2 = fma(x0, x0, nrm2);
+      const double nrm = y2 > 1e-290 && y2 < 1e290 ? fast_sqrt(y2) : sqrt(y2);
       beta = x0 >= 0.0 ? -nrm : nrm;
       t = (beta - x0) * fast_rcp(beta);
       scale = fast_rcp(x0 - beta);
@@ -308,8 +318,6 @@ tridiag_cluster_kernel(const double* __restrict__ A, int d, double* __restrict__
       const double vi1 = two ? v[i1] : 0.0, wi1 = two ? w[i1] : 0.0;
       double* R0 = R + (size_t)q * d;
       double* R1 = two ? R0 + (size_t)kTriWarps * d : R0;
-      double* pub0 = (i0 == s + 1 && cs > 1) ? rbuf + (size_t)((s + 1) & 1) * d : nullptr;
-      double* pub1 = (two && i1 == s + 1 && cs > 1) ? rbuf + (size_t)((s + 1) & 1) * d : nullptr;
       double dot0 = 0.0, dot1 = 0.0;
       for (int c = cbeg + 2 * lane; c < d; c += 64) {
         const double2 wv = *reinterpret_cast<const double2*>(w + c);
@@ -331,8 +339,6 @@ tridiag_cluster_kernel(const double* __restrict__ A, int d, double* __restrict__
         }
         *reinterpret_cast<double2*>(R0 + c) = a;
         if (two) *reinterpret_cast<double2*>(R1 + c) = b;
-        if (pub0 && !(trace & 4)) __stcg(reinterpret_cast<double2*>(pub0 + c), a);
-        if (pub1 && !(trace & 4)) __stcg(reinterpret_cast<double2*>(pub1 + c), b);
       }
       if (!(trace & 8)) {
 #pragma unroll
@@ -348,6 +354,16 @@ tridiag_cluster_kernel(const double* __restrict__ A, int d, double* __restrict__
     }
     tprev = t;
     if (++owner == cs) { owner = 0; ++oslot; }
+    // the owner of row s+1 pushes it (columns > s) into every CTA of the cluster, all its threads sharing the stores
+    if (owner == rank) {
+      __syncthreads();
+      const double* Rs = R + (size_t)oslot * d;
+      double* dst = rowp + (size_t)((s + 1) & 1) * d;
+      for (int c = s + 1 + tid; c < d; c += kTriThreads) {
+        const double val = Rs[c];
+        for (int r = 0; r < cs; ++r) st_cluster_f64(dst + c, (unsigned)r, val);
+      }
+    }
     TRI_TRACE(5);
     cluster_barrier();
     TRI_TRACE(6);
@@ -747,7 +763,7 @@ void launch_eigh_topk(Ctx& c, double* dA, int d, int k, double* dW, double* dVt,
   if (d <= 512 && d % 2 == 0 && c.eig_solver != 2) {   // the cluster kernel sweeps rows in aligned column pairs
     static const int cs_env = getenv("DR4G_TRI_CS") ? atoi(getenv("DR4G_TRI_CS")) : 0;  // tuning hook
     const int cs = cs_env > 0 ? cs_env : (d <= 128 ? 1 : 16);  // 16 beats 8 at d = 256 (1.16 vs 1.28 ms, measured)
-    const size_t smem = ((size_t)6 * d + (size_t)((d + cs - 1) / cs) * d) * sizeof(double);
+    const size_t smem = ((size_t)7 * d + (size_t)((d + cs - 1) / cs) * d) * sizeof(double);
     static size_t smem_set = 0;
     static bool nonportable_set = false;
     if (smem > 48 * 1024 && smem > smem_set) {

@@ -85,6 +85,17 @@ def main() -> None:
         ctx.sync()
         out[alg] = {kk: v.cpu().numpy() for kk, v in res.items() if v is not None}
     Z = ctx.transform(Xg, res["components"], mean=res["mean"]).cpu().numpy()
+    # streaming fit across ranks: every rank feeds its shard in two chunks (the first call carries the pilot
+    # allreduce), finalize all-reduces the packed accumulators: same model as the one-pass sharded fit
+    ctx.partial_fit_reset()
+    half = n_local // 2
+    ctx.partial_fit(Xg[:half].contiguous(), center=True)
+    ctx.partial_fit(Xg[half:].contiguous(), center=True)
+    part = ctx.partial_fit_finalize(d, k, True, torch.float32, algorithm="cusolver")
+    ctx.sync()
+    sp, so = part["singular_values"].cpu().numpy(), out["cusolver"]["singular_values"]
+    assert np.max(np.abs(sp - so) / so) < 2e-5, "streaming sharded fit differs from the one-pass sharded fit"
+    assert float((part["mean"].cpu() - torch.from_numpy(out["cusolver"]["mean"])).abs().max()) < 1e-5
     # every rank must hold the same model (replicated eigensolve on identical all-reduced inputs)
     mine = torch.from_numpy(out["cusolver"]["components"]).cuda()
     ref0 = mine.clone()
