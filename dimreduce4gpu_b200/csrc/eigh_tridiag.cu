@@ -23,6 +23,7 @@
 #include <cstdlib>
 
 #include "common.cuh"
+#include "ptx_sm100.cuh"
 
 namespace dr4g {
 namespace {
@@ -225,6 +226,18 @@ __device__ __forceinline__ void st_cluster_f64(double* local_ptr, unsigned cta, 
   asm volatile("st.shared::cluster.f64 [%0], %1;" ::"r"(ra), "d"(val) : "memory");
 }
 
+// 8-byte store into the shared memory of CTA `cta` that also counts its bytes on that CTA's mbarrier
+// (st.async): the data's arrival is the signal, no release fence / cluster barrier on the producer side.
+__device__ __forceinline__ void st_async_f64(double* local_ptr, uint64_t* local_bar, unsigned cta, double val) {
+  const unsigned la = static_cast<unsigned>(__cvta_generic_to_shared(local_ptr));
+  const unsigned lb = static_cast<unsigned>(__cvta_generic_to_shared(local_bar));
+  unsigned ra, rb;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(la), "r"(cta));
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(rb) : "r"(lb), "r"(cta));
+  asm volatile("st.async.shared::cluster.mbarrier::complete_tx::bytes.f64 [%0], %1, [%2];" ::"r"(ra), "d"(val), "r"(rb)
+               : "memory");
+}
+
 // Debug aid (DR4G_TRI_TRACE=1): clock64() of CTA 0, thread 0 at the phase boundaries of steps 100..103.
 __device__ long long g_tri_trace[4 * 8];
 #define TRI_TRACE(ev) \
@@ -241,10 +254,19 @@ tridiag_cluster_kernel(const double* __restrict__ A, int d, double* __restrict__
   double* pl = rowp + 2 * (size_t)d;  // p, two parities (pushed into every CTA by the row owners)
   double* R = pl + 2 * (size_t)d;  // own rows: slot i / cs
   __shared__ double red2[2][kTriWarps];
+  // data of step s+1 (p' and row s+1, 16 (d-s-1) bytes per CTA) lands in the parity-(s+1) buffers and is counted
+  // on xbar[(s+1) & 1]: the consumer waits for the bytes, there is no cluster barrier inside the loop
+  __shared__ __align__(8) uint64_t xbar[2];
+  unsigned xph[2] = {0u, 0u};
   int par = 0;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int rank = (int)cluster_rank(), cs = (int)cluster_size();
   (void)xbuf;
+  if (tid == 0) {
+    ptx::mbar_init(ptx::smem_u32(&xbar[0]), 1);
+    ptx::mbar_init(ptx::smem_u32(&xbar[1]), 1);
+    ptx::fence_barrier_init();
+  }
 
   for (int c = tid; c < d; c += kTriThreads) {
     v[c] = 0.0; w[c] = 0.0; vn[c] = 0.0; pl[c] = 0.0; pl[d + c] = 0.0;
@@ -263,6 +285,15 @@ tridiag_cluster_kernel(const double* __restrict__ A, int d, double* __restrict__
   for (int s = 0; s < d - 1; ++s) {
     const double* pcur = pl + (size_t)((s + 1) & 1) * d;  // parity (s-1)&1
     TRI_TRACE(0);
+    if (s > 0) {
+      // wait for this step's operands (pushed by every CTA during its step s-1), then one CTA barrier: the own
+      // rows in R are handed from warp to warp between steps
+      ptx::mbar_wait_cluster(ptx::smem_u32(&xbar[s & 1]), xph[s & 1]);
+      xph[s & 1] ^= 1u;
+      __syncthreads();
+    }
+    const bool last = s == d - 2;      // nothing is exchanged after the last step
+    if (tid == 0 && !last) ptx::mbar_arrive_expect_tx(ptx::smem_u32(&xbar[(s + 1) & 1]), (uint32_t)(16 * (d - s - 1)));
     // row s arrived in this CTA's shared memory before the last cluster barrier (an L2 round trip through a
     // published global copy cost ~1100 cycles per step here)
     double* row = rowp + (size_t)(s & 1) * d;
@@ -347,27 +378,27 @@ tridiag_cluster_kernel(const double* __restrict__ A, int d, double* __restrict__
         dot1 += __shfl_xor_sync(0xffffffffu, dot1, o);
       }
       }
-      if (lane < cs && !(trace & 2)) {
-        st_cluster_f64(&pnext[i0], (unsigned)lane, t * dot0);
-        if (two) st_cluster_f64(&pnext[i1], (unsigned)lane, t * dot1);
+      if (lane < cs && !last) {
+        st_async_f64(&pnext[i0], &xbar[(s + 1) & 1], (unsigned)lane, t * dot0);
+        if (two) st_async_f64(&pnext[i1], &xbar[(s + 1) & 1], (unsigned)lane, t * dot1);
       }
     }
     tprev = t;
     if (++owner == cs) { owner = 0; ++oslot; }
     // the owner of row s+1 pushes it (columns > s) into every CTA of the cluster, all its threads sharing the stores
-    if (owner == rank) {
+    if (owner == rank && !last) {
       __syncthreads();
       const double* Rs = R + (size_t)oslot * d;
       double* dst = rowp + (size_t)((s + 1) & 1) * d;
       for (int c = s + 1 + tid; c < d; c += kTriThreads) {
         const double val = Rs[c];
-        for (int r = 0; r < cs; ++r) st_cluster_f64(dst + c, (unsigned)r, val);
+        for (int r = 0; r < cs; ++r) st_async_f64(dst + c, &xbar[(s + 1) & 1], (unsigned)r, val);
       }
     }
     TRI_TRACE(5);
-    cluster_barrier();
-    TRI_TRACE(6);
+    TRI_TRACE(6);   // pushes issued; the wait for the next step's operands is event 1 of the next step
   }
+  cluster_barrier();   // no CTA may exit while its shared memory can still be a target
   if (d == 1) {
     if (tid == 0) { diag[0] = A[0]; off[0] = 0.0; tau[0] = 0.0; }
   } else if ((d - 1) % cs == rank && tid == 0) {
@@ -792,7 +823,7 @@ void launch_eigh_topk(Ctx& c, double* dA, int d, int k, double* dW, double* dVt,
       long long h[32];
       DR4G_CUDA(cudaStreamSynchronize(c.stream));
       DR4G_CUDA(cudaMemcpyFromSymbol(h, g_tri_trace, sizeof(h)));
-      fprintf(stderr, "tridiag trace d=%d (cycles from step start): row_fetched pv_done nrm_done vn_done rows_done barrier_done\n", d);
+      fprintf(stderr, "tridiag trace d=%d (cycles from step start): operands_arrived pv_done nrm_done vn_done rows_done pushes_issued\n", d);
       for (int i = 0; i < 4; ++i) {
         fprintf(stderr, "  step %d:", 100 + i);
         for (int e = 1; e < 7; ++e) fprintf(stderr, " %6lld", h[i * 8 + e] - h[i * 8]);
