@@ -239,10 +239,14 @@ __device__ __forceinline__ void st_async_f64(double* local_ptr, uint64_t* local_
 }
 
 // Debug aid (DR4G_TRI_TRACE=1): clock64() of CTA 0, thread 0 at the phase boundaries of steps 100..103.
-__device__ long long g_tri_trace[4 * 8];
+__device__ long long g_tri_trace[4 * 16];
 #define TRI_TRACE(ev) \
-  do { if ((trace & 1) && rank == 0 && tid == 0 && s >= 100 && s < 104) g_tri_trace[(s - 100) * 8 + (ev)] = clock64(); } while (0)
+  do { if ((trace & 1) && rank == 0 && tid == 0 && s >= 100 && s < 104) g_tri_trace[(s - 100) * 16 + (ev)] = clock64(); } while (0)
 
+// REG: d <= 256 in a 16-CTA cluster -> at most two own rows per warp; they stay in registers (lane: columns
+// 2 lane + 64 j) with a fixed row -> warp assignment, because the rows phase was bound by shared-memory bandwidth
+// (7 x 512 B per warp and 64 columns: 224 cycles per iteration for the CTA; only w, v, v' remain: 96).
+template <bool REG>
 __global__ void __launch_bounds__(kTriThreads)
 tridiag_cluster_kernel(const double* __restrict__ A, int d, double* __restrict__ diag, double* __restrict__ off,
                        double* __restrict__ tau, double* __restrict__ Vh, double* __restrict__ xbuf, int trace) {
@@ -257,7 +261,7 @@ tridiag_cluster_kernel(const double* __restrict__ A, int d, double* __restrict__
   // data of step s+1 (p' and row s+1, 16 (d-s-1) bytes per CTA) lands in the parity-(s+1) buffers and is counted
   // on xbar[(s+1) & 1]: the consumer waits for the bytes, there is no cluster barrier inside the loop
   __shared__ __align__(8) uint64_t xbar[2];
-  unsigned xph[2] = {0u, 0u};
+  unsigned xph = 0u;   // bit b: phase parity of xbar[b]
   int par = 0;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int rank = (int)cluster_rank(), cs = (int)cluster_size();
@@ -273,9 +277,22 @@ tridiag_cluster_kernel(const double* __restrict__ A, int d, double* __restrict__
     rowp[c] = A[c];            // row 0
     rowp[d + c] = 0.0;
   }
-  for (int i = rank + cs * warp; i < d; i += cs * kTriWarps) {
-    double* Ri = R + (size_t)(i / cs) * d;
-    for (int c = lane; c < d; c += 32) Ri[c] = A[(size_t)i * d + c];
+  double2 rr[2][4];   // REG: slot q = warp + 8 k, columns 2 lane + 64 j
+  if constexpr (REG) {
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const int i = rank + cs * (warp + kTriWarps * k);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int c = 2 * lane + 64 * j;
+        rr[k][j] = (i < d && c < d) ? *reinterpret_cast<const double2*>(A + (size_t)i * d + c) : make_double2(0.0, 0.0);
+      }
+    }
+  } else {
+    for (int i = rank + cs * warp; i < d; i += cs * kTriWarps) {
+      double* Ri = R + (size_t)(i / cs) * d;
+      for (int c = lane; c < d; c += 32) Ri[c] = A[(size_t)i * d + c];
+    }
   }
   cluster_barrier();  // also orders the zero-initialisation of pl before any remote push
 
@@ -288,8 +305,8 @@ tridiag_cluster_kernel(const double* __restrict__ A, int d, double* __restrict__
     if (s > 0) {
       // wait for this step's operands (pushed by every CTA during its step s-1), then one CTA barrier: the own
       // rows in R are handed from warp to warp between steps
-      ptx::mbar_wait_cluster(ptx::smem_u32(&xbar[s & 1]), xph[s & 1]);
-      xph[s & 1] ^= 1u;
+      ptx::mbar_wait_cluster(ptx::smem_u32(&xbar[s & 1]), (xph >> (s & 1)) & 1u);
+      xph ^= 1u << (s & 1);
       __syncthreads();
     }
     const bool last = s == d - 2;      // nothing is exchanged after the last step
@@ -341,6 +358,61 @@ tridiag_cluster_kernel(const double* __restrict__ A, int d, double* __restrict__
     // own slots q (row i = rank + cs q) with i > s; qfirst advances with s (no division in the loop)
     while (rank + cs * qfirst <= s) ++qfirst;
     const int cbeg = (s + 1) & ~63;          // lanes take aligned pairs of columns: c = cbeg + 2 lane + 64 j
+    if constexpr (REG) {
+      const int i0 = rank + cs * warp, i1 = i0 + cs * kTriWarps;
+      const bool act0 = i0 > s && i0 < d, act1 = i1 > s && i1 < d;
+      if (act0 || act1) {                       // warp-uniform
+        const double vi0 = act0 ? v[i0] : 0.0, wi0 = act0 ? w[i0] : 0.0;
+        const double vi1 = act1 ? v[i1] : 0.0, wi1 = act1 ? w[i1] : 0.0;
+        double dot0 = 0.0, dot1 = 0.0;
+        const int jbeg = (s + 1) >> 6;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int c = 2 * lane + 64 * j;
+          if (j >= jbeg && c < d) {
+            const double2 wv = *reinterpret_cast<const double2*>(w + c);
+            const double2 vv = *reinterpret_cast<const double2*>(v + c);
+            const double2 nv = *reinterpret_cast<const double2*>(vn + c);
+            double2 a = rr[0][j], b = rr[1][j];
+            if (c > s) {
+              a.x = a.x - vi0 * wv.x - wi0 * vv.x;
+              b.x = b.x - vi1 * wv.x - wi1 * vv.x;
+              dot0 = fma(a.x, nv.x, dot0);
+              dot1 = fma(b.x, nv.x, dot1);
+            }
+            if (c + 1 > s) {
+              a.y = a.y - vi0 * wv.y - wi0 * vv.y;
+              b.y = b.y - vi1 * wv.y - wi1 * vv.y;
+              dot0 = fma(a.y, nv.y, dot0);
+              dot1 = fma(b.y, nv.y, dot1);
+            }
+            if (act0) rr[0][j] = a;
+            if (act1) rr[1][j] = b;
+          }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          dot0 += __shfl_xor_sync(0xffffffffu, dot0, o);
+          dot1 += __shfl_xor_sync(0xffffffffu, dot1, o);
+        }
+        if (lane < cs && !last) {
+          if (act0) st_async_f64(&pnext[i0], &xbar[(s + 1) & 1], (unsigned)lane, t * dot0);
+          if (act1) st_async_f64(&pnext[i1], &xbar[(s + 1) & 1], (unsigned)lane, t * dot1);
+        }
+      }
+      // the warp that holds row s+1 stages it in shared memory for the push below
+      if (rank == (owner + 1 == cs ? 0 : owner + 1) && !last) {
+        const int os = owner + 1 == cs ? oslot + 1 : oslot;     // slot of row s+1
+        if ((os & (kTriWarps - 1)) == warp) {
+          const bool hi = os >= kTriWarps;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int c = 2 * lane + 64 * j;
+            if (c < d) *reinterpret_cast<double2*>(R + c) = hi ? rr[1][j] : rr[0][j];
+          }
+        }
+      }
+    } else {
     // two own rows per pass (independent dot chains and shuffle trees; w, v, v' are loaded once)
     for (int q = qfirst + warp; q < nslots; q += 2 * kTriWarps) {
       const bool two = q + kTriWarps < nslots;
@@ -383,12 +455,13 @@ tridiag_cluster_kernel(const double* __restrict__ A, int d, double* __restrict__
         if (two) st_async_f64(&pnext[i1], &xbar[(s + 1) & 1], (unsigned)lane, t * dot1);
       }
     }
+    }
     tprev = t;
     if (++owner == cs) { owner = 0; ++oslot; }
     // the owner of row s+1 pushes it (columns > s) into every CTA of the cluster, all its threads sharing the stores
     if (owner == rank && !last) {
       __syncthreads();
-      const double* Rs = R + (size_t)oslot * d;
+      const double* Rs = REG ? R : R + (size_t)oslot * d;
       double* dst = rowp + (size_t)((s + 1) & 1) * d;
       for (int c = s + 1 + tid; c < d; c += kTriThreads) {
         const double val = Rs[c];
@@ -401,6 +474,18 @@ tridiag_cluster_kernel(const double* __restrict__ A, int d, double* __restrict__
   cluster_barrier();   // no CTA may exit while its shared memory can still be a target
   if (d == 1) {
     if (tid == 0) { diag[0] = A[0]; off[0] = 0.0; tau[0] = 0.0; }
+  } else if (REG) {
+    const int sl = d - 1, q = sl / cs;
+    if (sl % cs == rank && (q & (kTriWarps - 1)) == warp && lane == ((sl & 63) >> 1)) {
+      const int j = sl >> 6;
+      double2 e = make_double2(0.0, 0.0);
+#pragma unroll
+      for (int jj = 0; jj < 4; ++jj)
+        if (jj == j) e = q >= kTriWarps ? rr[1][jj] : rr[0][jj];
+      diag[sl] = (sl & 1) ? e.y : e.x;
+      off[sl] = 0.0;
+      tau[sl] = 0.0;
+    }
   } else if ((d - 1) % cs == rank && tid == 0) {
     const int s = d - 1;
     diag[s] = R[(size_t)(s / cs) * d + s];
@@ -798,11 +883,13 @@ void launch_eigh_topk(Ctx& c, double* dA, int d, int k, double* dW, double* dVt,
     static size_t smem_set = 0;
     static bool nonportable_set = false;
     if (smem > 48 * 1024 && smem > smem_set) {
-      DR4G_CUDA(cudaFuncSetAttribute(tridiag_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      DR4G_CUDA(cudaFuncSetAttribute(tridiag_cluster_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      DR4G_CUDA(cudaFuncSetAttribute(tridiag_cluster_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
       smem_set = smem;
     }
     if (cs > 8 && !nonportable_set) {
-      DR4G_CUDA(cudaFuncSetAttribute(tridiag_cluster_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+      DR4G_CUDA(cudaFuncSetAttribute(tridiag_cluster_kernel<false>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+      DR4G_CUDA(cudaFuncSetAttribute(tridiag_cluster_kernel<true>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
       nonportable_set = true;
     }
     cudaLaunchConfig_t cfg{};
@@ -818,16 +905,21 @@ void launch_eigh_topk(Ctx& c, double* dA, int d, int k, double* dW, double* dVt,
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     static const int tri_trace = getenv("DR4G_TRI_TRACE") ? atoi(getenv("DR4G_TRI_TRACE")) : 0;
-    DR4G_CUDA(cudaLaunchKernelEx(&cfg, tridiag_cluster_kernel, (const double*)dA, d, diag, off, tau, Vh, xbuf, tri_trace));
+    static const int no_reg = getenv("DR4G_TRI_NOREG") ? atoi(getenv("DR4G_TRI_NOREG")) : 0;
+    const bool reg = !no_reg && d <= 256 && (d + cs - 1) / cs <= 2 * kTriWarps;   // at most two own rows per warp
+    if (reg)
+      DR4G_CUDA(cudaLaunchKernelEx(&cfg, tridiag_cluster_kernel<true>, (const double*)dA, d, diag, off, tau, Vh, xbuf, tri_trace));
+    else
+      DR4G_CUDA(cudaLaunchKernelEx(&cfg, tridiag_cluster_kernel<false>, (const double*)dA, d, diag, off, tau, Vh, xbuf, tri_trace));
     if (tri_trace & 1) {
-      long long h[32];
+      long long h[64];
       DR4G_CUDA(cudaStreamSynchronize(c.stream));
       DR4G_CUDA(cudaMemcpyFromSymbol(h, g_tri_trace, sizeof(h)));
       fprintf(stderr, "tridiag trace d=%d (cycles from step start): operands_arrived pv_done nrm_done vn_done rows_done pushes_issued\n", d);
       for (int i = 0; i < 4; ++i) {
         fprintf(stderr, "  step %d:", 100 + i);
-        for (int e = 1; e < 7; ++e) fprintf(stderr, " %6lld", h[i * 8 + e] - h[i * 8]);
-        if (i < 3) fprintf(stderr, "  | next step starts at %6lld", h[(i + 1) * 8] - h[i * 8]);
+        for (int e = 1; e < 7; ++e) fprintf(stderr, " %6lld", h[i * 16 + e] - h[i * 16]);
+        if (i < 3) fprintf(stderr, "  | next step starts at %6lld", h[(i + 1) * 16] - h[i * 16]);
         fprintf(stderr, "\n");
       }
     }
