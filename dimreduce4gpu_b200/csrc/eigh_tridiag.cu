@@ -514,7 +514,7 @@ __device__ __forceinline__ int sturm_count(const double* __restrict__ dg, const 
   return cnt;
 }
 
-// One warp per wanted eigenvalue (j-th largest, j = blockIdx.x*warps + warp).  lam[j] descending.
+// One CTA (4 warps) per wanted eigenvalue (j-th largest, j = blockIdx.x).  lam[j] descending.
 // info[0] = ||T||_1-ish scale (max Gershgorin radius bound), written by warp 0 for T3.
 __global__ void __launch_bounds__(128)
 bisect_kernel(const double* __restrict__ diag, const double* __restrict__ off, int d, int k,
@@ -551,20 +551,23 @@ bisect_kernel(const double* __restrict__ diag, const double* __restrict__ off, i
   hi += 2.0 * DBL_EPSILON * tnorm * d + 2.0 * pivmin;
   if (blockIdx.x == 0 && tid == 0) { info[0] = tnorm; info[1] = pivmin; }
 
-  const int j = blockIdx.x * nwarp + warp;
+  const int j = blockIdx.x;   // one CTA per wanted eigenvalue
   if (j >= k) return;
   const int idx = d - 1 - j;  // 0-based index in ascending order: count(x) <= idx  <=>  x <= lambda_idx
-  // 128-section: 4 independent Sturm recurrences per lane (the divide latency is the cost of a pass).
-  // Stops at 1e-13 ||T||: T3 refines every value with the Rayleigh quotient of its vector.
+  // 4 blockDim-section (512 at 128 threads): 4 independent Sturm recurrences per thread (the reciprocal's latency
+  // is the cost of a pass; a pass narrows the interval 513-fold: 5 passes from the Gershgorin interval to
+  // 1e-13 ||T||, where one warp per eigenvalue needed 7).  T3 refines every value with the Rayleigh quotient.
+  __shared__ int s_first[4];
+  const int S = 4 * blockDim.x;
   const double atol = 1e-13 * tnorm + 2.0 * pivmin;
   for (int it = 0; it < 12; ++it) {
     const double width = hi - lo;
-    if (!(width > atol)) break;
+    if (!(width > atol)) break;   // CTA-uniform: lo, hi are identical in every thread
     double x[4], q[4];
     int cnt[4];
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
-      x[u] = lo + width * (double)(4 * lane + u + 1) / 129.0;
+      x[u] = lo + width * (double)(4 * tid + u + 1) / (double)(S + 1);
       q[u] = dg[0] - x[u];
       if (fabs(q[u]) < pivmin) q[u] = -pivmin;
       cnt[u] = q[u] < 0.0;
@@ -584,13 +587,17 @@ bisect_kernel(const double* __restrict__ diag, const double* __restrict__ off, i
     const unsigned m = __ballot_sync(0xffffffffu, fl < 4);
     const int lane1 = m ? __ffs(m) - 1 : 0;
     const int u1 = __shfl_sync(0xffffffffu, fl, lane1);
-    const int first = m ? lane1 * 4 + u1 : 128;
-    const double nlo = first == 0 ? lo : lo + width * (double)first / 129.0;
-    const double nhi = first == 128 ? hi : lo + width * (double)(first + 1) / 129.0;
+    if (lane == 0) s_first[warp] = m ? warp * 128 + lane1 * 4 + u1 : S;
+    __syncthreads();
+    int first = S;
+    for (int i = 0; i < nwarp; ++i) first = min(first, s_first[i]);
+    __syncthreads();
+    const double nlo = first == 0 ? lo : lo + width * (double)first / (double)(S + 1);
+    const double nhi = first == S ? hi : lo + width * (double)(first + 1) / (double)(S + 1);
     lo = nlo;
     hi = nhi;
   }
-  if (lane == 0) lam[j] = 0.5 * (lo + hi);
+  if (tid == 0) lam[j] = 0.5 * (lo + hi);
 }
 
 // ---------------------------------------------------------------- T3: eigenvectors by inverse iteration
@@ -847,6 +854,106 @@ backtransform_warp_kernel(const double* __restrict__ Vh, const double* __restric
   }
 }
 
+// T4 for d <= 256: one warp per vector, TWO reflectors per shuffle tree.  With a = v_s.z, b = v_{s-1}.z and
+// g = v_{s-1}.v_s reduced together, H_{s-1} H_s z = z - ca v_s - cb v_{s-1}, ca = tau_s a, cb = tau_{s-1} (b - ca g).
+// The single-reflector kernel above spent ~560 cycles per reflector (an 8-long dependent dot, a 5-level shuffle
+// tree, and an L2 fetch only one step ahead); this one prefetches two pairs ahead (three register sets in rotation).
+template <int PER>
+struct ReflPair {
+  double a[PER], b[PER];
+  double ta, tb;
+};
+
+template <int PER>
+__global__ void __launch_bounds__(128)
+backtransform_pair_kernel(const double* __restrict__ Vh, const double* __restrict__ tau, int d, int k,
+                          double* __restrict__ Z) {
+  const int lane = threadIdx.x & 31, j = blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (j >= k) return;
+  double z[PER];
+#pragma unroll
+  for (int u = 0; u < PER; ++u) {
+    const int i = lane + 32 * u;
+    z[u] = i < d ? Z[(size_t)j * d + i] : 0.0;
+  }
+  int s = d - 3;   // next reflector to apply (H_s, s = d-3 ... 0)
+  if (s >= 0 && ((d - 2) & 1)) {   // odd count: one single reflector first
+    const double* vr = Vh + (size_t)s * d;
+    double cur[PER], dot = 0.0;
+#pragma unroll
+    for (int u = 0; u < PER; ++u) {
+      const int i = lane + 32 * u;
+      cur[u] = (i > s && i < d) ? __ldg(&vr[i]) : 0.0;
+      dot = fma(cur[u], z[u], dot);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
+    dot *= __ldg(&tau[s]);
+#pragma unroll
+    for (int u = 0; u < PER; ++u) z[u] = fma(-dot, cur[u], z[u]);
+    --s;
+  }
+  auto fetch = [&](ReflPair<PER>& P, int sp) {   // reflectors sp and sp-1
+    if (sp < 1) return;
+    const double* va = Vh + (size_t)sp * d;
+    const double* vb = va - d;
+#pragma unroll
+    for (int u = 0; u < PER; ++u) {
+      const int i = lane + 32 * u;
+      P.a[u] = (i > sp && i < d) ? __ldg(&va[i]) : 0.0;
+      P.b[u] = (i > sp - 1 && i < d) ? __ldg(&vb[i]) : 0.0;
+    }
+    P.ta = __ldg(&tau[sp]);
+    P.tb = __ldg(&tau[sp - 1]);
+  };
+  auto apply = [&](const ReflPair<PER>& P) {
+    double a0 = 0.0, a1 = 0.0, b0 = 0.0, b1 = 0.0, g0 = 0.0, g1 = 0.0;
+#pragma unroll
+    for (int u = 0; u < PER; u += 2) {
+      a0 = fma(P.a[u], z[u], a0);
+      b0 = fma(P.b[u], z[u], b0);
+      g0 = fma(P.a[u], P.b[u], g0);
+      if (u + 1 < PER) {
+        a1 = fma(P.a[u + 1], z[u + 1], a1);
+        b1 = fma(P.b[u + 1], z[u + 1], b1);
+        g1 = fma(P.a[u + 1], P.b[u + 1], g1);
+      }
+    }
+    double a = a0 + a1, b = b0 + b1, g = g0 + g1;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      a += __shfl_xor_sync(0xffffffffu, a, o);
+      b += __shfl_xor_sync(0xffffffffu, b, o);
+      g += __shfl_xor_sync(0xffffffffu, g, o);
+    }
+    const double ca = P.ta * a;
+    const double cb = P.tb * fma(-ca, g, b);
+#pragma unroll
+    for (int u = 0; u < PER; ++u) z[u] = fma(-cb, P.b[u], fma(-ca, P.a[u], z[u]));
+  };
+  ReflPair<PER> P0, P1, P2;
+  fetch(P0, s);
+  fetch(P1, s - 2);
+  while (s >= 1) {
+    fetch(P2, s - 4);
+    apply(P0);
+    s -= 2;
+    if (s < 1) break;
+    fetch(P0, s - 4);
+    apply(P1);
+    s -= 2;
+    if (s < 1) break;
+    fetch(P1, s - 4);
+    apply(P2);
+    s -= 2;
+  }
+#pragma unroll
+  for (int u = 0; u < PER; ++u) {
+    const int i = lane + 32 * u;
+    if (i < d) Z[(size_t)j * d + i] = z[u];
+  }
+}
+
 }  // namespace
 
 // ---------------------------------------------------------------- host side
@@ -948,7 +1055,7 @@ void launch_eigh_topk(Ctx& c, double* dA, int d, int k, double* dW, double* dVt,
     DR4G_CUDA(cudaFuncSetAttribute(bisect_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bs_smem));
     bs_smem_set = bs_smem;
   }
-  bisect_kernel<<<(k + 3) / 4, 128, bs_smem, c.stream>>>(diag, off, d, k, lam, info);
+  bisect_kernel<<<k, 128, bs_smem, c.stream>>>(diag, off, d, k, lam, info);
   // T3
   const size_t iv_smem = (size_t)5 * d * sizeof(double) + (size_t)d * sizeof(int);
   static size_t iv_smem_set = 0;
@@ -959,7 +1066,7 @@ void launch_eigh_topk(Ctx& c, double* dA, int d, int k, double* dW, double* dVt,
   invit_kernel<<<k, kInvThreads, iv_smem, c.stream>>>(diag, off, d, k, lam, info, dW, dVt);
   // T4
   const size_t bt_smem = (size_t)d * sizeof(double);
-  if (d <= 256) backtransform_warp_kernel<8><<<(k + 3) / 4, 128, 0, c.stream>>>(Vh, tau, d, k, dVt);
+  if (d <= 256) backtransform_pair_kernel<8><<<(k + 3) / 4, 128, 0, c.stream>>>(Vh, tau, d, k, dVt);
   else if (d <= 512) backtransform_warp_kernel<16><<<(k + 3) / 4, 128, 0, c.stream>>>(Vh, tau, d, k, dVt);
   else backtransform_kernel<<<k, 256, bt_smem, c.stream>>>(Vh, tau, d, k, dVt);
   c.launches += 4;
