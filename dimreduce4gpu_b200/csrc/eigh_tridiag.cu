@@ -641,7 +641,9 @@ invit_kernel(const double* __restrict__ diag, const double* __restrict__ off, in
   double* c = b + d;        // multipliers
   double* d2 = c + d;       // U second super-diagonal
   double* z = d2 + d;       // iterate
-  int* piv = reinterpret_cast<int*>(z + d);
+  double* dg0 = z + d;      // diag - x (read-only during the factorisation)
+  double* of0 = dg0 + d;    // off
+  int* piv = reinterpret_cast<int*>(of0 + d);
   __shared__ double red[kInvThreads / 32];
   const int tid = threadIdx.x;
   const double eps = DBL_EPSILON;
@@ -653,50 +655,72 @@ invit_kernel(const double* __restrict__ diag, const double* __restrict__ off, in
     double x = lam[j];
     if (j > j0 && prev - x < 10.0 * eps * tnorm) x = prev - 10.0 * eps * tnorm;
     prev = x;
-    // ---- factor T - x I = P L U (partial pivoting), sequential; a[] ends up holding 1 / pivot
+    // ---- factor T - x I = P L U (partial pivoting), sequential; a[] ends up holding 1 / pivot.  The running
+    // diagonal / super-diagonal entries are carried in registers (a shared-memory store -> load round trip per
+    // step was most of the chain); the inputs come from read-only copies so their loads can run ahead.
+    for (int i = tid; i < d; i += kInvThreads) {
+      dg0[i] = diag[i] - x;
+      of0[i] = i < d - 1 ? off[i] : 0.0;
+      z[i] = hash_uniform((unsigned)i, (unsigned)j * 7919u + 13u);
+    }
+    __syncthreads();
     if (tid == 0) {
-      for (int i = 0; i < d; ++i) { a[i] = diag[i] - x; b[i] = i < d - 1 ? off[i] : 0.0; c[i] = b[i]; d2[i] = 0.0; }
+      const double* __restrict__ dgr = dg0;
+      const double* __restrict__ ofr = of0;
+      double ai = dgr[0], bi = ofr[0];
       for (int i = 0; i < d - 1; ++i) {
-        if (fabs(a[i]) >= fabs(c[i]) || fabs(c[i]) < tiny) {
-          double pv = a[i];
+        const double ci = ofr[i];
+        const double an = dgr[i + 1], bn = ofr[i + 1];   // of0[d-1] = 0
+        if (fabs(ai) >= fabs(ci) || fabs(ci) < tiny) {
+          double pv = ai;
           if (fabs(pv) < tiny) pv = pv < 0 ? -tiny : tiny;
           const double ip = fast_rcp(pv);
-          const double m = c[i] * ip;
+          const double m = ci * ip;
           a[i] = ip;
-          a[i + 1] -= m * b[i];
+          b[i] = bi;
+          d2[i] = 0.0;
           c[i] = m;
           piv[i] = 0;
+          ai = fma(-m, bi, an);
+          bi = bn;
         } else {
-          const double ip = fast_rcp(c[i]);
-          const double m = a[i] * ip;
+          const double ip = fast_rcp(ci);
+          const double m = ai * ip;
           a[i] = ip;
-          const double t = a[i + 1];
-          a[i + 1] = b[i] - m * t;
-          if (i < d - 2) { d2[i] = b[i + 1]; b[i + 1] = -m * d2[i]; }
-          b[i] = t;
+          b[i] = an;
+          d2[i] = i < d - 2 ? bn : 0.0;
           c[i] = m;
           piv[i] = 1;
+          ai = fma(-m, an, bi);
+          bi = i < d - 2 ? -m * bn : 0.0;
         }
       }
-      double pv = a[d - 1];
+      double pv = ai;
       if (fabs(pv) < tiny) pv = pv < 0 ? -tiny : tiny;
       a[d - 1] = fast_rcp(pv);
+      b[d - 1] = 0.0;
+      d2[d - 1] = 0.0;
+      c[d - 1] = 0.0;
     }
-    for (int i = tid; i < d; i += kInvThreads) z[i] = hash_uniform((unsigned)i, (unsigned)j * 7919u + 13u);
     __syncthreads();
     for (int iter = 0; iter < 3; ++iter) {
       if (tid == 0) {
         if (iter > 0) {  // apply P, L to the right-hand side (the first solve uses U only, as dstein does)
+          double zi = z[0];
           for (int i = 0; i < d - 1; ++i) {
-            if (piv[i] == 0) z[i + 1] -= c[i] * z[i];
-            else { const double t = z[i]; z[i] = z[i + 1]; z[i + 1] = t - c[i] * z[i]; }
+            const double zn = z[i + 1];
+            if (piv[i] == 0) { z[i] = zi; zi = fma(-c[i], zi, zn); }
+            else { z[i] = zn; zi = fma(-c[i], zn, zi); }
           }
+          z[d - 1] = zi;
         }
+        double z1 = 0.0, z2 = 0.0;   // z[i+1], z[i+2]; b[d-1] = d2[d-1] = d2[d-2] = 0
         for (int i = d - 1; i >= 0; --i) {  // U z = y
-          double t = z[i];
-          if (i < d - 1) t -= b[i] * z[i + 1];
-          if (i < d - 2) t -= d2[i] * z[i + 2];
-          z[i] = t * a[i];
+          const double t = fma(-d2[i], z2, fma(-b[i], z1, z[i]));
+          const double zi = t * a[i];
+          z[i] = zi;
+          z2 = z1;
+          z1 = zi;
         }
       }
       __syncthreads();
@@ -1057,7 +1081,7 @@ void launch_eigh_topk(Ctx& c, double* dA, int d, int k, double* dW, double* dVt,
   }
   bisect_kernel<<<k, 128, bs_smem, c.stream>>>(diag, off, d, k, lam, info);
   // T3
-  const size_t iv_smem = (size_t)5 * d * sizeof(double) + (size_t)d * sizeof(int);
+  const size_t iv_smem = (size_t)7 * d * sizeof(double) + (size_t)d * sizeof(int);
   static size_t iv_smem_set = 0;
   if (iv_smem > 48 * 1024 && iv_smem > iv_smem_set) {
     DR4G_CUDA(cudaFuncSetAttribute(invit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)iv_smem));
