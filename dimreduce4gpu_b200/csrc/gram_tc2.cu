@@ -470,24 +470,61 @@ reduce_pair_slabs_kernel(const __grid_constant__ PJobTable table, const float* _
   const int m = (int)blockIdx.y, nn = (int)threadIdx.x;
   const int ga = (2 * job.I + r) * kBlk + m, gb = job.cb[j] * kBlk + nn;
   if (ga >= d || gb >= d) return;
+  const size_t cta_stride = 2 * (size_t)kSlabFloats;   // next cluster, same rank
+  const float* p = slab + ((size_t)(job.cl_begin * 2 + r)) * kSlabFloats + ((size_t)j * kBlk + m) * 256 + nn;
+  // fixed summation order (deterministic), eight loads in flight
+  auto sum_plane = [&](const float* q) {
+    double acc = 0.0;
+    int c = 0;
+    for (; c + 8 <= active; c += 8) {
+      float v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) v[u] = q[(size_t)(c + u) * cta_stride];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) acc += (double)v[u];
+    }
+    for (; c < active; ++c) acc += (double)q[(size_t)c * cta_stride];
+    return acc;
+  };
+  if (job.diag) {
+    // plane 0 = P = hi^T hi, plane 1 = R = hi^T lo, G = P + R + R^T.  Written here: M = P / 2 + R for EVERY (a, b) of
+    // the super-tile (coalesced); symmetrize_diag_kernel then forms G = M + M^T (exactly symmetric).  Reading
+    // R[b][a] here instead cost a 32-byte sector per 4 useful bytes, 74 times per element.
+    G[(size_t)ga * d + gb] = 0.5 * sum_plane(p) + sum_plane(p + (size_t)kBlk * 256);
+    return;
+  }
   // the diagonal chunk holds both (a, b) and (b, a), accumulated in different orders: keep the
   // upper one so that G is exactly symmetric
   if (gb < ga) return;
-  const size_t cta_stride = 2 * (size_t)kSlabFloats;   // next cluster, same rank
-  const float* p = slab + ((size_t)(job.cl_begin * 2 + r)) * kSlabFloats + ((size_t)j * kBlk + m) * 256 + nn;
-  double acc = 0.0;
-  for (int c = 0; c < active; ++c) acc += (double)p[(size_t)c * cta_stride];
-  if (job.diag) {
-    // plane 0 = P = hi^T hi (+ nothing else), plane 1 = R = hi^T lo:  G = P + R + R^T
-    const float* q = p + (size_t)kBlk * 256;   // R[a][b]
-    const int rb = nn >> 7, mb = nn & (kBlk - 1), na = r * kBlk + m;   // (b, a) inside the 256 x 256 super-tile
-    const float* qt = slab + ((size_t)(job.cl_begin * 2 + rb)) * kSlabFloats + ((size_t)kBlk + mb) * 256 + na;  // R[b][a]
-    double racc = 0.0;
-    for (int c = 0; c < active; ++c) racc += (double)q[(size_t)c * cta_stride] + (double)qt[(size_t)c * cta_stride];
-    acc += racc;
-  }
+  const double acc = sum_plane(p);
   G[(size_t)ga * d + gb] = acc;
   G[(size_t)gb * d + ga] = acc;
+}
+
+// G = M + M^T on the 256 x 256 diagonal super-tiles, in place: block (pair of 32 x 32 tiles (ti, tj), ti <= tj; I).
+__global__ void __launch_bounds__(256)
+symmetrize_diag_kernel(double* __restrict__ G, int d) {
+  __shared__ double A[32][33], B[32][33];
+  int t = (int)blockIdx.x, ti = 0;
+  while (t >= 8 - ti) { t -= 8 - ti; ++ti; }   // 36 pairs: ti = 0..7, tj = ti..7
+  const int tj = ti + t;
+  const int base = (int)blockIdx.y * 256;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  for (int rr = ty; rr < 32; rr += 8) {
+    const int a = base + ti * 32 + rr, b = base + tj * 32 + tx;        // M[a][b]
+    A[rr][tx] = (a < d && b < d) ? G[(size_t)a * d + b] : 0.0;
+    const int a2 = base + tj * 32 + rr, b2 = base + ti * 32 + tx;      // M[b'][a'] tile
+    B[rr][tx] = (a2 < d && b2 < d) ? G[(size_t)a2 * d + b2] : 0.0;
+  }
+  __syncthreads();
+  for (int rr = ty; rr < 32; rr += 8) {
+    const int a = base + ti * 32 + rr, b = base + tj * 32 + tx;
+    if (a < d && b < d) G[(size_t)a * d + b] = A[rr][tx] + B[tx][rr];
+    if (ti != tj) {
+      const int a2 = base + tj * 32 + rr, b2 = base + ti * 32 + tx;
+      if (a2 < d && b2 < d) G[(size_t)a2 * d + b2] = A[tx][rr] + B[rr][tx];
+    }
+  }
 }
 
 }  // namespace
@@ -656,6 +693,8 @@ void launch_gram_pair(Ctx& c, const float* dX, long long n, int d, const float* 
     }
   }
   reduce_pair_slabs_kernel<<<dim3(tab.njobs * 4, kBlk), 256, 0, c.stream>>>(tab, slab, n, d, dG);
+  symmetrize_diag_kernel<<<dim3(36, (d + 255) / 256), 256, 0, c.stream>>>(dG, d);
+  c.launches++;
   c.launches++;
   DR4G_CUDA(cudaGetLastError());
 }
