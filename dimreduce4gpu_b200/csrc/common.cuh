@@ -154,6 +154,17 @@ void launch_project(Ctx& c, const T* dX, long long n, int d, int k, const T* dQ,
 template <typename T>
 void launch_inverse(Ctx& c, const T* dZ, long long n, int d, int k, const T* dQ, const T* dmean, T* dX);
 
+// cudaFuncSetAttribute acts on the current device only: a call site remembers, per device, the largest dynamic
+// shared-memory size it has requested (a per-process flag broke the second device of a process).
+struct PerDeviceMax {
+  size_t v[64] = {};
+  bool need(int device, size_t want) {
+    if (device < 0 || device >= 64) return true;
+    if (want > v[device]) { v[device] = want; return true; }
+    return false;
+  }
+};
+
 inline int ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }
 
 }  // namespace dr4g

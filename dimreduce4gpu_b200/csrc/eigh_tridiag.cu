@@ -1011,17 +1011,14 @@ void launch_eigh_topk(Ctx& c, double* dA, int d, int k, double* dW, double* dVt,
     static const int cs_env = getenv("DR4G_TRI_CS") ? atoi(getenv("DR4G_TRI_CS")) : 0;  // tuning hook
     const int cs = cs_env > 0 ? cs_env : (d <= 128 ? 1 : 16);  // 16 beats 8 at d = 256 (1.16 vs 1.28 ms, measured)
     const size_t smem = ((size_t)7 * d + (size_t)((d + cs - 1) / cs) * d) * sizeof(double);
-    static size_t smem_set = 0;
-    static bool nonportable_set = false;
-    if (smem > 48 * 1024 && smem > smem_set) {
+    static PerDeviceMax smem_set, nonportable_set;
+    if (smem > 48 * 1024 && smem_set.need(c.device, smem)) {
       DR4G_CUDA(cudaFuncSetAttribute(tridiag_cluster_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
       DR4G_CUDA(cudaFuncSetAttribute(tridiag_cluster_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      smem_set = smem;
     }
-    if (cs > 8 && !nonportable_set) {
+    if (cs > 8 && nonportable_set.need(c.device, 1)) {
       DR4G_CUDA(cudaFuncSetAttribute(tridiag_cluster_kernel<false>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
       DR4G_CUDA(cudaFuncSetAttribute(tridiag_cluster_kernel<true>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
-      nonportable_set = true;
     }
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(cs);
@@ -1064,29 +1061,23 @@ void launch_eigh_topk(Ctx& c, double* dA, int d, int k, double* dW, double* dVt,
     const bool in_smem = vec_smem + rows_smem <= 200 * 1024;
     const size_t tri_smem = vec_smem + (in_smem ? rows_smem : 0);
     const void* tri_fn = in_smem ? (const void*)tridiag_kernel<true> : (const void*)tridiag_kernel<false>;
-    static size_t tri_smem_set[2] = {0, 0};
-    if (tri_smem > 48 * 1024 && tri_smem > tri_smem_set[in_smem]) {
+    static PerDeviceMax tri_smem_set[2];
+    if (tri_smem > 48 * 1024 && tri_smem_set[in_smem].need(c.device, tri_smem))
       DR4G_CUDA(cudaFuncSetAttribute(tri_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tri_smem));
-      tri_smem_set[in_smem] = tri_smem;
-    }
     void* args[] = {&dA, &d, &diag, &off, &tau, &Vh, &xbuf, &ctrl};
     DR4G_CUDA(cudaLaunchCooperativeKernel(tri_fn, dim3(grid), dim3(kTriThreads), args, tri_smem, c.stream));
   }
   // T2
   const size_t bs_smem = (size_t)2 * d * sizeof(double);
-  static size_t bs_smem_set = 0;
-  if (bs_smem > 48 * 1024 && bs_smem > bs_smem_set) {
+  static PerDeviceMax bs_smem_set;
+  if (bs_smem > 48 * 1024 && bs_smem_set.need(c.device, bs_smem))
     DR4G_CUDA(cudaFuncSetAttribute(bisect_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bs_smem));
-    bs_smem_set = bs_smem;
-  }
   bisect_kernel<<<k, 128, bs_smem, c.stream>>>(diag, off, d, k, lam, info);
   // T3
   const size_t iv_smem = (size_t)7 * d * sizeof(double) + (size_t)d * sizeof(int);
-  static size_t iv_smem_set = 0;
-  if (iv_smem > 48 * 1024 && iv_smem > iv_smem_set) {
+  static PerDeviceMax iv_smem_set;
+  if (iv_smem > 48 * 1024 && iv_smem_set.need(c.device, iv_smem))
     DR4G_CUDA(cudaFuncSetAttribute(invit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)iv_smem));
-    iv_smem_set = iv_smem;
-  }
   invit_kernel<<<k, kInvThreads, iv_smem, c.stream>>>(diag, off, d, k, lam, info, dW, dVt);
   // T4
   const size_t bt_smem = (size_t)d * sizeof(double);

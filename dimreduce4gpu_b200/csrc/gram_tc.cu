@@ -460,13 +460,10 @@ void launch_gram_tc(Ctx& c, const float* dX, long long n, int d, const float* ds
                                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) fail("cuTensorMapEncodeTiled failed (%d) for n=%lld d=%d", (int)r, n, d);
 
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
   const int smem = kStages * kStageBytes + 1024;
-  std::call_once(once, [&] {
-    attr_err = cudaFuncSetAttribute(gram_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-  });
-  DR4G_CUDA(attr_err);
+  static PerDeviceMax smem_set;
+  if (smem_set.need(c.device, (size_t)smem))
+    DR4G_CUDA(cudaFuncSetAttribute(gram_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
 
   const int flush_rows = c.flush_rows > 0 ? c.flush_rows : 1024;
   const int grid = tab.job[tab.njobs - 1].cta_begin + tab.job[tab.njobs - 1].ncta;

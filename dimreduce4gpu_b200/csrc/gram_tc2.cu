@@ -653,13 +653,10 @@ void launch_gram_pair(Ctx& c, const float* dX, long long n, int d, const float* 
       CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) fail("cuTensorMapEncodeTiled (3-D) failed (%d) for n=%lld d=%d", (int)r, n, d);
 
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
   const int smem = kRingBytes + 1024;
-  std::call_once(once, [&] {
-    attr_err = cudaFuncSetAttribute(gram_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-  });
-  DR4G_CUDA(attr_err);
+  static PerDeviceMax smem_set;
+  if (smem_set.need(c.device, (size_t)smem))
+    DR4G_CUDA(cudaFuncSetAttribute(gram_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
 
   static const int trace = getenv("DR4G_GRAM_TRACE") ? atoi(getenv("DR4G_GRAM_TRACE")) : 0;  // bit 0 trace (CTA = value >> 8), 2 no MMA, 4 no conversion
   const int flush_rows = c.flush_rows > 0 ? c.flush_rows : 1024;

@@ -453,11 +453,10 @@ static void cholqr2(Ctx& c, PowerWs& w, int d, int l, const int* done) {
   constexpr int kRegP = 10, kRegQ = 3;           // register-resident factorisation up to l = 80
   const bool reg = l <= 8 * kRegP && l <= 32 * kRegQ;
   const size_t smem = reg ? chol_bytes(l) + (size_t)(2 * 32 * kRegQ + l) * 8 : (w.chol_scratch ? 0 : chol_bytes(l));
-  static size_t smem_set[2] = {0, 0};
-  if (smem > 48 * 1024 && smem > smem_set[reg]) {
+  static PerDeviceMax smem_set[2];
+  if (smem > 48 * 1024 && smem_set[reg].need(c.device, smem)) {
     if (reg) DR4G_CUDA(cudaFuncSetAttribute(chol_inv_reg_kernel<kRegP, kRegQ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     else DR4G_CUDA(cudaFuncSetAttribute(chol_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    smem_set[reg] = smem;
   }
   const int splits = std::max(1, std::min(kSplits, d / 64));
   for (int pass = 0; pass < 2; ++pass) {

@@ -243,11 +243,9 @@ void launch_project_f32(Ctx& c, const float* dX, long long n, int d, int k, cons
                         const float* dw, float* dZ, float* dU) {
   constexpr int RT = 8192 / KP;
   const size_t smem = (size_t)2 * 32 * (RT + KP) * sizeof(float);
-  static bool set = false;
-  if (!set) {
+  static PerDeviceMax smem_set;
+  if (smem_set.need(c.device, smem))
     DR4G_CUDA(cudaFuncSetAttribute(project_f32_kernel<KP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    set = true;
-  }
   const long long blocks = (n + RT - 1) / RT;
   project_f32_kernel<KP><<<(unsigned)blocks, 256, smem, c.stream>>>(dX, n, d, k, dmean, dQ, (dU && dw) ? dw : nullptr,
                                                                    dZ, (dU && dw) ? dU : nullptr);

@@ -73,20 +73,28 @@ def main() -> None:
 
     import dimreduce4gpu_b200 as pkg
 
+    def progress(msg):   # shows where a hang is when the launcher's timeout fires
+        print(f"[rank {rank}] {msg}", file=sys.stderr, flush=True)
+
     local = int(os.environ.get("LOCAL_RANK", rank))
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     ctx = pkg.DeviceContext(local)
     ctx.init_comm_from_torch()
+    progress("communicator up")
     Xg = torch.from_numpy(X).cuda()
     out = {}
+    Z = None
     for alg in ("cusolver", "power"):
         res = ctx.fit(Xg, k, center=True, algorithm=alg, n_iter=60, random_state=3, tol=1e-9)
         ctx.sync()
         out[alg] = {kk: v.cpu().numpy() for kk, v in res.items() if v is not None}
-    Z = ctx.transform(Xg, res["components"], mean=res["mean"]).cpu().numpy()
+        if alg == "cusolver":   # shard-local scores of the exact model (the flat spectrum leaves 'power' a rotated basis)
+            Z = ctx.transform(Xg, res["components"], mean=res["mean"]).cpu().numpy()
+        progress(f"sharded fit {alg} done")
     # streaming fit across ranks: every rank feeds its shard in two chunks (the first call carries the pilot
     # allreduce), finalize all-reduces the packed accumulators: same model as the one-pass sharded fit
+    progress("transform done")
     ctx.partial_fit_reset()
     half = n_local // 2
     ctx.partial_fit(Xg[:half].contiguous(), center=True)
@@ -96,6 +104,7 @@ def main() -> None:
     sp, so = part["singular_values"].cpu().numpy(), out["cusolver"]["singular_values"]
     assert np.max(np.abs(sp - so) / so) < 2e-5, "streaming sharded fit differs from the one-pass sharded fit"
     assert float((part["mean"].cpu() - torch.from_numpy(out["cusolver"]["mean"])).abs().max()) < 1e-5
+    progress("streaming fit done")
     # every rank must hold the same model (replicated eigensolve on identical all-reduced inputs)
     mine = torch.from_numpy(out["cusolver"]["components"]).cuda()
     ref0 = mine.clone()
@@ -103,9 +112,11 @@ def main() -> None:
     assert torch.equal(mine, ref0), "ranks disagree on components_"
     gathered = [None] * world
     dist.all_gather_object(gathered, X)
+    progress("gathered")
     if rank == 0:
         Xall = np.concatenate(gathered)
         ref = O.RefLib().pca(Xall, k, "cusolver") if O.REF_SO.is_file() else O.restated_pca(Xall, k)
+        progress("oracle done")
         single = pkg.DeviceContext(local)
         one = single.fit(torch.from_numpy(Xall).cuda(), k, center=True)
         single.sync()
@@ -127,4 +138,11 @@ def main() -> None:
 
 
 if __name__ == "__main__":
-    main()
+    try:
+        main()
+    except BaseException:   # a failed rank must not leave its peer spinning in a collective until the launcher's timeout
+        import traceback
+
+        traceback.print_exc()
+        sys.stderr.flush()
+        os._exit(1)

@@ -134,3 +134,30 @@ def test_legacy_symbols_out_of_core(kind, n, d, k, rows, monkeypatch):
     assert _rel(est2.singular_values_, est.singular_values_) < 1e-5
     assert float(np.max(np.abs(np.abs(Z2) - np.abs(Z)))) < 1e-3 * float(est.singular_values_[0])
     assert os.environ.get("DR4G_STREAM_ROWS") is None
+
+
+def test_second_device_in_the_same_process():
+    """cudaFuncSetAttribute is per device: a second GPU used by the same process must get its own opt-ins
+    (dynamic shared memory above 48 KB, cluster size 16).  Needs two visible GPUs."""
+    import torch
+
+    import dimreduce4gpu_b200 as pkg
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    X0 = torch.from_numpy(_data(6000, 256, 3)).cuda(0)
+    r0 = pkg.DeviceContext(0).fit(X0, 16, center=True)
+    torch.cuda.synchronize(0)
+    with torch.cuda.device(1):
+        X1 = X0.to("cuda:1")
+        c1 = pkg.DeviceContext(1)
+        r1 = c1.fit(X1, 16, center=True)
+        Z1 = c1.transform(X1, r1["components"], mean=r1["mean"])
+        rp = c1.fit(X1, 16, center=False, algorithm="power")
+        c1.sync()
+    assert Z1.shape == (6000, 16) and rp["singular_values"].shape == (16,)
+    assert torch.equal(r0["singular_values"].cpu(), r1["singular_values"].cpu())
+    # and through the legacy symbol with gpu_id = 1
+    est = pkg.PCA(n_components=8, backend="gpu", gpu_id=1)
+    Zh = est.fit_transform(_data(3000, 256, 4))
+    assert Zh.shape == (3000, 8) and np.isfinite(Zh).all()

@@ -37,5 +37,5 @@ def test_two_gpus_nccl_sharded_fit_matches_reference():
 
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs on the box")
-    out = _launch("gpu", 40000, 256, 16, 600)
+    out = _launch("gpu", 40000, 256, 16, 240)
     assert "MULTIRANK_GPU_OK" in out
