@@ -369,22 +369,27 @@ static void partial_fit_finalize_impl(CtxFull& c, int k, const params& p, T* dQ,
 // (partial fit), then the eigensolve; [2] H2D again, projection, D2H of the scores (third stream), all three
 // overlapped through two chunk buffers.  Device footprint: 2 chunks of X and of the two score matrices.
 template <typename T>
-static void legacy_out_of_core(CtxFull& c, bool is_pca, const T* X, long long n, int d, int k, long long chunk,
-                               const params& p, T* Q, T* w, T* U, T* Xt, T* ev, T* evr, T* mean) {
+static void legacy_pipelined(CtxFull& c, bool is_pca, bool resident, const T* X, long long n, int d, int k, long long chunk,
+                             const params& p, T* Q, T* w, T* U, T* Xt, T* ev, T* evr, T* mean) {
+  // resident: the chunks land in one device copy of X (one H2D sweep; the pass on chunk i runs under the copy of
+  // chunk i+1, the D2H of the scores of chunk i under the projection of chunk i+1); else two chunk buffers.
   if (!c.copy_stream) DR4G_CUDA(cudaStreamCreateWithFlags(&c.copy_stream, cudaStreamNonBlocking));
   if (!c.out_stream) DR4G_CUDA(cudaStreamCreateWithFlags(&c.out_stream, cudaStreamNonBlocking));
-  const size_t cx = (size_t)chunk * d * sizeof(T), cz = (size_t)chunk * k * sizeof(T);
-  c.io.reserve(2 * up256(cx) + 4 * up256(cz) + up256((size_t)k * d * sizeof(T)) + 3 * up256((size_t)k * sizeof(T)) +
-               up256((size_t)d * sizeof(T)) + 4096);
+  const size_t cx = (size_t)(resident ? n : 2 * chunk) * d * sizeof(T), cz = (size_t)(resident ? n : 2 * chunk) * k * sizeof(T);
+  c.io.reserve(up256(cx) + 2 * up256(cz) + up256((size_t)k * d * sizeof(T)) + 3 * up256((size_t)k * sizeof(T)) +
+               up256((size_t)d * sizeof(T)) + 8192);
   c.io.reset();
   T* dQ = c.io.take_n<T>((size_t)k * d);
   T* dw = c.io.take_n<T>(k);
   T* dev = c.io.take_n<T>(k);
   T* devr = c.io.take_n<T>(k);
   T* dmean = c.io.take_n<T>(d);
-  T* xb[2] = {c.io.take_n<T>((size_t)chunk * d), c.io.take_n<T>((size_t)chunk * d)};
-  T* zb[2] = {c.io.take_n<T>((size_t)chunk * k), c.io.take_n<T>((size_t)chunk * k)};
-  T* ub[2] = {c.io.take_n<T>((size_t)chunk * k), c.io.take_n<T>((size_t)chunk * k)};
+  T* xall = c.io.take_n<T>((size_t)(resident ? n : 2 * chunk) * d);
+  T* zall = c.io.take_n<T>((size_t)(resident ? n : 2 * chunk) * k);
+  T* uall = c.io.take_n<T>((size_t)(resident ? n : 2 * chunk) * k);
+  auto xbuf = [&](long long r0, int b) { return resident ? xall + (size_t)r0 * d : xall + (size_t)b * chunk * d; };
+  auto zbuf = [&](long long r0, int b) { return resident ? zall + (size_t)r0 * k : zall + (size_t)b * chunk * k; };
+  auto ubuf = [&](long long r0, int b) { return resident ? uall + (size_t)r0 * k : uall + (size_t)b * chunk * k; };
   cudaEvent_t loaded[2], xfree[2], projected[2], zfree[2];
   for (int b = 0; b < 2; ++b) {
     DR4G_CUDA(cudaEventCreateWithFlags(&loaded[b], cudaEventDisableTiming));
@@ -401,37 +406,47 @@ static void legacy_out_of_core(CtxFull& c, bool is_pca, const T* X, long long n,
     }
   };
   try {
+    // the copy stream must not overtake earlier work of this context that still reads the io arena
     DR4G_CUDA(cudaStreamSynchronize(c.stream));
-    c.sf.release();
+    // accumulators of the context are reused when the shape allows (cudaMalloc / cudaFree synchronise)
+    if (c.sf.acc && c.sf.d == d && c.sf.elem == (int)sizeof(T)) {
+      DR4G_CUDA(cudaMemsetAsync(c.sf.acc, 0, ((size_t)d * d + 2 * (size_t)d + 1) * 8, c.stream));
+      c.sf.center = is_pca ? 1 : 0;
+      c.sf.rows = 0;
+    } else {
+      c.sf.release();
+    }
     const long long nchunks = (n + chunk - 1) / chunk;
     // [1] fit
     for (long long i = 0; i < nchunks; ++i) {
       const int b = (int)(i & 1);
       const long long r0 = i * chunk, rows = n - r0 < chunk ? n - r0 : chunk;
-      if (i >= 2) DR4G_CUDA(cudaStreamWaitEvent(c.copy_stream, xfree[b], 0));
-      DR4G_CUDA(cudaMemcpyAsync(xb[b], X + (size_t)r0 * d, (size_t)rows * d * sizeof(T), cudaMemcpyDefault, c.copy_stream));
+      if (!resident && i >= 2) DR4G_CUDA(cudaStreamWaitEvent(c.copy_stream, xfree[b], 0));
+      DR4G_CUDA(cudaMemcpyAsync(xbuf(r0, b), X + (size_t)r0 * d, (size_t)rows * d * sizeof(T), cudaMemcpyDefault, c.copy_stream));
       DR4G_CUDA(cudaEventRecord(loaded[b], c.copy_stream));
       DR4G_CUDA(cudaStreamWaitEvent(c.stream, loaded[b], 0));
-      partial_fit_impl<T>(c, xb[b], rows, d, is_pca ? 1 : 0);
-      DR4G_CUDA(cudaEventRecord(xfree[b], c.stream));
+      partial_fit_impl<T>(c, xbuf(r0, b), rows, d, is_pca ? 1 : 0);
+      if (!resident) DR4G_CUDA(cudaEventRecord(xfree[b], c.stream));
     }
     partial_fit_finalize_impl<T>(c, k, p, dQ, dw, dev, devr, dmean);
     // [2] scores
     for (long long i = 0; i < nchunks; ++i) {
       const int b = (int)(i & 1);
       const long long r0 = i * chunk, rows = n - r0 < chunk ? n - r0 : chunk;
-      DR4G_CUDA(cudaStreamWaitEvent(c.copy_stream, xfree[b], 0));   // last reader: the pass or the projection of chunk i-2
-      DR4G_CUDA(cudaMemcpyAsync(xb[b], X + (size_t)r0 * d, (size_t)rows * d * sizeof(T), cudaMemcpyDefault, c.copy_stream));
-      DR4G_CUDA(cudaEventRecord(loaded[b], c.copy_stream));
-      DR4G_CUDA(cudaStreamWaitEvent(c.stream, loaded[b], 0));
-      if (i >= 2) DR4G_CUDA(cudaStreamWaitEvent(c.stream, zfree[b], 0));
-      launch_project<T>(c, xb[b], rows, d, k, dQ, is_pca ? dmean : nullptr, dw, zb[b], ub[b]);
+      if (!resident) {
+        DR4G_CUDA(cudaStreamWaitEvent(c.copy_stream, xfree[b], 0));   // last reader: the pass or the projection of chunk i-2
+        DR4G_CUDA(cudaMemcpyAsync(xbuf(r0, b), X + (size_t)r0 * d, (size_t)rows * d * sizeof(T), cudaMemcpyDefault, c.copy_stream));
+        DR4G_CUDA(cudaEventRecord(loaded[b], c.copy_stream));
+        DR4G_CUDA(cudaStreamWaitEvent(c.stream, loaded[b], 0));
+        if (i >= 2) DR4G_CUDA(cudaStreamWaitEvent(c.stream, zfree[b], 0));
+      }
+      launch_project<T>(c, xbuf(r0, b), rows, d, k, dQ, is_pca ? dmean : nullptr, dw, zbuf(r0, b), ubuf(r0, b));
       DR4G_CUDA(cudaEventRecord(projected[b], c.stream));
-      DR4G_CUDA(cudaEventRecord(xfree[b], c.stream));
+      if (!resident) DR4G_CUDA(cudaEventRecord(xfree[b], c.stream));
       DR4G_CUDA(cudaStreamWaitEvent(c.out_stream, projected[b], 0));
-      DR4G_CUDA(cudaMemcpyAsync(Xt + (size_t)r0 * k, zb[b], (size_t)rows * k * sizeof(T), cudaMemcpyDefault, c.out_stream));
-      DR4G_CUDA(cudaMemcpyAsync(U + (size_t)r0 * k, ub[b], (size_t)rows * k * sizeof(T), cudaMemcpyDefault, c.out_stream));
-      DR4G_CUDA(cudaEventRecord(zfree[b], c.out_stream));
+      DR4G_CUDA(cudaMemcpyAsync(Xt + (size_t)r0 * k, zbuf(r0, b), (size_t)rows * k * sizeof(T), cudaMemcpyDefault, c.out_stream));
+      DR4G_CUDA(cudaMemcpyAsync(U + (size_t)r0 * k, ubuf(r0, b), (size_t)rows * k * sizeof(T), cudaMemcpyDefault, c.out_stream));
+      if (!resident) DR4G_CUDA(cudaEventRecord(zfree[b], c.out_stream));
     }
     auto out = [&](T* dst, const T* src, size_t count) {
       if (dst) DR4G_CUDA(cudaMemcpyAsync(dst, src, count * sizeof(T), cudaMemcpyDefault, c.stream));
@@ -444,7 +459,6 @@ static void legacy_out_of_core(CtxFull& c, bool is_pca, const T* X, long long n,
     DR4G_CUDA(cudaStreamSynchronize(c.copy_stream));
     DR4G_CUDA(cudaStreamSynchronize(c.stream));
     DR4G_CUDA(cudaStreamSynchronize(c.out_stream));
-    c.sf.release();
   } catch (...) {
     cudaStreamSynchronize(c.copy_stream);
     cudaStreamSynchronize(c.stream);
@@ -491,20 +505,20 @@ static void legacy_entry(bool is_pca, const T* X, T* Q, T* w, T* U, T* Xt, T* ev
     const size_t xbytes = (size_t)n * d * sizeof(T);
     const size_t zbytes = (size_t)n * k * sizeof(T);
     const bool x_on_device = is_device_pointer(X);
-    // Out of core: X and its scores do not fit beside each other on the device (or
-    // DR4G_STREAM_ROWS forces a chunk size): two streamed sweeps over the host copy of X.
-    {
+    // Host X: chunk pipeline on three streams (H2D | pass, projection | D2H).  Out of core when X and
+    // its scores do not fit beside each other on the device (or DR4G_STREAM_ROWS forces a chunk size): two chunk
+    // buffers and a second H2D sweep for the scores; otherwise one device copy of X, filled chunk by chunk.
+    if (!x_on_device) {
       size_t free_b = 0, total_b = 0;
       DR4G_CUDA(cudaMemGetInfo(&free_b, &total_b));
       const char* env = getenv("DR4G_STREAM_ROWS");
       const long long forced = env ? atoll(env) : 0;
-      if (!x_on_device && (forced > 0 || (double)xbytes + 2.0 * (double)zbytes > 0.8 * (double)total_b)) {
-        long long chunk = forced > 0 ? forced : (long long)(((size_t)256 << 20) / ((size_t)d * sizeof(T)));
-        if (chunk < 1024 && forced <= 0) chunk = 1024;
-        if (chunk > n) chunk = n;
-        legacy_out_of_core<T>(*c, is_pca, X, n, d, k, chunk, p, Q, w, U, Xt, ev, evr, mean);
-        return;
-      }
+      const bool resident = forced <= 0 && (double)xbytes + 2.0 * (double)zbytes <= 0.8 * (double)total_b;
+      long long chunk = forced > 0 ? forced : (long long)(((size_t)(resident ? 128 : 256) << 20) / ((size_t)d * sizeof(T)));
+      if (chunk < 1024 && forced <= 0) chunk = 1024;
+      if (chunk > n) chunk = n;
+      legacy_pipelined<T>(*c, is_pca, resident, X, n, d, k, chunk, p, Q, w, U, Xt, ev, evr, mean);
+      return;
     }
     size_t need = 2 * up256(zbytes) + up256((size_t)k * d * sizeof(T)) + 3 * up256((size_t)k * sizeof(T)) +
                   up256((size_t)d * sizeof(T)) + 4096;
