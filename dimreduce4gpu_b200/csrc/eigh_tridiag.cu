@@ -516,13 +516,15 @@ __device__ __forceinline__ int sturm_count(const double* __restrict__ dg, const 
 
 // One CTA (4 warps) per wanted eigenvalue (j-th largest, j = blockIdx.x).  lam[j] descending.
 // info[0] = ||T||_1-ish scale (max Gershgorin radius bound), written by warp 0 for T3.
-__global__ void __launch_bounds__(128)
+constexpr int kBsThreads = 512, kBsU = 1;   // sections per pass = kBsThreads * kBsU
+
+__global__ void __launch_bounds__(kBsThreads)
 bisect_kernel(const double* __restrict__ diag, const double* __restrict__ off, int d, int k,
               double* __restrict__ lam, double* __restrict__ info) {
   extern __shared__ double bs_sm[];
   double* dg = bs_sm;
   double* e2 = dg + d;
-  __shared__ double s_lo[4], s_hi[4], s_emax[4];
+  __shared__ double s_lo[kBsThreads / 32], s_hi[kBsThreads / 32], s_emax[kBsThreads / 32];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   double lo = DBL_MAX, hi = -DBL_MAX, emax = 0.0;
   for (int i = tid; i < d; i += blockDim.x) {
@@ -554,20 +556,21 @@ bisect_kernel(const double* __restrict__ diag, const double* __restrict__ off, i
   const int j = blockIdx.x;   // one CTA per wanted eigenvalue
   if (j >= k) return;
   const int idx = d - 1 - j;  // 0-based index in ascending order: count(x) <= idx  <=>  x <= lambda_idx
-  // 4 blockDim-section (512 at 128 threads): 4 independent Sturm recurrences per thread (the reciprocal's latency
-  // is the cost of a pass; a pass narrows the interval 513-fold: 5 passes from the Gershgorin interval to
-  // 1e-13 ||T||, where one warp per eigenvalue needed 7).  T3 refines every value with the Rayleigh quotient.
-  __shared__ int s_first[4];
-  const int S = 4 * blockDim.x;
-  const double atol = 1e-13 * tnorm + 2.0 * pivmin;
+  // kBsThreads * kBsU sections per pass, one Sturm recurrence per thread: with 4 recurrences per thread the pass was
+  // bound by the fp64 issue rate of the four schedulers (138 us at d = 256, k = 32), one per thread leaves the
+  // 255-step dependent chain (~130 cycles per step).  A pass narrows the interval 513-fold (1024 threads and four
+  // passes to 2e-12 ||T|| were slower: two warps' worth of fp64 issue per scheduler again).
+  __shared__ int s_first[kBsThreads / 32];
+  const int S = kBsU * kBsThreads;
+  const double atol = 1e-13 * tnorm + 2.0 * pivmin;   // five 513-section passes from the Gershgorin interval; T3 refines by Rayleigh quotient
   for (int it = 0; it < 12; ++it) {
     const double width = hi - lo;
     if (!(width > atol)) break;   // CTA-uniform: lo, hi are identical in every thread
-    double x[4], q[4];
-    int cnt[4];
+    double x[kBsU], q[kBsU];
+    int cnt[kBsU];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      x[u] = lo + width * (double)(4 * tid + u + 1) / (double)(S + 1);
+    for (int u = 0; u < kBsU; ++u) {
+      x[u] = lo + width * (double)(kBsU * tid + u + 1) / (double)(S + 1);
       q[u] = dg[0] - x[u];
       if (fabs(q[u]) < pivmin) q[u] = -pivmin;
       cnt[u] = q[u] < 0.0;
@@ -575,19 +578,19 @@ bisect_kernel(const double* __restrict__ diag, const double* __restrict__ off, i
     for (int i = 1; i < d; ++i) {
       const double di = dg[i], ei = e2[i - 1];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < kBsU; ++u) {
         q[u] = di - x[u] - ei * fast_rcp(q[u]);
         if (fabs(q[u]) < pivmin) q[u] = -pivmin;
         cnt[u] += q[u] < 0.0;
       }
     }
-    int fl = 4;
+    int fl = kBsU;
 #pragma unroll
-    for (int u = 3; u >= 0; --u) if (cnt[u] > idx) fl = u;  // counts are monotone in x: first shift right of lambda_idx
-    const unsigned m = __ballot_sync(0xffffffffu, fl < 4);
+    for (int u = kBsU - 1; u >= 0; --u) if (cnt[u] > idx) fl = u;  // counts are monotone in x: first shift right of lambda_idx
+    const unsigned m = __ballot_sync(0xffffffffu, fl < kBsU);
     const int lane1 = m ? __ffs(m) - 1 : 0;
     const int u1 = __shfl_sync(0xffffffffu, fl, lane1);
-    if (lane == 0) s_first[warp] = m ? warp * 128 + lane1 * 4 + u1 : S;
+    if (lane == 0) s_first[warp] = m ? (warp * 32 + lane1) * kBsU + u1 : S;
     __syncthreads();
     int first = S;
     for (int i = 0; i < nwarp; ++i) first = min(first, s_first[i]);
@@ -1072,7 +1075,7 @@ void launch_eigh_topk(Ctx& c, double* dA, int d, int k, double* dW, double* dVt,
   static PerDeviceMax bs_smem_set;
   if (bs_smem > 48 * 1024 && bs_smem_set.need(c.device, bs_smem))
     DR4G_CUDA(cudaFuncSetAttribute(bisect_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bs_smem));
-  bisect_kernel<<<k, 128, bs_smem, c.stream>>>(diag, off, d, k, lam, info);
+  bisect_kernel<<<k, kBsThreads, bs_smem, c.stream>>>(diag, off, d, k, lam, info);
   // T3
   const size_t iv_smem = (size_t)7 * d * sizeof(double) + (size_t)d * sizeof(int);
   static PerDeviceMax iv_smem_set;
