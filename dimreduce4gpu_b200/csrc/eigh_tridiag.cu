@@ -923,15 +923,17 @@ backtransform_pair_kernel(const double* __restrict__ Vh, const double* __restric
     for (int u = 0; u < PER; ++u) z[u] = fma(-dot, cur[u], z[u]);
     --s;
   }
+  bool inb[PER];   // T1 stores the reflector rows with exact zeros up to their leading 1: no per-element mask
+#pragma unroll
+  for (int u = 0; u < PER; ++u) inb[u] = lane + 32 * u < d;
   auto fetch = [&](ReflPair<PER>& P, int sp) {   // reflectors sp and sp-1
     if (sp < 1) return;
-    const double* va = Vh + (size_t)sp * d;
+    const double* va = Vh + (size_t)sp * d + lane;
     const double* vb = va - d;
 #pragma unroll
     for (int u = 0; u < PER; ++u) {
-      const int i = lane + 32 * u;
-      P.a[u] = (i > sp && i < d) ? __ldg(&va[i]) : 0.0;
-      P.b[u] = (i > sp - 1 && i < d) ? __ldg(&vb[i]) : 0.0;
+      P.a[u] = inb[u] ? __ldg(&va[32 * u]) : 0.0;
+      P.b[u] = inb[u] ? __ldg(&vb[32 * u]) : 0.0;
     }
     P.ta = __ldg(&tau[sp]);
     P.tb = __ldg(&tau[sp - 1]);
