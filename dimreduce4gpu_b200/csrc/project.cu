@@ -12,8 +12,6 @@
 //   inverse: A = Z (n x k), B(m,t) = Q[t*d + m],  m < d, t < k
 // CTA = 256 threads, 128 rows x 64 outputs per pass, 32-wide (fp32) / 16-wide (fp64) contraction chunks; each thread owns
 // an 8 x 4 register tile.  HBM-bound for k << d: algorithmic bytes = n*(d+k)*sizeof(T).
-#include <cstdlib>
-
 #include "common.cuh"
 
 namespace dr4g {
@@ -240,125 +238,6 @@ project_f32_kernel(const float* __restrict__ X, long long n, int d, int k, const
   }
 }
 
-// k <= 32 variant with 8 x 8 register tiles: 512 rows per CTA, contraction in chunks of 16 columns.  Per contraction
-// step a thread issues 4 LDS.128 for 64 FMAs (8 x 4 tiles: 3 for 32), which takes the shared-memory pipe off the
-// critical path; one CTA per SM (64 accumulators + prefetch registers).  Selected by launch_project when it wins.
-__global__ void __launch_bounds__(256, 1)
-project_f32_k32_8x8_kernel(const float* __restrict__ X, long long n, int d, int k, const float* __restrict__ mean,
-                           const float* __restrict__ Q, const float* __restrict__ sigma, float* __restrict__ Z,
-                           float* __restrict__ U) {
-  constexpr int KP = 32, RT = 512, TC = 16;
-  extern __shared__ __align__(16) float psm[];
-  float* As = psm;                       // [2][TC][RT], rows XOR-swizzled in groups of 8 by (t / 4) % 4
-  float* Bs = psm + 2 * TC * RT;         // [2][TC][KP]
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int tx = tid & 3, ty = tid >> 2;               // outputs tx*8..+7, rows ty*8..+7
-  const long long row0 = (long long)blockIdx.x * RT;
-  const int c4 = lane & 3, r8 = lane >> 2;             // staging: float4 c4 of row r8 (+ 8 j) of the warp's 64 rows
-  const int srow0 = warp * 64 + r8;
-  const int swz = c4 << 3;
-  const int bm = tid & 31, bt0 = (tid >> 5) * 2;       // Q chunk: 2 floats per thread
-  const bool full_rows = row0 + RT <= n;
-
-  float4 xa[8], mu4;
-  float2 bq;
-  auto fetch = [&](int t0) {
-    const int t = t0 + 4 * c4;
-    const bool tin = t + 3 < d;
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const long long r = row0 + srow0 + 8 * j;
-      xa[j] = (tin && (full_rows || r < n)) ? __ldg(reinterpret_cast<const float4*>(X + r * (long long)d + t))
-                                            : make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-    mu4 = (mean && tin) ? __ldg(reinterpret_cast<const float4*>(mean + t)) : make_float4(0.f, 0.f, 0.f, 0.f);
-    const int tq = t0 + bt0;
-    bq = (bm < k && tq + 1 < d) ? __ldg(reinterpret_cast<const float2*>(Q + (long long)bm * d + tq)) : make_float2(0.f, 0.f);
-  };
-  auto stash = [&](int buf, int t0) {
-    float* Ab = As + buf * TC * RT + (4 * c4) * RT;
-    float* Bb = Bs + buf * TC * KP;
-    const bool tin = t0 + 4 * c4 + 3 < d;
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const int rl = srow0 + 8 * j;
-      const bool in = tin && (full_rows || row0 + rl < n);
-      const int pr = rl ^ swz;
-      Ab[0 * RT + pr] = in ? xa[j].x - mu4.x : 0.f;
-      Ab[1 * RT + pr] = in ? xa[j].y - mu4.y : 0.f;
-      Ab[2 * RT + pr] = in ? xa[j].z - mu4.z : 0.f;
-      Ab[3 * RT + pr] = in ? xa[j].w - mu4.w : 0.f;
-    }
-    Bb[bt0 * KP + bm] = bq.x;
-    Bb[(bt0 + 1) * KP + bm] = bq.y;
-  };
-
-  float acc[8][8];
-#pragma unroll
-  for (int i = 0; i < 8; ++i)
-#pragma unroll
-    for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
-
-  fetch(0);
-  stash(0, 0);
-  __syncthreads();
-  int buf = 0;
-  for (int t0 = 0; t0 < d; t0 += TC) {
-    const bool more = t0 + TC < d;
-    if (more) fetch(t0 + TC);
-    const float* Ab = As + buf * TC * RT;
-    const float* Bb = Bs + buf * TC * KP + tx * 8;
-#pragma unroll
-    for (int t = 0; t < TC; ++t) {
-      const int g = ((t >> 2) & 3) << 3;
-      const float4 a0 = *reinterpret_cast<const float4*>(Ab + t * RT + ((ty * 8) ^ g));
-      const float4 a1 = *reinterpret_cast<const float4*>(Ab + t * RT + ((ty * 8) ^ g) + 4);
-      const float4 b0 = *reinterpret_cast<const float4*>(Bb + t * KP);
-      const float4 b1 = *reinterpret_cast<const float4*>(Bb + t * KP + 4);
-      const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-      const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-#pragma unroll
-      for (int i = 0; i < 8; ++i)
-#pragma unroll
-        for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(a[i], bb[j], acc[i][j]);
-    }
-    if (more) stash(buf ^ 1, t0 + TC);
-    __syncthreads();
-    buf ^= 1;
-  }
-  float inv[8];
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const int m = tx * 8 + j;
-    const float sg = (U && sigma && m < k) ? __ldg(sigma + m) : 0.f;
-    inv[j] = sg != 0.f ? 1.f / sg : 0.f;
-  }
-  const bool vec = (k % 4) == 0;
-#pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    const long long r = row0 + ty * 8 + i;
-    if (r >= n) continue;
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-      const int m0 = tx * 8 + 4 * h;
-      if (vec && m0 + 3 < k) {
-        *reinterpret_cast<float4*>(Z + r * k + m0) =
-            make_float4(acc[i][4 * h], acc[i][4 * h + 1], acc[i][4 * h + 2], acc[i][4 * h + 3]);
-        if (U) *reinterpret_cast<float4*>(U + r * k + m0) =
-            make_float4(acc[i][4 * h] * inv[4 * h], acc[i][4 * h + 1] * inv[4 * h + 1], acc[i][4 * h + 2] * inv[4 * h + 2],
-                        acc[i][4 * h + 3] * inv[4 * h + 3]);
-      } else {
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
-          if (m0 + j < k) {
-            Z[r * k + m0 + j] = acc[i][4 * h + j];
-            if (U) U[r * k + m0 + j] = acc[i][4 * h + j] * inv[4 * h + j];
-          }
-      }
-    }
-  }
-}
-
 template <int KP>
 void launch_project_f32(Ctx& c, const float* dX, long long n, int d, int k, const float* dQ, const float* dmean,
                         const float* dw, float* dZ, float* dU) {
@@ -383,15 +262,7 @@ void launch_project(Ctx& c, const T* dX, long long n, int d, int k, const T* dQ,
     const bool aligned = (reinterpret_cast<uintptr_t>(dX) & 15) == 0 && (d % 4) == 0 &&
                          (reinterpret_cast<uintptr_t>(dZ) & 15) == 0 && (!dU || (reinterpret_cast<uintptr_t>(dU) & 15) == 0);
     if (aligned && k <= 64) {
-      static const int tile8 = getenv("DR4G_PROJECT_8X8") ? atoi(getenv("DR4G_PROJECT_8X8")) : 0;
-      if (k <= 32 && tile8) {
-        const size_t smem = (size_t)2 * 16 * (512 + 32) * sizeof(float);
-        static PerDeviceMax smem_set;
-        if (smem_set.need(c.device, smem))
-          DR4G_CUDA(cudaFuncSetAttribute(project_f32_k32_8x8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        project_f32_k32_8x8_kernel<<<(unsigned)((n + 511) / 512), 256, smem, c.stream>>>(
-            dX, n, d, k, dmean, dQ, (dU && dw) ? dw : nullptr, dZ, (dU && dw) ? dU : nullptr);
-      } else if (k <= 32) launch_project_f32<32>(c, dX, n, d, k, dQ, dmean, dw, dZ, dU);
+      if (k <= 32) launch_project_f32<32>(c, dX, n, d, k, dQ, dmean, dw, dZ, dU);
       else launch_project_f32<64>(c, dX, n, d, k, dQ, dmean, dw, dZ, dU);
       c.launches++;
       DR4G_CUDA(cudaGetLastError());
