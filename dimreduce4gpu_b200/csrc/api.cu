@@ -279,7 +279,7 @@ static void fit_impl(Ctx& c, const T* dX, long long n_local, int d, int k, int c
     launch_gram_generic<T>(c, dX, n_local, d, shift_arg, G);
     launch_mirror_upper(c, G, d);
   }
-  c.last_gram_path = used_tc ? (c.last_gram_kernel == 2 ? 3 : 2) : 1;
+  c.last_gram_path = used_tc ? (c.last_gram_kernel == 3 ? 4 : c.last_gram_kernel == 2 ? 3 : 2) : 1;
   launch_set_scalar(c, cnt, (double)n_local);
   }
   if (phase == 1) {
@@ -303,7 +303,7 @@ static void fit_impl(Ctx& c, const T* dX, long long n_local, int d, int k, int c
     launch_eigh_topk(c, C, d, k, W, Vt, ws);
     mark(4);
     launch_postproc<T>(c, W, k, Vt, d, /*vectors_in_rows=*/true, /*check_mass=*/false, d, k, cnt, total_var,
-                       center ? mean_d : nullptr, dQ, dw, dev, devr, center ? dmean : nullptr);
+                       center ? mean_d : nullptr, dQ, dw, dev, devr, center ? dmean : nullptr, p.whiten);
   } else if (exact) {
     double* A = c.arena.take_n<double>((size_t)dp * dp);
     double* V = c.arena.take_n<double>((size_t)dp * dp);
@@ -314,7 +314,7 @@ static void fit_impl(Ctx& c, const T* dX, long long n_local, int d, int k, int c
     launch_jacobi(c, A, V, dp, W, ws, tol, c.jacobi_sweeps);
     mark(4);
     launch_postproc<T>(c, W, dp, V, dp, /*vectors_in_rows=*/false, /*check_mass=*/dp != d, d, k, cnt, total_var,
-                       center ? mean_d : nullptr, dQ, dw, dev, devr, center ? dmean : nullptr);
+                       center ? mean_d : nullptr, dQ, dw, dev, devr, center ? dmean : nullptr, p.whiten);
   } else {
     void* ws = c.arena.take(power_workspace_bytes(d, l));
     double* W = c.arena.take_n<double>(lp);
@@ -324,7 +324,7 @@ static void fit_impl(Ctx& c, const T* dX, long long n_local, int d, int k, int c
     launch_power(c, C, d, k, l, p.n_iter, tol, seed, W, Vt, ws);
     mark(4);
     launch_postproc<T>(c, W, lp, Vt, d, /*vectors_in_rows=*/true, /*check_mass=*/true, d, k, cnt, total_var,
-                       center ? mean_d : nullptr, dQ, dw, dev, devr, center ? dmean : nullptr);
+                       center ? mean_d : nullptr, dQ, dw, dev, devr, center ? dmean : nullptr, p.whiten);
   }
   mark(5);
   c.stage_valid = timing;
@@ -430,7 +430,7 @@ static void legacy_pipelined(CtxFull& c, bool is_pca, bool resident, const T* X,
     }
     partial_fit_finalize_impl<T>(c, k, p, dQ, dw, dev, devr, dmean);
     // [2] scores
-    for (long long i = 0; i < nchunks; ++i) {
+    for (long long i = 0; Xt && i < nchunks; ++i) {
       const int b = (int)(i & 1);
       const long long r0 = i * chunk, rows = n - r0 < chunk ? n - r0 : chunk;
       if (!resident) {
@@ -440,12 +440,12 @@ static void legacy_pipelined(CtxFull& c, bool is_pca, bool resident, const T* X,
         DR4G_CUDA(cudaStreamWaitEvent(c.stream, loaded[b], 0));
         if (i >= 2) DR4G_CUDA(cudaStreamWaitEvent(c.stream, zfree[b], 0));
       }
-      launch_project<T>(c, xbuf(r0, b), rows, d, k, dQ, is_pca ? dmean : nullptr, dw, zbuf(r0, b), ubuf(r0, b));
+      launch_project<T>(c, xbuf(r0, b), rows, d, k, dQ, is_pca ? dmean : nullptr, dw, zbuf(r0, b), U ? ubuf(r0, b) : nullptr);
       DR4G_CUDA(cudaEventRecord(projected[b], c.stream));
       if (!resident) DR4G_CUDA(cudaEventRecord(xfree[b], c.stream));
       DR4G_CUDA(cudaStreamWaitEvent(c.out_stream, projected[b], 0));
       DR4G_CUDA(cudaMemcpyAsync(Xt + (size_t)r0 * k, zbuf(r0, b), (size_t)rows * k * sizeof(T), cudaMemcpyDefault, c.out_stream));
-      DR4G_CUDA(cudaMemcpyAsync(U + (size_t)r0 * k, ubuf(r0, b), (size_t)rows * k * sizeof(T), cudaMemcpyDefault, c.out_stream));
+      if (U) DR4G_CUDA(cudaMemcpyAsync(U + (size_t)r0 * k, ubuf(r0, b), (size_t)rows * k * sizeof(T), cudaMemcpyDefault, c.out_stream));
       if (!resident) DR4G_CUDA(cudaEventRecord(zfree[b], c.out_stream));
     }
     auto out = [&](T* dst, const T* src, size_t count) {
@@ -468,6 +468,48 @@ static void legacy_pipelined(CtxFull& c, bool is_pca, bool resident, const T* X,
     throw;
   }
   cleanup();
+}
+
+// Host-resident X (pageable or pinned) -> fit + scores on the device -> host outputs.  Chunk pipeline on three streams
+// (H2D | pass, projection | D2H).  One device copy of X filled chunk by chunk when X, its scores and the fit's
+// workspace fit into the memory that is FREE now (other tenants of the device - a torch caching allocator in the same
+// process - are respected); otherwise out of core: two chunk buffers and a second H2D sweep for the
+// scores.  DR4G_STREAM_ROWS forces the out-of-core path with that chunk size.  With a communicator on the context the
+// pass is the row-sharded one (pilot + packed allreduce), X being this rank's shard.
+template <typename T>
+static void host_fit_transform(CtxFull& c, bool is_pca, const T* X, long long n, int d, int k, const params& p, T* Q, T* w,
+                               T* U, T* Xt, T* ev, T* evr, T* mean) {
+  const size_t xbytes = (size_t)n * d * sizeof(T);
+  const size_t zbytes = (size_t)n * k * sizeof(T);
+  size_t free_b = 0, total_b = 0;
+  DR4G_CUDA(cudaMemGetInfo(&free_b, &total_b));
+  const char* env = getenv("DR4G_STREAM_ROWS");
+  const long long forced = env ? atoll(env) : 0;
+  // what the resident path would have to allocate on top of what the context already owns: the io arena (grown by
+  // Arena::reserve's 12.5 % + 1 MB policy; the old block is released first) and the fit workspace (packed accumulators,
+  // covariance, eigensolver scratch ~ 6 d^2 doubles, Gram slabs ~ 40 MB)
+  const size_t io_need = up256(xbytes) + 2 * up256(zbytes) + up256((size_t)k * d * sizeof(T)) + ((size_t)1 << 20);
+  const size_t io_grow = io_need > c.io.cap ? io_need + (io_need >> 3) + ((size_t)1 << 20) - c.io.cap : 0;
+  const size_t ws_need = (size_t)d * d * 8 * 6 + ((size_t)48 << 20);
+  const size_t ws_grow = ws_need > c.arena.cap ? ws_need - c.arena.cap : 0;
+  bool resident = forced <= 0 && (double)io_grow + (double)ws_grow <= 0.92 * (double)free_b;
+  auto chunk_rows = [&](bool res) {
+    long long chunk = forced > 0 ? forced : (long long)(((size_t)(res ? 128 : 256) << 20) / ((size_t)d * sizeof(T)));
+    if (chunk < 1024 && forced <= 0) chunk = 1024;
+    return chunk > n ? n : chunk;
+  };
+  if (resident) {
+    try {
+      legacy_pipelined<T>(c, is_pca, true, X, n, d, k, chunk_rows(true), p, Q, w, U, Xt, ev, evr, mean);
+      return;
+    } catch (const Error& e) {
+      // lost a race for device memory: fall back to the out-of-core pipeline instead of failing
+      if (std::strstr(e.what(), "cudaMalloc") == nullptr) throw;
+      cudaGetLastError();
+      resident = false;
+    }
+  }
+  legacy_pipelined<T>(c, is_pca, false, X, n, d, k, chunk_rows(false), p, Q, w, U, Xt, ev, evr, mean);
 }
 
 // ---------------------------------------------------------------- legacy host-pointer entry points
@@ -502,28 +544,14 @@ static void legacy_entry(bool is_pca, const T* X, T* Q, T* w, T* U, T* Xt, T* ev
       fprintf(stderr, "[dimreduce4gpu] %s: algorithm=%s n=%lld d=%d k=%d device=%d\n", name,
               is_exact(p) ? "cusolver (blocked Jacobi)" : "power (subspace iteration)", n, d, k, c->device);
 
-    const size_t xbytes = (size_t)n * d * sizeof(T);
     const size_t zbytes = (size_t)n * k * sizeof(T);
-    const bool x_on_device = is_device_pointer(X);
-    // Host X: chunk pipeline on three streams (H2D | pass, projection | D2H).  Out of core when X and
-    // its scores do not fit beside each other on the device (or DR4G_STREAM_ROWS forces a chunk size): two chunk
-    // buffers and a second H2D sweep for the scores; otherwise one device copy of X, filled chunk by chunk.
-    if (!x_on_device) {
-      size_t free_b = 0, total_b = 0;
-      DR4G_CUDA(cudaMemGetInfo(&free_b, &total_b));
-      const char* env = getenv("DR4G_STREAM_ROWS");
-      const long long forced = env ? atoll(env) : 0;
-      const bool resident = forced <= 0 && (double)xbytes + 2.0 * (double)zbytes <= 0.8 * (double)total_b;
-      long long chunk = forced > 0 ? forced : (long long)(((size_t)(resident ? 128 : 256) << 20) / ((size_t)d * sizeof(T)));
-      if (chunk < 1024 && forced <= 0) chunk = 1024;
-      if (chunk > n) chunk = n;
-      legacy_pipelined<T>(*c, is_pca, resident, X, n, d, k, chunk, p, Q, w, U, Xt, ev, evr, mean);
+    if (!is_device_pointer(X)) {
+      host_fit_transform<T>(*c, is_pca, X, n, d, k, p, Q, w, U, Xt, ev, evr, mean);
       return;
     }
-    size_t need = 2 * up256(zbytes) + up256((size_t)k * d * sizeof(T)) + 3 * up256((size_t)k * sizeof(T)) +
-                  up256((size_t)d * sizeof(T)) + 4096;
-    if (!x_on_device) need += up256(xbytes);
-    c->io.reserve(need);
+    // X already on the device (a caller handing device pointers to the legacy symbols): fit + projection in place
+    c->io.reserve(2 * up256(zbytes) + up256((size_t)k * d * sizeof(T)) + 3 * up256((size_t)k * sizeof(T)) +
+                  up256((size_t)d * sizeof(T)) + 4096);
     c->io.reset();
     T* dQ = c->io.take_n<T>((size_t)k * d);
     T* dw = c->io.take_n<T>(k);
@@ -533,18 +561,6 @@ static void legacy_entry(bool is_pca, const T* X, T* Q, T* w, T* U, T* Xt, T* ev
     T* dZ = c->io.take_n<T>((size_t)n * k);
     T* dU = c->io.take_n<T>((size_t)n * k);
     const T* dX = X;
-    if (!x_on_device) {
-      T* buf = c->io.take_n<T>((size_t)n * d);
-      // one async copy per 256 MiB slab: pinned sources stream at PCIe rate, pageable ones are
-      // staged by the driver; either way the stream orders them before the pass
-      const size_t slab = (size_t)256 << 20;
-      for (size_t off = 0; off < xbytes; off += slab) {
-        const size_t len = xbytes - off < slab ? xbytes - off : slab;
-        DR4G_CUDA(cudaMemcpyAsync(reinterpret_cast<char*>(buf) + off, reinterpret_cast<const char*>(X) + off, len,
-                                  cudaMemcpyDefault, c->stream));
-      }
-      dX = buf;
-    }
     fit_impl<T>(*c, dX, n, d, k, is_pca ? 1 : 0, p, dQ, dw, dev, devr, dmean);
     launch_project<T>(*c, dX, n, d, k, dQ, is_pca ? dmean : nullptr, dw, dZ, dU);
 
@@ -641,6 +657,7 @@ int dr4g_set_option(dr4g_ctx* ctx, const char* key, double value) {
   if (!ctx || !key) fail("null argument");
   const std::string k(key);
   if (k == "gram_path") ctx->gram_path = (int)value;
+  else if (k == "gram_split") ctx->gram_split = (int)value;
   else if (k == "flush_rows") ctx->flush_rows = (int)value;
   else if (k == "pilot_rows") ctx->pilot_rows = (int)value;
   else if (k == "jacobi_tol") ctx->jacobi_tol = value;
@@ -697,6 +714,31 @@ int dr4g_comm_world(dr4g_ctx* ctx) { return ctx ? ctx->world : 0; }
 DR4G_FIT(dr4g_fit_float, float)
 DR4G_FIT(dr4g_fit_double, double)
 
+// ---- host-resident shard in, host results out, on THIS context (communicator honoured) -------------
+#define DR4G_HOST_FT(NAME, T)                                                                               \
+  int NAME(dr4g_ctx* ctx, const T* X, long long n_local, int d, int k, int center, params p, T* Q, T* w, T* U, \
+           T* Xt, T* ev, T* evr, T* mean) {                                                                \
+    DR4G_API_BEGIN                                                                                          \
+    if (!ctx || !X || !Q || !w || (center && !mean)) fail(#NAME ": null argument");                         \
+    if (n_local <= 0 || d <= 0 || k <= 0) fail(#NAME ": empty problem");                                    \
+    if (k > d) k = d;                                                                                       \
+    if (ctx->world <= 1 && k > n_local) k = (int)n_local;                                                   \
+    std::lock_guard<std::mutex> lk(ctx->mu);                                                                \
+    DeviceGuard g(ctx->device);                                                                             \
+    cudaStream_t keep = ctx->stream;                                                                        \
+    ctx->stream = ctx->own_stream; /* blocking call with its own copy streams: never the caller's stream */  \
+    try {                                                                                                   \
+      host_fit_transform<T>(*ctx, center != 0, X, n_local, d, k, p, Q, w, U, Xt, ev, evr, mean);            \
+    } catch (...) {                                                                                         \
+      ctx->stream = keep;                                                                                   \
+      throw;                                                                                                \
+    }                                                                                                       \
+    ctx->stream = keep;                                                                                     \
+    DR4G_API_END                                                                                            \
+  }
+DR4G_HOST_FT(dr4g_fit_transform_host_float, float)
+DR4G_HOST_FT(dr4g_fit_transform_host_double, double)
+
 // ---- streaming fit ----------------------------------------------------------------
 int dr4g_partial_fit_reset(dr4g_ctx* ctx) {
   DR4G_API_BEGIN
@@ -736,6 +778,7 @@ DR4G_PARTIAL(dr4g_partial_fit_double, dr4g_partial_fit_finalize_double, double)
     DR4G_API_BEGIN                                                                                         \
     if (!ctx || !dX || !dQ || !dZ) fail(#NAME ": null argument");                                          \
     if (d <= 0 || k <= 0 || n < 0) fail(#NAME ": bad shape");                                              \
+    std::lock_guard<std::mutex> lk(ctx->mu);                                                               \
     DeviceGuard g(ctx->device);                                                                            \
     launch_project<T>(*ctx, dX, n, d, k, dQ, dmean, dw, dZ, dU);                                           \
     DR4G_API_END                                                                                           \
@@ -748,6 +791,7 @@ DR4G_TRANSFORM(dr4g_transform_double, double)
     DR4G_API_BEGIN                                                                                           \
     if (!ctx || !dZ || !dQ || !dX) fail(#NAME ": null argument");                                            \
     if (d <= 0 || k <= 0 || n < 0) fail(#NAME ": bad shape");                                                \
+    std::lock_guard<std::mutex> lk(ctx->mu);                                                                 \
     DeviceGuard g(ctx->device);                                                                              \
     launch_inverse<T>(*ctx, dZ, n, d, k, dQ, dmean, dX);                                                     \
     DR4G_API_END                                                                                             \
@@ -759,6 +803,7 @@ DR4G_INVERSE(dr4g_inverse_transform_double, double)
   int NAME(dr4g_ctx* ctx, const T* dX, long long n, int d, const T* dshift, double* dsum, double* dsumsq) { \
     DR4G_API_BEGIN                                                                                     \
     if (!ctx || !dX || !dsum || !dsumsq) fail(#NAME ": null argument");                                \
+    std::lock_guard<std::mutex> lk(ctx->mu);                                                           \
     DeviceGuard g(ctx->device);                                                                        \
     DR4G_CUDA(cudaMemsetAsync(dsum, 0, (size_t)d * 8, ctx->stream));                                   \
     DR4G_CUDA(cudaMemsetAsync(dsumsq, 0, (size_t)d * 8, ctx->stream));                                 \
@@ -779,7 +824,7 @@ int dr4g_gram_float(dr4g_ctx* ctx, const float* dX, long long n, int d, const fl
     ctx->arena.reserve(ws + 4096);
     ctx->arena.reset();
     launch_gram_tc(*ctx, dX, n, d, dshift, dG, nullptr, nullptr, ctx->arena.take(ws));
-    ctx->last_gram_path = ctx->last_gram_kernel == 2 ? 3 : 2;
+    ctx->last_gram_path = ctx->last_gram_kernel == 3 ? 4 : ctx->last_gram_kernel == 2 ? 3 : 2;
   } else {
     if (ctx->gram_path >= 2) fail("gram_path=2 (tcgen05) requested but the shape is not eligible: n=%lld d=%d", n, d);
     launch_gram_generic<float>(*ctx, dX, n, d, dshift, dG);
@@ -792,6 +837,7 @@ int dr4g_gram_float(dr4g_ctx* ctx, const float* dX, long long n, int d, const fl
 int dr4g_gram_double(dr4g_ctx* ctx, const double* dX, long long n, int d, const double* dshift, double* dG) {
   DR4G_API_BEGIN
   if (!ctx || !dX || !dG) fail("dr4g_gram_double: null argument");
+  std::lock_guard<std::mutex> lk(ctx->mu);
   DeviceGuard g(ctx->device);
   DR4G_CUDA(cudaMemsetAsync(dG, 0, (size_t)d * d * 8, ctx->stream));
   launch_gram_generic<double>(*ctx, dX, n, d, dshift, dG);

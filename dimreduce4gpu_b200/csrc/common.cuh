@@ -73,6 +73,7 @@ struct Ctx {
   int rank = 0, world = 1;
   // options
   int gram_path = 0;          // 0 auto, 1 generic, 2 tcgen05 (pair kernel where eligible), 3 tcgen05 single-CTA kernel only
+  int gram_split = 0;         // pair kernel operand split: 0 auto (bf16x3), 1 3xTF32 (kind::tf32), 2 bf16x3 (kind::f16)
   int flush_rows = 1024;      // rows between TMEM flushes in the tcgen05 Gram
   int pilot_rows = 4096;      // rows sampled for the pilot shift
   double jacobi_tol = 0.0;    // 0 -> per-dtype default
@@ -81,7 +82,7 @@ struct Ctx {
   int timing = 1;             // record per-stage events
   // telemetry
   int last_gram_path = 0;
-  int last_gram_kernel = 0;   // tcgen05 path: 1 single-CTA kernel (gram_tc.cu), 2 CTA-pair kernel (gram_tc2.cu)
+  int last_gram_kernel = 0;   // tcgen05 path: 1 single-CTA kernel (gram_tc.cu), 2 CTA-pair kernel 3xTF32, 3 CTA-pair kernel bf16x3 (gram_tc2.cu)
   long long launches = 0;
   // tensor-map encoder (driver entry point fetched lazily)
   void* encode_tiled = nullptr;
@@ -145,7 +146,7 @@ void launch_power(Ctx& c, const double* dC, int d, int k, int l, int n_iter, dou
 template <typename T>
 void launch_postproc(Ctx& c, const double* dW, int nw, const double* dV, int ldv, bool vectors_in_rows,
                      bool check_mass, int d, int k, const double* packed_n /* pointer to n */, const double* dtotal_var,
-                     const double* dmean_d, T* dQ, T* dw, T* dev, T* devr, T* dmean);
+                     const double* dmean_d, T* dQ, T* dw, T* dev, T* devr, T* dmean, bool whiten = false);
 
 // K7: projection and its inverse.
 template <typename T>

@@ -645,8 +645,9 @@ invit_kernel(const double* __restrict__ diag, const double* __restrict__ off, in
   double* a = iv_sm;        // U diagonal
   double* b = a + d;        // U first super-diagonal
   double* c = b + d;        // multipliers
-  double* d2 = c + d;       // U second super-diagonal
-  double* z = d2 + d;       // iterate
+  // (the second super-diagonal of U is not stored: it is off[i+1] where rows were swapped and 0 elsewhere, so that
+  //  the kernel needs 52 d bytes of shared memory and d = 4096 - BASELINE config 5 - fits the 227 KB limit)
+  double* z = c + d;        // iterate
   double* dg0 = z + d;      // diag - x (read-only during the factorisation)
   double* of0 = dg0 + d;    // off
   int* piv = reinterpret_cast<int*>(of0 + d);
@@ -684,7 +685,6 @@ invit_kernel(const double* __restrict__ diag, const double* __restrict__ off, in
           const double m = ci * ip;
           a[i] = ip;
           b[i] = bi;
-          d2[i] = 0.0;
           c[i] = m;
           piv[i] = 0;
           ai = fma(-m, bi, an);
@@ -694,7 +694,6 @@ invit_kernel(const double* __restrict__ diag, const double* __restrict__ off, in
           const double m = ai * ip;
           a[i] = ip;
           b[i] = an;
-          d2[i] = i < d - 2 ? bn : 0.0;
           c[i] = m;
           piv[i] = 1;
           ai = fma(-m, an, bi);
@@ -705,8 +704,8 @@ invit_kernel(const double* __restrict__ diag, const double* __restrict__ off, in
       if (fabs(pv) < tiny) pv = pv < 0 ? -tiny : tiny;
       a[d - 1] = fast_rcp(pv);
       b[d - 1] = 0.0;
-      d2[d - 1] = 0.0;
       c[d - 1] = 0.0;
+      piv[d - 1] = 0;
     }
     __syncthreads();
     for (int iter = 0; iter < 3; ++iter) {
@@ -720,9 +719,10 @@ invit_kernel(const double* __restrict__ diag, const double* __restrict__ off, in
           }
           z[d - 1] = zi;
         }
-        double z1 = 0.0, z2 = 0.0;   // z[i+1], z[i+2]; b[d-1] = d2[d-1] = d2[d-2] = 0
+        double z1 = 0.0, z2 = 0.0;   // z[i+1], z[i+2]; b[d-1] = 0, second super-diagonal 0 in the last two rows
         for (int i = d - 1; i >= 0; --i) {  // U z = y
-          const double t = fma(-d2[i], z2, fma(-b[i], z1, z[i]));
+          const double d2i = (piv[i] != 0 && i < d - 2) ? of0[i + 1] : 0.0;   // off the dependent chain
+          const double t = fma(-d2i, z2, fma(-b[i], z1, z[i]));
           const double zi = t * a[i];
           z[i] = zi;
           z2 = z1;
@@ -1082,7 +1082,9 @@ void launch_eigh_topk(Ctx& c, double* dA, int d, int k, double* dW, double* dVt,
     DR4G_CUDA(cudaFuncSetAttribute(bisect_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bs_smem));
   bisect_kernel<<<k, kBsThreads, bs_smem, c.stream>>>(diag, off, d, k, lam, info);
   // T3
-  const size_t iv_smem = (size_t)7 * d * sizeof(double) + (size_t)d * sizeof(int);
+  const size_t iv_smem = (size_t)6 * d * sizeof(double) + (size_t)d * sizeof(int);
+  if (iv_smem > 227 * 1024)
+    fail("eigh_topk: d=%d needs %zu bytes of shared memory for the inverse iteration (limit 227 KB, d <= 4469)", d, iv_smem);
   static PerDeviceMax iv_smem_set;
   if (iv_smem > 48 * 1024 && iv_smem_set.need(c.device, iv_smem))
     DR4G_CUDA(cudaFuncSetAttribute(invit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)iv_smem));

@@ -443,8 +443,7 @@ size_t gram_tc_workspace_bytes(const Ctx& c, int d) {
 void launch_gram_tc(Ctx& c, const float* dX, long long n, int d, const float* dshift, double* dG, double* dsum,
                     double* dsumsq, void* workspace) {
   if (use_pair(c, dX, n, d)) {
-    launch_gram_pair(c, dX, n, d, dshift, dG, dsum, dsumsq, workspace);
-    c.last_gram_kernel = 2;
+    launch_gram_pair(c, dX, n, d, dshift, dG, dsum, dsumsq, workspace);   // sets last_gram_kernel = 2 (3xTF32) / 3 (bf16x3)
     return;
   }
   c.last_gram_kernel = 1;

@@ -92,6 +92,15 @@ __device__ long long g_trace2[kTraceIts * 8];
 
 __device__ __forceinline__ float clear13(float v) { return __uint_as_float(__float_as_uint(v) & 0xffffe000u); }
 
+// BF16 = false: 3xTF32 (kind::tf32, hi/lo = two 11-bit halves, fp32-exact products except lo*lo).
+// BF16 = true:  bf16x3 (kind::f16, twice the multiply rate, K = 16 per instruction): y = b1 + b2 + (|rest| <= 2^-18 |y|)
+//   with b1 = bf16(y), b2 = bf16(y - b1), both rounded to nearest so the dropped parts have zero mean; products
+//   b1^T b1 + b1^T b2 + b2^T b1, dropped b2^T b2 <= 2^-18 relative (measured Gram error ~2e-6 of sqrt(G_ii G_jj), below
+//   the truncation of the tensor core's own fp32 accumulation).  The converters write 4 B per element (hi + lo) in
+//   the MN-major SWIZZLE_128B layout of 16-bit operands ([64-column group][8-row atom][8 rows][128 B]) into the second
+//   half of the stage instead of 8 B, and the MMA reads half as many operand bytes: the pass is bound by shared-
+//   memory bandwidth (TMA write + converter read + converter write + operand reads), not by the tensor pipe.
+template <bool BF16>
 __global__ void __launch_bounds__(kThreads, 1)
 gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ PJobTable table, long long n, int d,
                  const float* __restrict__ shift, float* __restrict__ slab, double* __restrict__ osum,
@@ -207,11 +216,13 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
     if (rank == 0 && ptx::elect_one()) {
       // One thread feeds the tensor pipe: no divisions, no constant-bank indexing inside the loop
       // (a first version spent ~1900 cycles per 12-MMA stage on exactly that, measured).
-      constexpr uint32_t idesc = ptx::make_idesc_tf32(256, 256, true, true);
+      constexpr uint32_t idesc = BF16 ? ptx::make_idesc_bf16(256, 256, true, true) : ptx::make_idesc_tf32(256, 256, true, true);
       const int nks = (trace & 2) ? 0 : kt / 8;
       const uint32_t boff0 = (uint32_t)job.lb_of[0] * kSlotBytes, boff1 = (uint32_t)job.lb_of[1] * kSlotBytes;
       const uint32_t slot_row_bytes = (uint32_t)nlb * kSlotBytes;   // next 16 rows of the same local block
-      const uint64_t desc0 = ptx::make_smem_desc(0, 2048, 512, ptx::kLayoutSw128Base32);  // address added below
+      // address added below.  tf32: [32-column group][4-row atom][4 rows][128 B]; bf16: [64-column group][8-row atom][8 rows][128 B]
+      const uint64_t desc0 = BF16 ? ptx::make_smem_desc(0, 2048, 1024, ptx::kLayoutSw128)
+                                  : ptx::make_smem_desc(0, 2048, 512, ptx::kLayoutSw128Base32);
       int s = 0, window = 0, wpos = stagger, set = 0;
       uint32_t ph = 0, racc = 0u;
       uint32_t sx = smem_base;
@@ -227,6 +238,36 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
         DR4G_TRACE2(5);
         const uint32_t d0 = tmem_base + (uint32_t)set * 256u;
         uint32_t acc = window_start ? 0u : 1u;
+        if constexpr (BF16) {
+          // one K = 16 instruction per product and 16-row slot; hi at the slot's offset in the second half of the
+          // stage, lo 4 KB behind it
+          uint32_t row = sx + half_bytes;
+#pragma unroll 1
+          for (int ks = 0; ks < nks; ks += 2) {
+            const uint64_t a_hi = desc0 | (uint64_t)((row >> 4) & 0x3FFF);
+            const uint64_t a_lo = desc0 | (uint64_t)(((row + 4096u) >> 4) & 0x3FFF);
+            const uint64_t b_hi = desc0 | (uint64_t)(((row + boff0) >> 4) & 0x3FFF);
+            const uint64_t b_lo = desc0 | (uint64_t)(((row + boff0 + 4096u) >> 4) & 0x3FFF);
+            if (diag) {
+              ptx::mma_f16_ss_pair(d0, a_hi, b_hi, idesc, acc);
+              ptx::mma_f16_ss_pair(d0 + 256u, a_hi, b_lo, idesc, racc);
+              racc = 1u;
+            } else {
+              ptx::mma_f16_ss_pair(d0, a_hi, b_hi, idesc, acc);
+              ptx::mma_f16_ss_pair(d0, a_hi, b_lo, idesc, 1u);
+              ptx::mma_f16_ss_pair(d0, a_lo, b_hi, idesc, 1u);
+              if (nchunk == 2) {
+                const uint64_t c_hi = desc0 | (uint64_t)(((row + boff1) >> 4) & 0x3FFF);
+                const uint64_t c_lo = desc0 | (uint64_t)(((row + boff1 + 4096u) >> 4) & 0x3FFF);
+                ptx::mma_f16_ss_pair(d0 + 256u, a_hi, c_hi, idesc, acc);
+                ptx::mma_f16_ss_pair(d0 + 256u, a_hi, c_lo, idesc, 1u);
+                ptx::mma_f16_ss_pair(d0 + 256u, a_lo, c_hi, idesc, 1u);
+              }
+            }
+            acc = 1u;
+            row += slot_row_bytes;
+          }
+        } else {
         uint32_t row = sx;
 #pragma unroll 1
         for (int ks = 0; ks < nks; ks += 2) {
@@ -259,6 +300,7 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
             acc = 1u;
           }
           row += slot_row_bytes;
+        }
         }
         ptx::mma_commit_pair(ptx::smem_u32(&bar_empty[s]), 3);   // stage free in both CTAs
         DR4G_TRACE2(6);
@@ -303,6 +345,15 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
       const int r = rg + 4 * h;
       toff[h] = (uint32_t)g * 2048u + (uint32_t)r * 128u + (uint32_t)(((((lc >> 1) ^ (r & 3)) << 1) | (lc & 1)) << 4);
     }
+    // bf16 operand layout of a slot (second half of the stage): hi 4 KB then lo 4 KB, each [64-column group
+    // g >> 1][8-row atom][8 rows][128 B], 16-byte chunks XOR (row % 8) = SWIZZLE_128B; this thread's 4 columns are 8 B
+    uint32_t boff[4];
+#pragma unroll
+    for (int h = 0; h < 4; ++h) {
+      const int r = rg + 4 * h;
+      boff[h] = (uint32_t)(g >> 1) * 2048u + (uint32_t)(r >> 3) * 1024u + (uint32_t)(r & 7) * 128u +
+                (uint32_t)((((((g & 1) << 2) | (lc >> 1)) ^ (r & 7)) << 4) | ((lc & 1) << 3));
+    }
     int s = 0, pending = 0;
     uint32_t ph = 0;
     float fs[4] = {0.f, 0.f, 0.f, 0.f}, fq[4] = {0.f, 0.f, 0.f, 0.f};
@@ -342,6 +393,25 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
             for (int h = 0; h < 4; ++h) {
               const int i = (c * NLB + lb) * 4 + h;
               const uint32_t a = sx + (uint32_t)(c * NLB + lb) * kSlotBytes + toff[h];
+              if constexpr (BF16) {
+                uint32_t h01 = 0u, h23 = 0u, l01 = 0u, l23 = 0u;
+                if (ok[i]) {
+                  const float y0 = x[i].x - sh[lb].x, y1 = x[i].y - sh[lb].y, y2 = x[i].z - sh[lb].z, y3 = x[i].w - sh[lb].w;
+                  if (lb == 0) {
+                    fs[0] += y0; fs[1] += y1; fs[2] += y2; fs[3] += y3;
+                    fq[0] = fmaf(y0, y0, fq[0]); fq[1] = fmaf(y1, y1, fq[1]);
+                    fq[2] = fmaf(y2, y2, fq[2]); fq[3] = fmaf(y3, y3, fq[3]);
+                  }
+                  h01 = ptx::pack_bf16x2(y0, y1);
+                  h23 = ptx::pack_bf16x2(y2, y3);
+                  // y - bf16(y) is exact in fp32; its bf16 rounding is the second term
+                  l01 = ptx::pack_bf16x2(y0 - __uint_as_float(h01 << 16), y1 - __uint_as_float(h01 & 0xffff0000u));
+                  l23 = ptx::pack_bf16x2(y2 - __uint_as_float(h23 << 16), y3 - __uint_as_float(h23 & 0xffff0000u));
+                }
+                const uint32_t o = sx + half_bytes + (uint32_t)(c * NLB + lb) * kSlotBytes + boff[h];
+                asm volatile("st.shared.v2.b32 [%0], {%1,%2};" ::"r"(o), "r"(h01), "r"(h23) : "memory");
+                asm volatile("st.shared.v2.b32 [%0], {%1,%2};" ::"r"(o + 4096u), "r"(l01), "r"(l23) : "memory");
+              } else {
               float4 hi = make_float4(0.f, 0.f, 0.f, 0.f), lo = hi;
               if (ok[i]) {
                 const float y0 = x[i].x - sh[lb].x, y1 = x[i].y - sh[lb].y, y2 = x[i].z - sh[lb].z, y3 = x[i].w - sh[lb].w;
@@ -355,6 +425,7 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
               }
               asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(a), "f"(hi.x), "f"(hi.y), "f"(hi.z), "f"(hi.w) : "memory");
               asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(a + half_bytes), "f"(lo.x), "f"(lo.y), "f"(lo.z), "f"(lo.w) : "memory");
+              }
             }
       };
       if (trace & 4) {
@@ -400,7 +471,7 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
     const uint32_t acc_empty_leader = ptx::mapa(ptx::smem_u32(&bar_acc_empty[0]), 0);
     int window = 0;
     // a window of fc stages lasts about fc * kt / 8 * nchunk * 384 cycles; spend ~1/3 of it draining
-    const unsigned pace_ns = (unsigned)(fc * kt * nchunk * 48 / 3 / 4 / 2);  // cycles -> ~ns at 2 GHz, per part
+    const unsigned pace_ns = (unsigned)(fc * kt * nchunk * 48 / 3 / 4 / 2) / (BF16 ? 2u : 1u);  // cycles -> ~ns at 2 GHz, per part
     int wpos = stagger;
     for (int it = 0; it < my_chunks; ++it) {
       if (++wpos != fc && it != my_chunks - 1) continue;
@@ -535,12 +606,19 @@ namespace {
 // Relative cost of a job per row (x10): MMA time is 2 : 3 per chunk, but an off-diagonal job converts
 // two blocks per 16 rows against a diagonal job's one per 16 rows, and conversion is not free.
 // DR4G_OCOST overrides the off-diagonal figure (tuning hook).
-int job_cost(const PJob& j) {
+// bf16x3: the pass is bound by shared-memory bytes per 16 rows and CTA (TMA write + converter read + converter write +
+// operand reads): diagonal 8 + 8 + 8 + 2 x 8 = 40 KB, one off-diagonal chunk 16 + 16 + 16 + 3 x 8 = 72 KB, two chunks
+// 24 + 24 + 24 + 6 x 8 = 120 KB (tensor time 256 / 384 / 768 cycles): 20 : 36 : 60.  DR4G_OCOST_BF16 / DR4G_OCOST2_BF16 override.
+int job_cost(const PJob& j, bool bf16) {
   static const int ocost = getenv("DR4G_OCOST") ? atoi(getenv("DR4G_OCOST")) : 40;  // 26..42 swept on B200: 40 is best at d = 512 and 1024
-  return j.diag ? 20 : ocost * j.nchunk;
+  static const int ocost_b = getenv("DR4G_OCOST_BF16") ? atoi(getenv("DR4G_OCOST_BF16")) : 36;
+  static const int ocost2_b = getenv("DR4G_OCOST2_BF16") ? atoi(getenv("DR4G_OCOST2_BF16")) : 60;
+  if (j.diag) return 20;
+  if (bf16) return j.nchunk == 2 ? ocost2_b : ocost_b;
+  return ocost * j.nchunk;
 }
 
-bool build_pair_jobs(int d, int sm_count, PJobTable& tab) {
+bool build_pair_jobs(int d, int sm_count, bool bf16, PJobTable& tab) {
   const int T = (d + kBlk - 1) / kBlk;
   const int S = (T + 1) / 2;
   const int clusters = sm_count / 2;
@@ -549,7 +627,7 @@ bool build_pair_jobs(int d, int sm_count, PJobTable& tab) {
   auto push = [&](const PJob& j) {
     if (tab.njobs == kMaxPJobs) return false;
     tab.job[tab.njobs++] = j;
-    total_cost += job_cost(j);
+    total_cost += job_cost(j, bf16);
     return true;
   };
   for (int I = 0; I < S; ++I) {
@@ -582,7 +660,7 @@ bool build_pair_jobs(int d, int sm_count, PJobTable& tab) {
   if (tab.njobs > clusters) return false;
   int given = 0;
   for (int i = 0; i < tab.njobs; ++i) {
-    int m = (int)((long long)clusters * job_cost(tab.job[i]) / total_cost);
+    int m = (int)((long long)clusters * job_cost(tab.job[i], bf16) / total_cost);
     if (m < 1) m = 1;
     tab.job[i].ncl = m;
     given += m;
@@ -592,7 +670,7 @@ bool build_pair_jobs(int d, int sm_count, PJobTable& tab) {
     int best = 0;
     double worst = -1.0;
     for (int i = 0; i < tab.njobs; ++i) {
-      const double load = (double)job_cost(tab.job[i]) / tab.job[i].ncl;
+      const double load = (double)job_cost(tab.job[i], bf16) / tab.job[i].ncl;
       if (load > worst) { worst = load; best = i; }
     }
     tab.job[best].ncl++;
@@ -603,7 +681,7 @@ bool build_pair_jobs(int d, int sm_count, PJobTable& tab) {
     double least = 1e30;
     for (int i = 0; i < tab.njobs; ++i) {
       if (tab.job[i].ncl <= 1) continue;
-      const double load = (double)job_cost(tab.job[i]) / (tab.job[i].ncl - 1);
+      const double load = (double)job_cost(tab.job[i], bf16) / (tab.job[i].ncl - 1);
       if (load < least) { least = load; best = i; }
     }
     if (best < 0) return false;
@@ -630,7 +708,7 @@ bool gram_pair_eligible(const Ctx& c, const float* dX, long long n, int d) {
   if (n >= (1ll << 31)) return false;                               // TMA coordinates are int32
   if (c.sm_count < 2) return false;
   PJobTable tab;
-  return build_pair_jobs(d, c.sm_count, tab);
+  return build_pair_jobs(d, c.sm_count, c.gram_split != 1, tab);
 }
 
 size_t gram_pair_workspace_bytes(const Ctx& c, int d) {
@@ -639,8 +717,9 @@ size_t gram_pair_workspace_bytes(const Ctx& c, int d) {
 
 void launch_gram_pair(Ctx& c, const float* dX, long long n, int d, const float* dshift, double* dG, double* dsum,
                       double* dsumsq, void* workspace) {
+  const bool bf16 = c.gram_split != 1;   // 0 auto / 2: bf16x3, 1: 3xTF32
   PJobTable tab;
-  if (!build_pair_jobs(d, c.sm_count, tab)) fail("gram_pair: d=%d does not fit the job table", d);
+  if (!build_pair_jobs(d, c.sm_count, bf16, tab)) fail("gram_pair: d=%d does not fit the job table", d);
   // X as a 3-D tensor: (column within a 32-column group, row, column group); one box = 32 x 16 x 4
   CUtensorMap tmap;
   const cuuint64_t gdim[3] = {32, (cuuint64_t)n, (cuuint64_t)(d / 32)};
@@ -654,9 +733,11 @@ void launch_gram_pair(Ctx& c, const float* dX, long long n, int d, const float* 
   if (r != CUDA_SUCCESS) fail("cuTensorMapEncodeTiled (3-D) failed (%d) for n=%lld d=%d", (int)r, n, d);
 
   const int smem = kRingBytes + 1024;
-  static PerDeviceMax smem_set;
-  if (smem_set.need(c.device, (size_t)smem))
-    DR4G_CUDA(cudaFuncSetAttribute(gram_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  static PerDeviceMax smem_set[2];
+  if (smem_set[bf16 ? 1 : 0].need(c.device, (size_t)smem)) {
+    if (bf16) DR4G_CUDA(cudaFuncSetAttribute(gram_pair_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    else DR4G_CUDA(cudaFuncSetAttribute(gram_pair_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  }
 
   static const int trace = getenv("DR4G_GRAM_TRACE") ? atoi(getenv("DR4G_GRAM_TRACE")) : 0;  // bit 0 trace (CTA = value >> 8), 2 no MMA, 4 no conversion
   const int flush_rows = c.flush_rows > 0 ? c.flush_rows : 1024;
@@ -674,8 +755,11 @@ void launch_gram_pair(Ctx& c, const float* dX, long long n, int d, const float* 
   at[0].val.clusterDim.z = 1;
   lc.attrs = at;
   lc.numAttrs = 1;
-  DR4G_CUDA(cudaLaunchKernelEx(&lc, gram_pair_kernel, tmap, tab, n, d, dshift, slab, dsum, dsumsq, flush_rows,
-                               trace));
+  if (bf16)
+    DR4G_CUDA(cudaLaunchKernelEx(&lc, gram_pair_kernel<true>, tmap, tab, n, d, dshift, slab, dsum, dsumsq, flush_rows, trace));
+  else
+    DR4G_CUDA(cudaLaunchKernelEx(&lc, gram_pair_kernel<false>, tmap, tab, n, d, dshift, slab, dsum, dsumsq, flush_rows, trace));
+  c.last_gram_kernel = bf16 ? 3 : 2;
   c.launches++;
   if (trace & 1) {
     static long long h[kTraceIts * 8];

@@ -53,7 +53,7 @@ template <typename T>
 __global__ void gather_kernel(const double* __restrict__ keys, const int* __restrict__ sel,
                               const double* __restrict__ V, int ldv, bool vectors_in_rows, int d, int k,
                               const double* __restrict__ n_ptr, const double* __restrict__ total_var,
-                              const double* __restrict__ mean_d, T* __restrict__ Q, T* __restrict__ w,
+                              const double* __restrict__ mean_d, bool whiten, T* __restrict__ Q, T* __restrict__ w,
                               T* __restrict__ ev, T* __restrict__ evr, T* __restrict__ mean) {
   const int i = blockIdx.x;
   const int j = sel[i];
@@ -82,7 +82,16 @@ __global__ void gather_kernel(const double* __restrict__ keys, const int* __rest
     }
     __syncthreads();
   }
-  const double sgn = (besti[0] < d && at(besti[0]) < 0.0) ? -1.0 : 1.0;
+  double sgn = (besti[0] < d && at(besti[0]) < 0.0) ? -1.0 : 1.0;
+  if (whiten) {
+    // opt-in (PCA(whiten=True)): component rows / sqrt(explained_variance), so that the scores X_c Q^T have unit
+    // variance.  What the reference's GPU code attempts at src/tsvd.cu:195-207 (it indexes lambda by feature there);
+    // its CPU backend - the parity oracle - ignores the flag, so nothing changes when it is off.
+    double lam = keys[j];
+    const double nn = *n_ptr;
+    const double e = (lam > 0 ? lam : 0) / (nn - 1 > 1 ? nn - 1 : 1);
+    sgn = e > 0 ? sgn / sqrt(e) : 0.0;
+  }
   for (int c = threadIdx.x; c < d; c += blockDim.x) Q[(size_t)i * d + c] = (T)(sgn * at(c));
   if (threadIdx.x == 0) {
     double lam = keys[j];
@@ -104,20 +113,20 @@ __global__ void gather_kernel(const double* __restrict__ keys, const int* __rest
 template <typename T>
 void launch_postproc(Ctx& c, const double* dW, int nw, const double* dV, int ldv, bool vectors_in_rows,
                      bool check_mass, int d, int k, const double* packed_n, const double* dtotal_var, const double* dmean_d,
-                     T* dQ, T* dw, T* dev, T* devr, T* dmean) {
+                     T* dQ, T* dw, T* dev, T* devr, T* dmean, bool whiten) {
   double* keys = c.arena.take_n<double>(nw);
   int* sel = c.arena.take_n<int>(k);
   keys_kernel<<<ceil_div(nw, 4), 128, 0, c.stream>>>(dW, nw, dV, ldv, vectors_in_rows, check_mass, d, keys);
   rank_kernel<<<ceil_div(nw, 128), 128, 0, c.stream>>>(keys, nw, k, sel);
   gather_kernel<T><<<k, 256, 0, c.stream>>>(keys, sel, dV, ldv, vectors_in_rows, d, k, packed_n, dtotal_var,
-                                            dmean_d, dQ, dw, dev, devr, dmean);
+                                            dmean_d, whiten, dQ, dw, dev, devr, dmean);
   c.launches += 3;
   DR4G_CUDA(cudaGetLastError());
 }
 
 template void launch_postproc<float>(Ctx&, const double*, int, const double*, int, bool, bool, int, int, const double*,
-                                     const double*, const double*, float*, float*, float*, float*, float*);
+                                     const double*, const double*, float*, float*, float*, float*, float*, bool);
 template void launch_postproc<double>(Ctx&, const double*, int, const double*, int, bool, bool, int, int, const double*,
-                                      const double*, const double*, double*, double*, double*, double*, double*);
+                                      const double*, const double*, double*, double*, double*, double*, double*, bool);
 
 }  // namespace dr4g

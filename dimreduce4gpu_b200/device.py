@@ -110,7 +110,8 @@ class DeviceContext:
 
     # ------------------------------------------------------------------ fit / transform
     def fit(self, X, n_components: int, center: bool, algorithm: str = "cusolver", n_iter: int = 5,
-            random_state: int = 0, tol: float = 1e-5, verbose: bool = False, out: Optional[dict] = None) -> dict:
+            random_state: int = 0, tol: float = 1e-5, verbose: bool = False, out: Optional[dict] = None,
+            whiten: bool = False) -> dict:
         """X: (n_local, d) CUDA tensor, this rank's row shard.  Returns device tensors
         components (k,d), singular_values, explained_variance, explained_variance_ratio (k,), mean (d,)|None.
         Asynchronous on the current torch stream."""
@@ -130,7 +131,7 @@ class DeviceContext:
         p.X_n, p.X_m, p.k = min(n, 2**31 - 1), d, k
         p.algorithm = algorithm.encode("utf-8")
         p.n_iter, p.random_state, p.tol = int(n_iter), int(random_state) & 0x7FFFFFFF, float(tol)
-        p.verbose, p.gpu_id, p.whiten = int(bool(verbose)), self.device, False
+        p.verbose, p.gpu_id, p.whiten = int(bool(verbose)), self.device, bool(whiten)
         self._on_torch_stream()
         mean_ptr = out["mean"].data_ptr() if center else None
         rc = getattr(self._lib, f"dr4g_fit_{sfx}")(
@@ -138,6 +139,33 @@ class DeviceContext:
             out["singular_values"].data_ptr(), out["explained_variance"].data_ptr(),
             out["explained_variance_ratio"].data_ptr(), mean_ptr)
         _check(rc, f"dr4g_fit_{sfx}")
+        return out
+
+    def fit_transform_host(self, X: np.ndarray, n_components: int, center: bool, algorithm: str = "cusolver",
+                           n_iter: int = 5, random_state: int = 0, tol: float = 1e-5, verbose: bool = False,
+                           whiten: bool = False, want_u: bool = True, out: Optional[dict] = None) -> dict:
+        """Host-resident row shard (numpy, C-contiguous fp32/fp64; pinned or pageable) -> model + this shard's scores
+        in host arrays (dr4g_fit_transform_host_*).  With a communicator the fit is the row-sharded one.  Blocking."""
+        if X.ndim != 2 or not X.flags.c_contiguous or X.dtype not in (np.float32, np.float64):
+            raise ValueError("X must be a C-contiguous 2-D float32/float64 array")
+        n, d = X.shape
+        k = min(int(n_components), d) if self.world > 1 else min(int(n_components), n, d)
+        sfx = "float" if X.dtype == np.float32 else "double"
+        if out is None:
+            z = lambda *s: np.zeros(s, dtype=X.dtype)  # noqa: E731
+            out = dict(components=z(k, d), singular_values=z(k), explained_variance=z(k), explained_variance_ratio=z(k),
+                       mean=z(d) if center else None, X_transformed=z(n, k), U=z(n, k) if want_u else None)
+        p = params()
+        p.X_n, p.X_m, p.k = min(n, 2**31 - 1), d, k
+        p.algorithm = algorithm.encode("utf-8")
+        p.n_iter, p.random_state, p.tol = int(n_iter), int(random_state) & 0x7FFFFFFF, float(tol)
+        p.verbose, p.gpu_id, p.whiten = int(bool(verbose)), self.device, bool(whiten)
+        ptr = lambda a: a.ctypes.data if a is not None else None  # noqa: E731
+        rc = getattr(self._lib, f"dr4g_fit_transform_host_{sfx}")(
+            self._h, ptr(X), n, d, k, 1 if center else 0, p, ptr(out["components"]), ptr(out["singular_values"]),
+            ptr(out.get("U")), ptr(out["X_transformed"]), ptr(out["explained_variance"]),
+            ptr(out["explained_variance_ratio"]), ptr(out["mean"]) if center else None)
+        _check(rc, f"dr4g_fit_transform_host_{sfx}")
         return out
 
     # ------------------------------------------------------------------ streaming fit (SURVEY 8f-1)
@@ -160,7 +188,8 @@ class DeviceContext:
         _check(self._lib.dr4g_partial_fit_reset(self._h), "dr4g_partial_fit_reset")
 
     def partial_fit_finalize(self, n_features: int, n_components: int, center: bool, dtype, algorithm: str = "cusolver",
-                             n_iter: int = 5, random_state: int = 0, tol: float = 1e-5, verbose: bool = False) -> dict:
+                             n_iter: int = 5, random_state: int = 0, tol: float = 1e-5, verbose: bool = False,
+                             whiten: bool = False) -> dict:
         """Eigensolve + outputs from the accumulated chunks; same result dictionary as fit()."""
         import torch
 
@@ -178,7 +207,7 @@ class DeviceContext:
         p.X_n, p.X_m, p.k = min(rows, 2**31 - 1), d, k
         p.algorithm = algorithm.encode("utf-8")
         p.n_iter, p.random_state, p.tol = int(n_iter), int(random_state) & 0x7FFFFFFF, float(tol)
-        p.verbose, p.gpu_id, p.whiten = int(bool(verbose)), self.device, False
+        p.verbose, p.gpu_id, p.whiten = int(bool(verbose)), self.device, bool(whiten)
         self._on_torch_stream()
         rc = getattr(self._lib, f"dr4g_partial_fit_finalize_{sfx}")(
             self._h, k, p, out["components"].data_ptr(), out["singular_values"].data_ptr(),
@@ -299,7 +328,7 @@ class DeviceContext:
 
     @property
     def last_gram_path(self) -> str:
-        return {0: "none", 1: "generic_dmma", 2: "tcgen05", 3: "tcgen05_pair"}[int(self._lib.dr4g_last_gram_path(self._h))]
+        return {0: "none", 1: "generic_dmma", 2: "tcgen05", 3: "tcgen05_pair", 4: "tcgen05_pair_bf16x3"}[int(self._lib.dr4g_last_gram_path(self._h))]
 
     @property
     def launch_count(self) -> int:

@@ -37,6 +37,8 @@ def _bind(lib: ctypes.CDLL) -> None:
         # device-pointer API: pointers are passed as integers (tensor.data_ptr())
         f = getattr(lib, f"dr4g_fit_{name}")
         f.argtypes, f.restype = [vp, vp, ll, ci, ci, ci, params, vp, vp, vp, vp, vp], ci
+        f = getattr(lib, f"dr4g_fit_transform_host_{name}")
+        f.argtypes, f.restype = [vp, vp, ll, ci, ci, ci, params, vp, vp, vp, vp, vp, vp, vp], ci
         f = getattr(lib, f"dr4g_partial_fit_{name}")
         f.argtypes, f.restype = [vp, vp, ll, ci, ci], ci
         f = getattr(lib, f"dr4g_partial_fit_finalize_{name}")
@@ -77,6 +79,7 @@ EXPORTED_SYMBOLS = (
     "dr4g_inverse_transform_float", "dr4g_inverse_transform_double", "dr4g_colstats_float",
     "dr4g_colstats_double", "dr4g_gram_float", "dr4g_gram_double", "dr4g_eigh_double", "dr4g_eigh_topk_double", "dr4g_stage_times",
     "dr4g_last_gram_path", "dr4g_launch_count",
+    "dr4g_fit_transform_host_float", "dr4g_fit_transform_host_double",
     "dr4g_partial_fit_float", "dr4g_partial_fit_double", "dr4g_partial_fit_finalize_float",
     "dr4g_partial_fit_finalize_double", "dr4g_partial_fit_reset", "dr4g_partial_fit_rows",
 )

@@ -1,6 +1,9 @@
 """PCA estimator - same surface as the reference (dimreduce4gpu/pca.py:15-94): TruncatedSVD of the
-column-centred data, plus ``mean_``.  ``whiten`` is accepted and ignored exactly as the reference's
-CPU backend (the parity oracle) ignores it."""
+column-centred data, plus ``mean_``.  ``whiten=True`` is an opt-in the GPU applies (K6, csrc/postproc.cu): the rows
+of ``components_`` are divided by sqrt(explained_variance_), so the scores have unit variance and
+``inverse_transform`` undoes it.  That is what the reference's GPU code intends at src/tsvd.cu:195-207 (it indexes
+lambda by feature there, a bug); the reference's CPU backend - the parity oracle - ignores the flag, and with
+``whiten=False`` (default) nothing changes."""
 from __future__ import annotations
 
 from typing import Optional

@@ -102,13 +102,22 @@ class TruncatedSVD:
 
     def fit(self, X, y=None):
         if _is_torch_cuda(X):
+            select_backend(self.backend)
+            self._drop_stream_state()
             self._fit_device(X, want_scores=False)
         else:
             self.fit_transform(X)
         return self
 
+    def _drop_stream_state(self):
+        """A one-shot fit replaces whatever partial_fit accumulated: without this a later read of components_ would
+        finalize the stale chunks over the fresh fit."""
+        if getattr(self, "_stream_dirty", False) or getattr(self, "_stream_d", None) is not None:
+            self.reset_partial_fit()
+
     def fit_transform(self, X):
         select_backend(self.backend)
+        self._drop_stream_state()
         if _is_torch_cuda(X):
             return self._fit_device(X, want_scores=True)
         X = np.ascontiguousarray(_densify(X), dtype=self.dtype)
@@ -146,7 +155,8 @@ class TruncatedSVD:
         """X is a torch CUDA tensor: nothing leaves the device except the k- and d-sized results."""
         ctx = _device_context(X.device.index)
         res = ctx.fit(X, self.n_components, center=self._center, algorithm=self.algorithm, n_iter=self.n_iter,
-                      random_state=self.random_state, tol=self.tol, verbose=self.verbose)
+                      random_state=self.random_state, tol=self.tol, verbose=self.verbose,
+                      whiten=bool(getattr(self, "whiten", False)))
         self._Q_dev, self._w_dev, self._mean_dev = res["components"], res["singular_values"], res["mean"]
         Z = None
         if want_scores:
@@ -197,7 +207,8 @@ class TruncatedSVD:
         with torch.cuda.device(self._sctx.device):
             res = self._sctx.partial_fit_finalize(self._stream_d, self.n_components, self._center, tdt,
                                                   algorithm=self.algorithm, n_iter=self.n_iter,
-                                                  random_state=self.random_state, tol=self.tol, verbose=self.verbose)
+                                                  random_state=self.random_state, tol=self.tol, verbose=self.verbose,
+                                                  whiten=bool(getattr(self, "whiten", False)))
             self._sctx.sync()
         self._Q = res["components"].cpu().numpy()
         self._w = res["singular_values"].cpu().numpy()
@@ -250,6 +261,9 @@ class TruncatedSVD:
         Q = self.components_
         tdt = torch.float32 if Q.dtype == np.float32 else torch.float64
         Zd, on_dev = self._to_device(Z, tdt)
+        if getattr(self, "whiten", False):
+            # components_ rows carry 1/sqrt(ev): Xc = sum_i z_i ev_i q_i
+            Zd = Zd * torch.from_numpy(np.ascontiguousarray(self.explained_variance_)).to(Zd.device, Zd.dtype)
         ctx = _device_context(Zd.device.index)
         Qd = torch.from_numpy(np.ascontiguousarray(Q)).to(Zd.device)
         md = torch.from_numpy(np.ascontiguousarray(self.mean_)).to(Zd.device) if self.mean_ is not None else None

@@ -84,6 +84,7 @@ DR4G_EXPORT int dr4g_ctx_set_stream(dr4g_ctx* ctx, void* cuda_stream);
 /* Block until everything enqueued on the context's stream is done; returns deferred errors. */
 DR4G_EXPORT int dr4g_sync(dr4g_ctx* ctx);
 /* Tunables / test hooks.  Keys: "gram_path" (0 auto, 1 generic DMMA kernel, 2 tcgen05 kernels, 3 tcgen05 single-CTA kernel only),
+ * "gram_split" (CTA-pair kernel operands: 0 auto = 2 bf16x3 on kind::f16, 1 = 3xTF32 on kind::tf32),
  * "flush_rows" (rows between TMEM accumulator flushes), "pilot_rows", "jacobi_tol", "jacobi_sweeps",
  * "eig_solver" (exact path: 0 tridiagonal route for the top k, 1 blocked Jacobi), "timing". */
 DR4G_EXPORT int dr4g_set_option(dr4g_ctx* ctx, const char* key, double value);
@@ -104,6 +105,18 @@ DR4G_EXPORT int dr4g_fit_float(dr4g_ctx* ctx, const float* dX, long long n_local
                    params p, float* dQ, float* dw, float* dev, float* devr, float* dmean);
 DR4G_EXPORT int dr4g_fit_double(dr4g_ctx* ctx, const double* dX, long long n_local, int d, int k, int center,
                     params p, double* dQ, double* dw, double* dev, double* devr, double* dmean);
+
+/* Host-resident row shard in, host results out, on THIS context: what the legacy symbols do behind
+ * truncated_svd.py:98-107 / pca.py:73-86 (H2D of X, fit, projection, D2H of the scores), but on a caller-owned context
+ * so that a communicator set with dr4g_comm_init is honoured: X is then this rank's shard (n_local rows) of a
+ * row-sharded matrix and Q, w, ev, evr, mean are the global model; U / Xt (n_local x k, each may be NULL) are the
+ * shard's scores.  All pointers are host memory (pinned or pageable).  Blocking.  Out of core when the shard does not
+ * fit in free device memory (second H2D sweep for the scores). */
+DR4G_EXPORT int dr4g_fit_transform_host_float(dr4g_ctx* ctx, const float* X, long long n_local, int d, int k, int center,
+                                  params p, float* Q, float* w, float* U, float* Xt, float* ev, float* evr, float* mean);
+DR4G_EXPORT int dr4g_fit_transform_host_double(dr4g_ctx* ctx, const double* X, long long n_local, int d, int k, int center,
+                                   params p, double* Q, double* w, double* U, double* Xt, double* ev, double* evr,
+                                   double* mean);
 
 /* Streaming (out-of-core) fit, SURVEY 8f-1: the packed accumulators [G | s | q | n] of the fit are summed
  * over row chunks, so X never has to be device-resident as a whole (the reference's host-pointer symbols,
@@ -162,7 +175,7 @@ DR4G_EXPORT int dr4g_eigh_topk_double(dr4g_ctx* ctx, double* dA, int d, int k, d
  * [3] eigensolve (Jacobi or subspace iteration), [4] sort/flip/outputs, [5] total.
  * Returns the number of entries written (<= n). */
 DR4G_EXPORT int dr4g_stage_times(dr4g_ctx* ctx, double* ms, int n);
-/* Which Gram kernel the last fit used (1 generic DMMA, 2 tcgen05 single-CTA, 3 tcgen05 CTA pairs), and launches it issued. */
+/* Which Gram kernel the last fit used (1 generic DMMA, 2 tcgen05 single-CTA, 3 tcgen05 CTA pairs 3xTF32, 4 tcgen05 CTA pairs bf16x3), and launches it issued. */
 DR4G_EXPORT int dr4g_last_gram_path(dr4g_ctx* ctx);
 DR4G_EXPORT long long dr4g_launch_count(dr4g_ctx* ctx);
 

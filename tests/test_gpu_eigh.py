@@ -51,6 +51,34 @@ def test_eigh_topk_matches_lapack(kind, d, k):
     assert np.max(np.abs(Vt @ Vt.T - np.eye(k))) < 1e-11
 
 
+@pytest.mark.parametrize("d,k,kind", [(1024, 64, "aniso"), (1030, 16, "lowrank"), (2048, 40, "aniso"), (4096, 100, "geom")])
+def test_eigh_topk_large_d_matches_lapack(d, k, kind):
+    """d > 512: the cooperative-grid tridiagonalisation (rows in shared memory at 1024, in L2 above), the inverse
+    iteration at its shared-memory limit (d = 4096 = BASELINE config 5) and the CTA-per-vector back-transformation."""
+    import torch
+
+    import dimreduce4gpu_b200 as pkg
+
+    if kind == "geom":
+        rng = np.random.default_rng(d)
+        X = rng.standard_normal((d + 200, d)) * np.geomspace(4.0, 0.5, d)
+        A = X.T @ X
+    else:
+        A = _sym(d, kind, 7 * d + k)
+    ctx = pkg.DeviceContext(0)
+    w, Vt = ctx.eigh_topk(torch.from_numpy(A).cuda(), k)
+    ctx.sync()
+    w, Vt = w.cpu().numpy(), Vt.cpu().numpy()
+    ev = np.linalg.eigvalsh(A)
+    wr, scale = ev[::-1][:k], np.abs(ev).max()
+    e_w = np.max(np.abs(w - wr)) / scale
+    e_r = np.max(np.linalg.norm(A @ Vt.T - Vt.T * w, axis=0)) / scale
+    e_o = np.max(np.abs(Vt @ Vt.T - np.eye(k)))
+    msg = f"d={d} k={k} {kind}: eigenvalue err {e_w:.2e}, residual {e_r:.2e}, orthogonality {e_o:.2e}"
+    print(msg)
+    assert e_w < 1e-12 and e_r < 1e-11 and e_o < 1e-10, msg
+
+
 @pytest.mark.parametrize("d", [5, 64, 200])
 def test_jacobi_all_pairs_matches_lapack(d):
     import torch
