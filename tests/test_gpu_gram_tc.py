@@ -74,9 +74,44 @@ def test_pair_kernel_agrees_with_single_cta_kernel(n, d):
     Gp = cp.gram(X).clone()
     Gs = cs.gram(X).clone()
     torch.cuda.synchronize()
-    assert cp.last_gram_path == "tcgen05_pair" and cs.last_gram_path == "tcgen05"
+    assert cp.last_gram_path.startswith("tcgen05_pair") and cs.last_gram_path == "tcgen05"
     dg = torch.sqrt(torch.diag(Gs))
     assert float(((Gp - Gs).abs() / (dg[:, None] * dg[None, :])).max()) < GRAM_TOL
+
+
+@pytest.mark.parametrize("n,d", [(5000, 256), (3001, 320), (70000, 512), (4096, 1024), (33, 512), (300000, 256)])
+@pytest.mark.parametrize("split,name,tol", [(1, "tcgen05_pair", GRAM_TOL), (2, "tcgen05_pair_bf16x3", GRAM_TOL)])
+def test_pair_kernel_both_operand_splits(n, d, split, name, tol):
+    """gram_split=1: 3xTF32 on kind::tf32; gram_split=2 (the default): two bf16 terms, three kind::f16 products.  Both
+    against the fp64 product at the same gate; the achieved error is printed."""
+    ctx = _ctx(2, gram_split=split)
+    X = _make(n, d, 13 * n + d)
+    shift = X[: min(n, 4096)].mean(0).contiguous()
+    G = ctx.gram(X, shift)
+    ctx.sync()
+    assert ctx.last_gram_path == name
+    err = _rel_err(G, X.double() - shift.double())
+    print(f"n={n} d={d} {name}: max |G - G_fp64| / sqrt(G_ii G_jj) = {err:.2e}")
+    assert err < tol, err
+    assert float((G - G.T).abs().max()) == 0.0
+
+
+def test_bf16x3_split_on_badly_scaled_columns():
+    """Column scales from 1e-6 to 1e6 and a duplicated column: bf16 keeps the fp32 exponent range, so the error stays
+    relative to sqrt(G_ii G_jj) per entry; the duplicate must give an exactly symmetric, consistent 2 x 2 block."""
+    import torch
+
+    n, d = 40000, 256
+    X = _make(n, d, 77, offset=0.0) * torch.logspace(-6, 6, d, device="cuda")
+    X[:, 17] = X[:, 200]
+    ctx = _ctx(2, gram_split=2)
+    G = ctx.gram(X)
+    ctx.sync()
+    assert ctx.last_gram_path == "tcgen05_pair_bf16x3"
+    err = _rel_err(G, X.double())
+    assert err < GRAM_TOL, err
+    a, b, c = float(G[17, 17]), float(G[200, 200]), float(G[17, 200])
+    assert abs(a - b) <= 1e-7 * a and abs(a - c) <= 1e-7 * a, (a, b, c)
 
 
 def test_gram_tc_agrees_with_generic_dmma_path():
