@@ -209,6 +209,10 @@ static void fit_impl(Ctx& c, const T* dX, long long n_local, int d, int k, int c
   if constexpr (sizeof(T) == 4)
     want_tc = c.gram_path != 1 && gram_tc_eligible(c, reinterpret_cast<const float*>(dX), n_local, d);
   if (want_tc) need += up256(gram_tc_workspace_bytes(c, d));
+  bool want_f64 = false;
+  if constexpr (sizeof(T) == 8)
+    want_f64 = c.gram_path != 5 && phase != 2 && gram_f64_eligible(c, reinterpret_cast<const double*>(dX), n_local, d);
+  if (want_f64) need += up256(gram_f64_workspace_bytes(c, n_local, d));
   c.arena.reserve(need);
   c.arena.reset();
 
@@ -276,10 +280,19 @@ static void fit_impl(Ctx& c, const T* dX, long long n_local, int d, int k, int c
   }
   if (!used_tc) {
     launch_colstats<T>(c, dX, n_local, d, shift_arg, s, q);
-    launch_gram_generic<T>(c, dX, n_local, d, shift_arg, G);
+    bool done = false;
+    if constexpr (sizeof(T) == 8) {
+      if (want_f64) {
+        void* ws = c.arena.take(gram_f64_workspace_bytes(c, n_local, d));
+        launch_gram_f64(c, reinterpret_cast<const double*>(dX), n_local, d, reinterpret_cast<const double*>(shift_arg), G, ws);
+        done = true;
+      }
+    }
+    if (!done) launch_gram_generic<T>(c, dX, n_local, d, shift_arg, G);
     launch_mirror_upper(c, G, d);
+    if (done) c.last_gram_kernel = 4;
   }
-  c.last_gram_path = used_tc ? (c.last_gram_kernel == 3 ? 4 : c.last_gram_kernel == 2 ? 3 : 2) : 1;
+  c.last_gram_path = (!used_tc && c.last_gram_kernel == 4) ? 5 : used_tc ? (c.last_gram_kernel == 3 ? 4 : c.last_gram_kernel == 2 ? 3 : 2) : 1;
   launch_set_scalar(c, cnt, (double)n_local);
   }
   if (phase == 1) {
@@ -840,9 +853,17 @@ int dr4g_gram_double(dr4g_ctx* ctx, const double* dX, long long n, int d, const 
   std::lock_guard<std::mutex> lk(ctx->mu);
   DeviceGuard g(ctx->device);
   DR4G_CUDA(cudaMemsetAsync(dG, 0, (size_t)d * d * 8, ctx->stream));
-  launch_gram_generic<double>(*ctx, dX, n, d, dshift, dG);
+  if (ctx->gram_path != 5 && gram_f64_eligible(*ctx, dX, n, d)) {
+    const size_t ws = gram_f64_workspace_bytes(*ctx, n, d);
+    ctx->arena.reserve(ws + 4096);
+    ctx->arena.reset();
+    launch_gram_f64(*ctx, dX, n, d, dshift, dG, ctx->arena.take(ws));
+    ctx->last_gram_path = 5;
+  } else {
+    launch_gram_generic<double>(*ctx, dX, n, d, dshift, dG);
+    ctx->last_gram_path = 1;
+  }
   launch_mirror_upper(*ctx, dG, d);
-  ctx->last_gram_path = 1;
   DR4G_API_END
 }
 

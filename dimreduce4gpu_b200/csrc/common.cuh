@@ -72,7 +72,8 @@ struct Ctx {
   void* comm = nullptr;
   int rank = 0, world = 1;
   // options
-  int gram_path = 0;          // 0 auto, 1 generic, 2 tcgen05 (pair kernel where eligible), 3 tcgen05 single-CTA kernel only
+  int gram_path = 0;          // 0 auto, 1 generic, 2 tcgen05 (pair kernel where eligible), 3 tcgen05 single-CTA kernel only,
+                              // 5 first-generation 64 x 64 DMMA kernel for fp64 input too (cross-check of gram_f64.cu)
   int gram_split = 0;         // pair kernel operand split: 0 auto (bf16x3), 1 3xTF32 (kind::tf32), 2 bf16x3 (kind::f16)
   int flush_rows = 1024;      // rows between TMEM flushes in the tcgen05 Gram
   int pilot_rows = 4096;      // rows sampled for the pilot shift
@@ -99,6 +100,12 @@ void launch_colstats(Ctx& c, const T* dX, long long n, int d, const T* dshift, d
 template <typename T>
 void launch_gram_generic(Ctx& c, const T* dX, long long n, int d, const T* dshift, double* dG);
 void launch_mirror_upper(Ctx& c, double* dG, int d);
+
+// Gram, fp64 input (gram_f64.cu): 128 x 128 DMMA tiles, cp.async ring, persistent schedule, fixed summation order.
+// Writes the upper block triangle (by 128) of dG; mirror_upper() completes it.
+bool gram_f64_eligible(const Ctx& c, const double* dX, long long n, int d);
+size_t gram_f64_workspace_bytes(const Ctx& c, long long n, int d);
+void launch_gram_f64(Ctx& c, const double* dX, long long n, int d, const double* dshift, double* dG, void* workspace);
 
 // Gram + column statistics, tcgen05 path (fp32 input, 3xTF32).  Returns false if the shape is not
 // eligible (caller falls back to the generic path).  Writes the full symmetric dG (double) and,
