@@ -144,6 +144,7 @@ static void ctx_delete(CtxFull* c) {
   for (auto& ev : c->stage_ev) if (ev) cudaEventDestroy(ev);
   c->arena.release();
   c->io.release();
+  if (c->proj_buf) cudaFree(c->proj_buf);
   c->sf.release();
   if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
   if (c->out_stream) cudaStreamDestroy(c->out_stream);
@@ -671,6 +672,7 @@ int dr4g_set_option(dr4g_ctx* ctx, const char* key, double value) {
   const std::string k(key);
   if (k == "gram_path") ctx->gram_path = (int)value;
   else if (k == "gram_split") ctx->gram_split = (int)value;
+  else if (k == "proj_path") ctx->proj_path = (int)value;
   else if (k == "flush_rows") ctx->flush_rows = (int)value;
   else if (k == "pilot_rows") ctx->pilot_rows = (int)value;
   else if (k == "jacobi_tol") ctx->jacobi_tol = value;
@@ -920,6 +922,7 @@ int dr4g_stage_times(dr4g_ctx* ctx, double* ms, int n) {
 }
 
 int dr4g_last_gram_path(dr4g_ctx* ctx) { return ctx ? ctx->last_gram_path : 0; }
+int dr4g_last_proj_path(dr4g_ctx* ctx) { return ctx ? ctx->last_proj_path : 0; }
 long long dr4g_launch_count(dr4g_ctx* ctx) { return ctx ? ctx->launches : 0; }
 
 }  // extern "C"

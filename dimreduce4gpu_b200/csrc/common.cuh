@@ -85,6 +85,11 @@ struct Ctx {
   int last_gram_path = 0;
   int last_gram_kernel = 0;   // tcgen05 path: 1 single-CTA kernel (gram_tc.cu), 2 CTA-pair kernel 3xTF32, 3 CTA-pair kernel bf16x3 (gram_tc2.cu)
   long long launches = 0;
+  // K7 on tcgen05: pre-split components image (grow-only, private to the projection)
+  void* proj_buf = nullptr;
+  size_t proj_cap = 0;
+  int proj_path = 0;          // 0 auto (tcgen05 where eligible), 1 CUDA-core kernels only
+  int last_proj_path = 0;     // 1 CUDA cores, 2 tcgen05
   // tensor-map encoder (driver entry point fetched lazily)
   void* encode_tiled = nullptr;
 };
@@ -159,6 +164,10 @@ void launch_postproc(Ctx& c, const double* dW, int nw, const double* dV, int ldv
 template <typename T>
 void launch_project(Ctx& c, const T* dX, long long n, int d, int k, const T* dQ, const T* dmean,
                     const T* dw, T* dZ, T* dU);
+// tcgen05 projection (project_tc.cu): fp32, k <= 128, k % 4 == 0, d % 4 == 0, 16-byte aligned X / Z / U.
+bool project_tc_eligible(const Ctx& c, const float* dX, long long n, int d, int k, const float* dZ, const float* dU);
+void launch_project_tc(Ctx& c, const float* dX, long long n, int d, int k, const float* dQ, const float* dmean,
+                       const float* dw, float* dZ, float* dU);
 template <typename T>
 void launch_inverse(Ctx& c, const T* dZ, long long n, int d, int k, const T* dQ, const T* dmean, T* dX);
 

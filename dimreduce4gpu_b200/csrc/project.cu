@@ -257,7 +257,13 @@ template <typename T>
 void launch_project(Ctx& c, const T* dX, long long n, int d, int k, const T* dQ, const T* dmean, const T* dw,
                     T* dZ, T* dU) {
   if (n <= 0) return;
+  c.last_proj_path = 1;
   if constexpr (sizeof(T) == 4) {
+    if (c.proj_path != 1 && project_tc_eligible(c, dX, n, d, k, dZ, (dU && dw) ? dU : nullptr)) {
+      launch_project_tc(c, dX, n, d, k, dQ, dmean, dw, dZ, dU);
+      c.last_proj_path = 2;
+      return;
+    }
     // 16-byte aligned rows (float4 loads of X, float4 stores of Z when k % 4 == 0)
     const bool aligned = (reinterpret_cast<uintptr_t>(dX) & 15) == 0 && (d % 4) == 0 &&
                          (reinterpret_cast<uintptr_t>(dZ) & 15) == 0 && (!dU || (reinterpret_cast<uintptr_t>(dU) & 15) == 0);

@@ -84,6 +84,7 @@ DR4G_EXPORT int dr4g_ctx_set_stream(dr4g_ctx* ctx, void* cuda_stream);
 /* Block until everything enqueued on the context's stream is done; returns deferred errors. */
 DR4G_EXPORT int dr4g_sync(dr4g_ctx* ctx);
 /* Tunables / test hooks.  Keys: "gram_path" (0 auto, 1 generic DMMA kernel, 2 tcgen05 kernels, 3 tcgen05 single-CTA kernel only),
+ * "proj_path" (projection: 0 auto = tcgen05 where eligible, 1 CUDA-core kernels),
  * "gram_split" (CTA-pair kernel operands: 0 auto = 2 bf16x3 on kind::f16, 1 = 3xTF32 on kind::tf32),
  * "flush_rows" (rows between TMEM accumulator flushes), "pilot_rows", "jacobi_tol", "jacobi_sweeps",
  * "eig_solver" (exact path: 0 tridiagonal route for the top k, 1 blocked Jacobi), "timing". */
@@ -177,6 +178,8 @@ DR4G_EXPORT int dr4g_eigh_topk_double(dr4g_ctx* ctx, double* dA, int d, int k, d
 DR4G_EXPORT int dr4g_stage_times(dr4g_ctx* ctx, double* ms, int n);
 /* Which Gram kernel the last fit used (1 generic DMMA, 2 tcgen05 single-CTA, 3 tcgen05 CTA pairs 3xTF32, 4 tcgen05 CTA pairs bf16x3), and launches it issued. */
 DR4G_EXPORT int dr4g_last_gram_path(dr4g_ctx* ctx);
+/* Which projection kernel the last transform used: 1 CUDA cores (project.cu), 2 tcgen05 (project_tc.cu). */
+DR4G_EXPORT int dr4g_last_proj_path(dr4g_ctx* ctx);
 DR4G_EXPORT long long dr4g_launch_count(dr4g_ctx* ctx);
 
 #ifdef __cplusplus

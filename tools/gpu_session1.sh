@@ -8,6 +8,8 @@ timeout 600 python -m pytest tests/test_gpu_gram_tc.py -x -q -m gpu -s > gpurun_
 tail -5 gpurun_out/s1_pytest_gram.log
 timeout 600 python -m pytest tests/test_gpu_gram_f64.py -x -q -m gpu > gpurun_out/s1_pytest_f64.log 2>&1; echo "f64 gram rc=$?"
 tail -5 gpurun_out/s1_pytest_f64.log
+timeout 600 python -m pytest tests/test_gpu_project_tc.py -x -q -m gpu -s > gpurun_out/s1_pytest_proj.log 2>&1; echo "proj rc=$?"
+tail -25 gpurun_out/s1_pytest_proj.log
 timeout 300 python tools/measure_peaks.py gpurun_out/r02_measured_peaks.json > gpurun_out/s1_peaks.log 2>&1; echo "peaks rc=$?"
 for split in 1 2; do
   for ocost in 36; do
