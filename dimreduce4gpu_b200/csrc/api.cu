@@ -178,6 +178,12 @@ static void allreduce_f64(Ctx& c, double* buf, size_t count) {
   if (rc != 0) fail("ncclAllReduce failed: %s", api->GetErrorString(rc));
 }
 
+static void allgather_f64(Ctx& c, const double* send, double* recv, size_t count) {
+  NcclApi* api = nccl_api();
+  int rc = api->AllGather(send, recv, count, kNcclFloat64, c.comm, c.stream);
+  if (rc != 0) fail("ncclAllGather failed: %s", api->GetErrorString(rc));
+}
+
 constexpr int kOversample = 10;  // same block oversampling as the CPU backend's randomized path (src/cpu_backend.cpp:170)
 
 template <typename T>
@@ -190,14 +196,16 @@ static void fit_impl(Ctx& c, const T* dX, long long n_local, int d, int k, int c
   const bool exact = is_exact(p);
   const size_t dd = (size_t)d * d;
   const size_t packed_count = dd + 2 * (size_t)d + 1;
+  const size_t ext_count = packed_count + (size_t)d;   // + this rank's pilot shift: what travels in the exchange
   const int dp = jacobi_padded_dim(d);
   int l = k + kOversample;
   if (l > d) l = d;
   const int lp = power_padded_block(l);
 
   // workspace
-  size_t need = up256(packed_count * 8) + up256((size_t)d * 8) * 4 + up256((size_t)d * sizeof(T)) + up256(dd * 8) + 4096;
+  size_t need = 2 * up256(ext_count * 8) + up256((size_t)d * 8) * 4 + up256((size_t)d * sizeof(T)) + up256(dd * 8) + 4096;
   need += up256(((size_t)d + 1) * 8);
+  if (c.world > 1 && center) need += up256((size_t)c.world * ext_count * 8);
   const bool use_jacobi = c.eig_solver == 1;
   if (exact && use_jacobi)
     need += 2 * up256((size_t)dp * dp * 8) + up256((size_t)dp * 8) + up256(jacobi_workspace_bytes(dp));
@@ -217,13 +225,13 @@ static void fit_impl(Ctx& c, const T* dX, long long n_local, int d, int k, int c
   c.arena.reserve(need);
   c.arena.reset();
 
-  double* packed = c.arena.take_n<double>(packed_count);
+  double* packed = c.arena.take_n<double>(ext_count);   // [G | s | q | n | c]
   double* G = packed;
   double* s = packed + dd;
   double* q = s + d;
   double* cnt = q + d;
   double* pilot = c.arena.take_n<double>((size_t)d + 1);
-  double* shift_d = c.arena.take_n<double>(d);
+  double* shift_d = cnt + 1;                            // the pilot shift travels with the moments
   T* shift_t = c.arena.take_n<T>(d);
   if (sf) {
     shift_d = sf->shift_d;
@@ -237,8 +245,8 @@ static void fit_impl(Ctx& c, const T* dX, long long n_local, int d, int k, int c
   c.stage_valid = false;
   mark(0);
 
-  // [0] pilot shift: every rank contributes its first rows; the shift must be identical on all
-  // ranks, hence the (d+1)-element allreduce before the pass.
+  // [0] pilot shift: column means of this rank's first rows.  Every rank keeps ITS OWN shift (no collective before the
+  // pass); the exchange re-bases the moments to a common shift (finalize.cu: rebase_sum_*).
   const T* shift_arg = nullptr;
   const double* shift_d_arg = nullptr;
   if (center && sf && !(phase == 1 && sf->rows == 0)) {
@@ -252,7 +260,6 @@ static void fit_impl(Ctx& c, const T* dX, long long n_local, int d, int k, int c
     DR4G_CUDA(cudaMemsetAsync(shift_d, 0, (size_t)d * 8, c.stream));
     launch_colstats<T>(c, dX, rows, d, nullptr, pilot, shift_d /* scratch for sumsq */);
     launch_set_scalar(c, pilot + d, (double)rows);
-    allreduce_f64(c, pilot, (size_t)d + 1);
     if constexpr (sizeof(T) == 4)
       launch_pilot_finish(c, pilot, d, reinterpret_cast<float*>(shift_t), shift_d);
     else
@@ -266,8 +273,11 @@ static void fit_impl(Ctx& c, const T* dX, long long n_local, int d, int k, int c
   // [1] the streamed pass
   if (phase == 2) {
     DR4G_CUDA(cudaMemcpyAsync(packed, sf->acc, packed_count * 8, cudaMemcpyDeviceToDevice, c.stream));
+    DR4G_CUDA(cudaMemcpyAsync(cnt + 1, sf->shift_d, (size_t)d * 8, cudaMemcpyDeviceToDevice, c.stream));
+    shift_d_arg = center ? cnt + 1 : nullptr;
   } else {
   DR4G_CUDA(cudaMemsetAsync(packed, 0, packed_count * 8, c.stream));
+  if (!center) DR4G_CUDA(cudaMemsetAsync(cnt + 1, 0, (size_t)d * 8, c.stream));
   bool used_tc = false;
   if constexpr (sizeof(T) == 4) {
     const float* Xf = reinterpret_cast<const float*>(dX);
@@ -303,10 +313,22 @@ static void fit_impl(Ctx& c, const T* dX, long long n_local, int d, int k, int c
   }
   mark(2);
 
-  // [2] combine ranks, centre
-  allreduce_f64(c, packed, packed_count);
+  // [2] combine ranks, centre.  PCA: ONE all-gather of [G | s | q | n | c_r], re-based to the common shift and summed in
+  // rank order on every rank (bit-identical everywhere).  TruncatedSVD has no shift: one all-reduce.
+  const double* moments = packed;
+  if (c.world > 1 && center) {
+    double* gathered = c.arena.take_n<double>((size_t)c.world * ext_count);
+    double* merged = c.arena.take_n<double>(ext_count);
+    allgather_f64(c, packed, gathered, ext_count);
+    launch_rebase_sum(c, gathered, c.world, d, merged);
+    moments = merged;
+    cnt = merged + dd + 2 * (size_t)d;
+    shift_d_arg = cnt + 1;
+  } else {
+    allreduce_f64(c, packed, packed_count);
+  }
   double* C = c.arena.take_n<double>(dd);
-  launch_center(c, packed, d, center, shift_d_arg, C, mean_d, total_var);
+  launch_center(c, moments, d, center, shift_d_arg, C, mean_d, total_var);
   mark(3);
 
   // [3] eigensolve + [4] outputs

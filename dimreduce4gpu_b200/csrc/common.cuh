@@ -132,6 +132,9 @@ void* tensor_map_encoder(Ctx& c);  // cuTensorMapEncodeTiled, fetched lazily thr
 void launch_pilot_finish(Ctx& c, const double* dsum_and_count, int d, float* shift_f, double* shift_d);
 void launch_set_scalar(Ctx& c, double* dst, double value);
 void launch_add_f64(Ctx& c, double* acc, const double* x, size_t count);  // acc += x (streaming fit)
+// gathered: world x (d*d + 3d + 1) doubles [G | s | q | n | c_r] of every rank; out (same layout) <- moments re-based to the
+// common shift and summed in rank order (finalize.cu)
+void launch_rebase_sum(Ctx& c, const double* gathered, int world, int d, double* out);
 void launch_center(Ctx& c, const double* packed, int d, int center, const double* shift_d,
                    double* dC /* d x d, may alias packed G */, double* dmean, double* dtotal_var);
 

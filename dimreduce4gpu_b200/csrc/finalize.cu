@@ -6,7 +6,14 @@
 //    src/pca.cu:46-49), mean = c + s_c / n (src/pca.cu:37-43), and the total variance
 //    sum_j (q_j - s_j^2/n) / max(1, n-1) that the reference gets from two more sweeps over X
 //    (src/tsvd.cu:274-290; definition follows the CPU backend, src/cpu_backend.cpp:283-296).
-// Packed layout (doubles): [G d*d | s d | q d | n 1] - the buffer that is all-reduced across ranks.
+// Packed layout (doubles): [G d*d | s d | q d | n 1 | c d] - the buffer that is exchanged across ranks.  Every rank runs
+// its pass with its OWN pilot shift c_r (no collective before the pass); the exchange is ONE all-gather of the packed
+// buffers and rebase_sum_* re-bases every rank's moments to the common shift c = sum_r n_r c_r / sum_r n_r:
+//   (x - c) = (x - c_r) + delta_r, delta_r = c_r - c
+//   G  = sum_r [ G_r + s_r delta_r^T + delta_r s_r^T + n_r delta_r delta_r^T ]
+//   s  = sum_r [ s_r + n_r delta_r ],   q = sum_r [ q_r + 2 delta_r o s_r + n_r delta_r^2 ],   n = sum_r n_r
+// exact algebra with a tiny correction (the pilots differ by ~sigma / sqrt(pilot_rows)), summed in rank order on every
+// rank, so all ranks hold bit-identical results.
 #include "common.cuh"
 
 namespace dr4g {
@@ -69,6 +76,45 @@ __global__ void moments_kernel(const double* __restrict__ packed, int d, const d
   }
 }
 
+// gathered: world x ext doubles, ext = d*d + 3d + 1.  out: same layout, holds the common shift and the re-based s, q, n.
+__global__ void rebase_sum_vec_kernel(const double* __restrict__ gathered, int world, int d, double* __restrict__ out) {
+  const size_t dd = (size_t)d * d, ext = dd + 3 * (size_t)d + 1;
+  double ntot = 0.0;
+  for (int r = 0; r < world; ++r) ntot += gathered[r * ext + dd + 2 * d];
+  for (int j = threadIdx.x + blockIdx.x * blockDim.x; j < d; j += blockDim.x * gridDim.x) {
+    double c = 0.0;
+    for (int r = 0; r < world; ++r) c += gathered[r * ext + dd + 2 * d] * gathered[r * ext + dd + 2 * d + 1 + j];
+    c = ntot > 0 ? c / ntot : 0.0;
+    double s = 0.0, q = 0.0;
+    for (int r = 0; r < world; ++r) {
+      const double* g = gathered + r * ext + dd;
+      const double nr = g[2 * d], dl = g[2 * d + 1 + j] - c, sr = g[j];
+      s += sr + nr * dl;
+      q += g[d + j] + 2.0 * dl * sr + nr * dl * dl;
+    }
+    out[dd + j] = s;
+    out[dd + d + j] = q;
+    out[dd + 2 * d + 1 + j] = c;
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) out[dd + 2 * d] = ntot;
+}
+
+__global__ void rebase_sum_gram_kernel(const double* __restrict__ gathered, int world, int d, double* __restrict__ out) {
+  const size_t dd = (size_t)d * d, ext = dd + 3 * (size_t)d + 1;
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = blockIdx.y;
+  if (j >= d) return;
+  const double ci = out[dd + 2 * d + 1 + i], cj = out[dd + 2 * d + 1 + j];   // common shift (rebase_sum_vec_kernel ran first)
+  double acc = 0.0;
+  for (int r = 0; r < world; ++r) {
+    const double* g = gathered + r * ext;
+    const double* v = g + dd;
+    const double nr = v[2 * d], di = v[2 * d + 1 + i] - ci, dj = v[2 * d + 1 + j] - cj;
+    acc += g[(size_t)i * d + j] + v[i] * dj + di * v[j] + nr * di * dj;
+  }
+  out[(size_t)i * d + j] = acc;
+}
+
 __global__ void pad_copy_kernel(const double* __restrict__ src, int d, double* __restrict__ dst, int dp) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   const int r = blockIdx.y;
@@ -107,6 +153,14 @@ void launch_center(Ctx& c, const double* packed, int d, int center, const double
   dim3 grid(ceil_div(d, 128), d);
   center_kernel<<<grid, 128, 0, c.stream>>>(packed, d, center, shift_d, dC);
   moments_kernel<<<1, 256, 0, c.stream>>>(packed, d, shift_d, dmean, dtotal_var);
+  c.launches += 2;
+  DR4G_CUDA(cudaGetLastError());
+}
+
+void launch_rebase_sum(Ctx& c, const double* gathered, int world, int d, double* out) {
+  rebase_sum_vec_kernel<<<ceil_div(d, 256), 256, 0, c.stream>>>(gathered, world, d, out);
+  dim3 grid(ceil_div(d, 128), d);
+  rebase_sum_gram_kernel<<<grid, 128, 0, c.stream>>>(gathered, world, d, out);
   c.launches += 2;
   DR4G_CUDA(cudaGetLastError());
 }

@@ -30,6 +30,7 @@ NcclApi* nccl_api() {
     LOAD(CommInitRank, "ncclCommInitRank");
     LOAD(CommDestroy, "ncclCommDestroy");
     LOAD(AllReduce, "ncclAllReduce");
+    LOAD(AllGather, "ncclAllGather");
     LOAD(GetErrorString, "ncclGetErrorString");
 #undef LOAD
     api.ok = true;

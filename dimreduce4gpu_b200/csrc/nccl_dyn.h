@@ -16,6 +16,7 @@ struct NcclApi {
   int (*CommDestroy)(void* comm) = nullptr;
   int (*AllReduce)(const void* send, void* recv, size_t count, int dtype, int op, void* comm,
                    cudaStream_t stream) = nullptr;
+  int (*AllGather)(const void* send, void* recv, size_t sendcount, int dtype, void* comm, cudaStream_t stream) = nullptr;
   const char* (*GetErrorString)(int) = nullptr;
 };
 

@@ -1,8 +1,8 @@
 """Worker for the world_size > 1 tests (launched by torch.distributed.run).
 
-mode=cpu : gloo.  Mirrors, in numpy, the exchange structure of fit_impl (csrc/api.cu): pilot-shift
-           allreduce of (d+1) numbers, one allreduce of the packed [G | s | q | n] partials, replicated
-           centring + eigensolve, and checks the result against the oracle on the concatenated rows.
+mode=cpu : gloo.  Mirrors, in numpy, the exchange structure of fit_impl (csrc/api.cu, csrc/finalize.cu): rank-local
+           pilot shifts, ONE all-gather of the packed [G | s | q | n | c_r] partials, re-basing to the common shift,
+           replicated centring + eigensolve, and checks the result against the oracle on the concatenated rows.
 mode=gpu : nccl, one process per GPU.  The real thing: DeviceContext.init_comm_from_torch + sharded
            dr4g_fit_float, compared with a single-GPU fit of the concatenated rows on rank 0 and
            with the oracle."""
@@ -40,14 +40,24 @@ def main() -> None:
         dist.init_process_group("gloo")
         Xd = X.astype(np.float64)
         rows = min(n_local, 4096)
-        pilot = torch.from_numpy(np.concatenate([Xd[:rows].sum(0), [float(rows)]]))
-        dist.all_reduce(pilot)
-        c = (pilot[:d] / pilot[d]).numpy().astype(np.float32).astype(np.float64)  # shift is held in fp32
-        Y = Xd - c
-        packed = torch.from_numpy(np.concatenate([(Y.T @ Y).ravel(), Y.sum(0), (Y * Y).sum(0), [float(n_local)]]))
-        dist.all_reduce(packed)
-        p = packed.numpy()
-        G, s, q, nt = p[: d * d].reshape(d, d), p[d * d: d * d + d], p[d * d + d: d * d + 2 * d], p[-1]
+        # every rank keeps its OWN pilot shift (held in fp32); ONE all-gather of [G | s | q | n | c_r]; every rank
+        # re-bases the moments to the common shift c = sum n_r c_r / sum n_r and sums them in rank order
+        c_r = (Xd[:rows].sum(0) / rows).astype(np.float32).astype(np.float64)
+        Y = Xd - c_r
+        mine = np.concatenate([(Y.T @ Y).ravel(), Y.sum(0), (Y * Y).sum(0), [float(n_local)], c_r])
+        parts = [torch.zeros(mine.size, dtype=torch.float64) for _ in range(world)]
+        dist.all_gather(parts, torch.from_numpy(mine))
+        parts = [p.numpy() for p in parts]
+        dd = d * d
+        nt = sum(p[dd + 2 * d] for p in parts)
+        c = sum(p[dd + 2 * d] * p[dd + 2 * d + 1:] for p in parts) / nt
+        G, s, q = np.zeros((d, d)), np.zeros(d), np.zeros(d)
+        for p in parts:
+            Gr, sr, qr, nr, cr = p[:dd].reshape(d, d), p[dd:dd + d], p[dd + d:dd + 2 * d], p[dd + 2 * d], p[dd + 2 * d + 1:]
+            dl = cr - c
+            G += Gr + np.outer(sr, dl) + np.outer(dl, sr) + nr * np.outer(dl, dl)
+            s += sr + nr * dl
+            q += qr + 2.0 * dl * sr + nr * dl * dl
         C = G - np.outer(s, s) / nt
         mean = c + s / nt
         total_var = float(((q - s * s / nt) / (nt - 1)).sum())
