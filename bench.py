@@ -298,21 +298,19 @@ def parity_check(torch, dist, ctx, wl, X, out, world) -> dict:
     if wl["dtype"] == "f32" and path != "generic_dmma":
         ctx.set_option("gram_path", 1)
         t0 = time.perf_counter()
-        ref_out = ctx.fit(X, k, center=center, algorithm="cusolver", n_iter=5, random_state=42, tol=1e-5)
+        ref_out = ctx.fit(X, k, center=center, algorithm=wl["algorithm"], n_iter=5, random_state=42, tol=1e-5)
         torch.cuda.synchronize()
-        res["reference_fit"] = f"same shard, gram_path=1 (fp64 DMMA products), exact eigensolve, {time.perf_counter() - t0:.2f} s"
+        res["reference_fit"] = (f"same shard, same algorithm and seed, gram_path=1 (fp64 DMMA products instead of the tcgen05 "
+                                f"split), {time.perf_counter() - t0:.2f} s")
         ctx.set_option("gram_path", 0)
         s, sr = out["singular_values"].double(), ref_out["singular_values"].double()
         res["sigma_rel"] = float(((s - sr).abs() / sr).max())
-        if wl["algorithm"] == "cusolver":
-            res["max_angle"] = principal_angle(torch, out["components"], ref_out["components"])
-            ev, evr = out["explained_variance_ratio"].double(), ref_out["explained_variance_ratio"].double()
-            res["evr_rel"] = float(((ev - evr).abs() / evr).max())
-        else:
-            # 'power' with the default n_iter on a flat spectrum: the reference's own criterion is the subspace angle
-            # (tests/test_sklearn_parity_comprehensive.py:185), reported here, not gated
-            res["max_angle"] = principal_angle(torch, out["components"], ref_out["components"])
-            res["note"] = "timed algorithm is 'power' (n_iter=5); the check compares it with the exact eigensolve"
+        res["max_angle"] = principal_angle(torch, out["components"], ref_out["components"])
+        ev, evr = out["explained_variance_ratio"].double(), ref_out["explained_variance_ratio"].double()
+        res["evr_rel"] = float(((ev - evr).abs() / evr).max())
+        if wl["algorithm"] != "cusolver" and wl["d"] > 256:
+            res["note"] = ("'power' (subspace iteration, n_iter=5) on both sides with the same seed: the check isolates the Gram "
+                           "kernel; on a flat spectrum the iteration amplifies Gram differences in the trailing Ritz vectors")
         if center:
             res["mean_abs"] = float((out["mean"].double() - ref_out["mean"].double()).abs().max())
     else:

@@ -77,6 +77,7 @@ struct Ctx {
   int gram_split = 0;         // pair kernel operand split: 0 auto (bf16x3), 1 3xTF32 (kind::tf32), 2 bf16x3 (kind::f16)
   int flush_rows = 1024;      // rows between TMEM flushes in the tcgen05 Gram
   int pilot_rows = 4096;      // rows sampled for the pilot shift
+  int power_min_dim = 256;    // min(n, d) <= this: exact path whatever `algorithm` says (src/cpu_backend.cpp:347)
   double jacobi_tol = 0.0;    // 0 -> per-dtype default
   int jacobi_sweeps = 30;
   int eig_solver = 0;         // exact path: 0 tridiagonal route (top-k), 1 blocked Jacobi (all pairs), 2 tridiagonal route without the cluster-resident T1
@@ -173,6 +174,11 @@ void launch_project_tc(Ctx& c, const float* dX, long long n, int d, int k, const
                        const float* dw, float* dZ, float* dU);
 template <typename T>
 void launch_inverse(Ctx& c, const T* dZ, long long n, int d, int k, const T* dQ, const T* dmean, T* dX);
+
+// CSR rows [row0, row0 + rows) -> dense row-major tile (csr.cu); indptr int64, indices int32, all device pointers
+template <typename T>
+void launch_csr_to_dense(Ctx& c, const long long* indptr, const int* indices, const T* data, long long row0, long long rows,
+                         int d, T* out);
 
 // cudaFuncSetAttribute acts on the current device only: a call site remembers, per device, the largest dynamic
 // shared-memory size it has requested (a per-process flag broke the second device of a process).

@@ -179,7 +179,24 @@ tridiag_kernel(double* __restrict__ A, int d, double* __restrict__ diag, double*
       double* Ai = kRowsInSmem ? R + (size_t)((i / nw) * kTriWarps + warp) * d : A + (size_t)i * d;
       double* pub = (i == s + 1) ? rbuf + (size_t)((s + 1) & 1) * d : nullptr;
       double dot = 0.0;
-      for (int c = s + 1 + lane; c < d; c += 32) {
+      int c = s + 1 + lane;
+      if (!kRowsInSmem) {
+        // rows in L2 / HBM (d > ~1000): four independent loads in flight per lane - the one-load-per-iteration loop
+        // paid the full memory latency 128 times per row at d = 4096 (100 us per column, measured)
+        for (; c + 96 < d; c += 128) {
+          double a[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) a[u] = __ldcg(&Ai[c + 32 * u]);
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            a[u] = a[u] - vi * w[c + 32 * u] - wi * v[c + 32 * u];
+            __stcg(&Ai[c + 32 * u], a[u]);
+            if (pub) __stcg(&pub[c + 32 * u], a[u]);
+            dot = fma(a[u], vn[c + 32 * u], dot);
+          }
+        }
+      }
+      for (; c < d; c += 32) {
         const double a = (kRowsInSmem ? Ai[c] : __ldcg(&Ai[c])) - vi * w[c] - wi * v[c];
         if (kRowsInSmem) Ai[c] = a; else __stcg(&Ai[c], a);
         if (pub) __stcg(&pub[c], a);

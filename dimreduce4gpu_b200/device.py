@@ -258,6 +258,22 @@ class DeviceContext:
         _check(rc, f"dr4g_inverse_transform_{sfx}")
         return X
 
+    def csr_to_dense(self, indptr, indices, data, row0: int, rows: int, d: int, out=None):
+        """Rows [row0, row0 + rows) of a device-resident CSR matrix (int64 indptr, int32 indices, fp32/fp64 data CUDA
+        tensors) expanded into a dense (rows, d) CUDA tensor (dr4g_csr_to_dense_*)."""
+        import torch
+
+        for t, nm in ((indptr, "indptr"), (indices, "indices"), (data, "data")):
+            _need_cuda_contig(t, nm, self.device)
+        if indptr.dtype != torch.int64 or indices.dtype != torch.int32:
+            raise TypeError("indptr must be int64 and indices int32")
+        D = out if out is not None else torch.empty(rows, d, dtype=data.dtype, device=data.device)
+        self._on_torch_stream()
+        rc = getattr(self._lib, f"dr4g_csr_to_dense_{_suffix(data)}")(
+            self._h, indptr.data_ptr(), indices.data_ptr(), data.data_ptr(), int(row0), int(rows), int(d), D.data_ptr())
+        _check(rc, "dr4g_csr_to_dense")
+        return D
+
     # ------------------------------------------------------------------ building blocks
     def colstats(self, X, shift=None):
         import torch

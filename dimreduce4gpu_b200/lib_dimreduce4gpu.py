@@ -47,6 +47,8 @@ def _bind(lib: ctypes.CDLL) -> None:
         f.argtypes, f.restype = [vp, vp, ll, ci, ci, vp, vp, vp, vp, vp], ci
         f = getattr(lib, f"dr4g_inverse_transform_{name}")
         f.argtypes, f.restype = [vp, vp, ll, ci, ci, vp, vp, vp], ci
+        f = getattr(lib, f"dr4g_csr_to_dense_{name}")
+        f.argtypes, f.restype = [vp, vp, vp, vp, ll, ll, ci, vp], ci
         f = getattr(lib, f"dr4g_colstats_{name}")
         f.argtypes, f.restype = [vp, vp, ll, ci, vp, vp, vp], ci
         f = getattr(lib, f"dr4g_gram_{name}")
@@ -81,6 +83,7 @@ EXPORTED_SYMBOLS = (
     "dr4g_colstats_double", "dr4g_gram_float", "dr4g_gram_double", "dr4g_eigh_double", "dr4g_eigh_topk_double", "dr4g_stage_times",
     "dr4g_last_gram_path", "dr4g_last_proj_path", "dr4g_launch_count",
     "dr4g_fit_transform_host_float", "dr4g_fit_transform_host_double",
+    "dr4g_csr_to_dense_float", "dr4g_csr_to_dense_double",
     "dr4g_partial_fit_float", "dr4g_partial_fit_double", "dr4g_partial_fit_finalize_float",
     "dr4g_partial_fit_finalize_double", "dr4g_partial_fit_reset", "dr4g_partial_fit_rows",
 )

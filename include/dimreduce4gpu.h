@@ -84,6 +84,8 @@ DR4G_EXPORT int dr4g_ctx_set_stream(dr4g_ctx* ctx, void* cuda_stream);
 /* Block until everything enqueued on the context's stream is done; returns deferred errors. */
 DR4G_EXPORT int dr4g_sync(dr4g_ctx* ctx);
 /* Tunables / test hooks.  Keys: "gram_path" (0 auto, 1 generic DMMA kernel, 2 tcgen05 kernels, 3 tcgen05 single-CTA kernel only),
+ * "power_min_dim" (min(n, d) <= this takes the exact path whatever params.algorithm says, default 256 as
+ * src/cpu_backend.cpp:347; 0 = off),
  * "proj_path" (projection: 0 auto = tcgen05 where eligible, 1 CUDA-core kernels),
  * "gram_split" (CTA-pair kernel operands: 0 auto = 2 bf16x3 on kind::f16, 1 = 3xTF32 on kind::tf32),
  * "flush_rows" (rows between TMEM accumulator flushes), "pilot_rows", "jacobi_tol", "jacobi_sweeps",
@@ -153,6 +155,15 @@ DR4G_EXPORT int dr4g_inverse_transform_float(dr4g_ctx* ctx, const float* dZ, lon
                                  const float* dQ, const float* dmean, float* dX);
 DR4G_EXPORT int dr4g_inverse_transform_double(dr4g_ctx* ctx, const double* dZ, long long n, int d, int k,
                                   const double* dQ, const double* dmean, double* dX);
+
+/* CSR input: expand rows [row0, row0 + rows) of a device-resident CSR matrix (dindptr: n+1 int64,
+ * dindices: nnz int32, ddata: nnz values) into the dense row-major tile dout (rows x d) that dr4g_partial_fit_* and
+ * dr4g_transform_* read.  Replaces the reference's host-side densify (dimreduce4gpu/truncated_svd.py:67-70,
+ * pca.py:44-47): only the CSR arrays cross PCIe.  Asynchronous on ctx's stream. */
+DR4G_EXPORT int dr4g_csr_to_dense_float(dr4g_ctx* ctx, const long long* dindptr, const int* dindices, const float* ddata,
+                            long long row0, long long rows, int d, float* dout);
+DR4G_EXPORT int dr4g_csr_to_dense_double(dr4g_ctx* ctx, const long long* dindptr, const int* dindices, const double* ddata,
+                             long long row0, long long rows, int d, double* dout);
 
 /* Building blocks, exported for parity tests and micro-benchmarks (device pointers).
  *   colstats: per-column sum and sum of squares of (x - shift) in double; shift may be NULL.

@@ -177,20 +177,13 @@ def test_config3_power_on_spiked_input():
 
 
 def test_config1_default_algorithm_live():
-    """BASELINE configs[0]: TruncatedSVD n_components=10 (default algorithm 'power') on 10,000 x 100 fp32.  The oracle
-    takes its exact path here (min(n,d) <= 256, src/cpu_backend.cpp:347), so 'power' is iterated to convergence for the
-    1e-4 gate and run with the defaults for the reference's criteria."""
+    """BASELINE configs[0]: TruncatedSVD n_components=10 with the DEFAULT algorithm ('power') on 10,000 x 100 fp32, exactly
+    as a user of the reference calls it.  The oracle takes its exact path here (min(n,d) <= 256, src/cpu_backend.cpp:347)
+    and so does the library (csrc/api.cu: same rule), so the default call is held to the full 1e-4 gate."""
     X = np.random.default_rng(1234).standard_normal((10_000, 100)).astype(np.float32) * np.linspace(1, 3, 100, dtype=np.float32)
     ref, tc = _oracle("tsvd", X, 10, "power")
-    est, Z, tg = _fit("tsvd", X, 10, "cusolver")
-    _compare("C1_10000x100_k10_exact", est, Z, ref, TOL32, tg, tc)
-    est5, Z5, _ = _fit("tsvd", X, 10, "power")
-    (Cr,), (C5,) = O.svd_flip_v(ref.components), O.svd_flip_v(est5.components_)
-    ang5 = O.max_principal_angle(Cr, C5)
-    rec5 = np.linalg.norm(X - Z5 @ est5.components_)
-    rec_x = np.linalg.norm(X - ref.X_transformed @ ref.components)
-    _report("C1_power_default", angle_deg=float(np.rad2deg(ang5)), rec_ratio=float(rec5 / rec_x))
-    assert ang5 < np.deg2rad(35) and rec5 <= 1.10 * rec_x, f"angle {np.rad2deg(ang5):.2f} deg, recon ratio {rec5 / rec_x:.4f}"
+    est, Z, tg = _fit("tsvd", X, 10, "power")
+    _compare("C1_10000x100_k10_default_algorithm", est, Z, ref, TOL32, tg, tc)
 
 
 def test_config5_family_fp64_vs_restatement():

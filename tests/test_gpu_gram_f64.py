@@ -44,8 +44,9 @@ def test_gram_f64_matches_fp64_product(n, d, shifted):
     assert ctx.last_gram_path == "dmma_f64_128"
     Xd = X - (shift if shifted else 0.0)
     Gr = Xd.T @ Xd
-    dg = torch.sqrt(torch.diag(Gr)).clamp_min(1e-300)
-    err = float(((G - Gr).abs() / (dg[:, None] * dg[None, :])).max())
+    dg = torch.sqrt(torch.diag(Gr))
+    den = (dg[:, None] * dg[None, :]).clamp_min(1e-30 + 1e-13 * float((X * X).sum()))   # n = 1 shifted: Gr is exactly 0
+    err = float(((G - Gr).abs() / den).max())
     assert err < 5e-14, err
     assert float((G - G.T).abs().max()) == 0.0
 

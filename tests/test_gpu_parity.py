@@ -123,7 +123,9 @@ def test_power_algorithm_on_gapped_spectrum(name):
 
 
 def test_power_default_iterations_meet_reference_criteria():
-    """Default n_iter=5: recon error <= 1.10x the exact one (reference comprehensive tests :196-210)."""
+    """Default n_iter=5: recon error <= 1.10x the exact one (reference comprehensive tests :196-210).  (d <= 256 takes the
+    exact path like the CPU backend, src/cpu_backend.cpp:347; the iteration itself at small d is covered through
+    DeviceContext with power_min_dim=0 in test_subspace_iteration_small_d_device_path.)"""
     X = inputs.comprehensive_matrix(256, 64, 16, False, np.float32, 0)
     est, Z = _fit("tsvd", X, 16, "power")
     ex = O.RefLib().tsvd(X, 16, "cusolver") if O.REF_SO.is_file() else O.restated_tsvd(X, 16)
@@ -181,6 +183,28 @@ def test_centering_with_huge_offset_fp32():
     est, Z = _fit("pca", X, 8, "cusolver")
     assert _rel(est.singular_values_, ref.singular_values) < 5e-4  # input rounding at 1e4 dominates
     np.testing.assert_allclose(est.mean_, ref.mean, rtol=1e-6)
+
+
+def test_subspace_iteration_small_d_device_path():
+    """K5 at d <= 256 (the legacy symbols route such shapes to the exact solver): power_min_dim=0 forces the iteration."""
+    import torch
+
+    import dimreduce4gpu_b200 as pkg
+
+    X = inputs.config1_matrix()
+    g = _gold("tsvd_config1_10000x100_k10")
+    ctx = pkg.DeviceContext(0)
+    ctx.set_option("power_min_dim", 0)
+    r = ctx.fit(torch.from_numpy(X).cuda(), 10, center=False, algorithm="power", n_iter=400, tol=1e-9, random_state=42)
+    ctx.sync()
+    assert _rel(r["singular_values"].cpu().numpy(), g["singular_values"]) < 2e-2
+    (Cr,), (Co,) = O.svd_flip_v(g["components"]), O.svd_flip_v(r["components"].cpu().numpy())
+    assert O.max_principal_angle(Cr, Co) < np.deg2rad(35)
+    r5 = ctx.fit(torch.from_numpy(X).cuda(), 10, center=False, algorithm="power", n_iter=5, random_state=42)
+    rx = ctx.fit(torch.from_numpy(X).cuda(), 10, center=False, algorithm="cusolver")
+    ctx.sync()
+    assert float(r5["singular_values"][0]) < float(rx["singular_values"][0]) * (1 + 1e-6)   # Ritz values from below
+    assert float((r5["singular_values"] - rx["singular_values"]).abs().max()) > 0            # really the iteration
 
 
 def test_transform_and_inverse_transform():

@@ -44,7 +44,7 @@ def test_project_tc_matches_fp64(n, d, k, centered):
     ctx.sync()
     assert ctx.last_proj_path == "tcgen05"
     Zr = (X.double() - (mean.double() if centered else 0.0)) @ Q.double().T
-    scale = float(Zr.abs().max())
+    scale = max(float(Zr.abs().max()), 1e-3 * float(X.abs().max()))   # n = 1 centred: Z is exactly 0
     ez = float((Z.double() - Zr).abs().max()) / scale
     eu = float((U.double() - Zr / sigma.double()).abs().max()) / scale
     print(f"n={n} d={d} k={k} centred={centered}: max |Z - Z_fp64| / max|Z| = {ez:.2e}, U {eu:.2e}")
