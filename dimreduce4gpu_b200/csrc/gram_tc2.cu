@@ -60,7 +60,7 @@ constexpr int kMaxStages = 6;
 constexpr int kConvWarps = 8;
 constexpr int kConvThreads = kConvWarps * 32;
 constexpr int kEpiWarps = 4;
-constexpr int kProducers = 3;            // TMA-issuing warps: one box costs its issuer ~700 cycles whatever its size
+constexpr int kProducers = 3;            // TMA-issuing warps: one box costs its issuer ~700 cycles whatever its size (a 4th warp = 544 threads caps the kernel at 96 registers: spills)
 constexpr int kMmaWarp = kConvWarps + kProducers;
 constexpr int kThreads = kConvThreads + (kProducers + 1 + kEpiWarps) * 32;
 constexpr int kMaxPJobs = 40;
@@ -136,7 +136,7 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
 
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
-  __shared__ __align__(8) uint64_t bar_full[kMaxStages], bar_conv[kMaxStages], bar_empty[kMaxStages];
+  __shared__ __align__(8) uint64_t bar_full[kMaxStages], bar_conv[kMaxStages], bar_empty[kMaxStages], bar_lfree[kMaxStages];
   __shared__ __align__(8) uint64_t bar_acc_full[2], bar_acc_empty[2];
   __shared__ uint32_t tmem_base_slot;
 
@@ -147,6 +147,7 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
       ptx::mbar_init(ptx::smem_u32(&bar_full[s]), kProducers);
       ptx::mbar_init(ptx::smem_u32(&bar_conv[s]), kConvWarps);       // a group of 4 warps per CTA; leader CTA only
       ptx::mbar_init(ptx::smem_u32(&bar_empty[s]), 1);
+      ptx::mbar_init(ptx::smem_u32(&bar_lfree[s]), kConvWarps / 2);   // bf16x3: the group of 4 warps that read the landing half
     }
     for (int a = 0; a < 2; ++a) {
       ptx::mbar_init(ptx::smem_u32(&bar_acc_full[a]), 1);
@@ -179,7 +180,13 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
 #pragma unroll
       for (int lb = 0; lb < 3; ++lb) blk_of[lb] = lb < nlb ? job.bb[lb] + (int)rank : T;
       for (int it = 0; it < my_chunks; ++it) {
-        ptx::mbar_wait(ptx::smem_u32(&bar_empty[s]), ph ^ 1u);
+        // 3xTF32: the stage (landing half converted in place + lo half) is free when its MMAs have completed.
+        // bf16x3: the operands live in the other half, so the landing half is free as soon as the converters have read
+        // it (bar_lfree) and the operand half when its MMAs have completed (bar_empty, waited for by the converters):
+        // the pass is bound by bytes in flight (a stage's way round a coupled ring is ~4000 cycles, 192 KB / 8 B per
+        // element / 4000 = 6 elements per cycle and CTA, which is what the first bf16x3 version ran at); decoupled,
+        // every byte of shared memory is held for about half as long.
+        ptx::mbar_wait(ptx::smem_u32(BF16 ? &bar_lfree[s] : &bar_empty[s]), ph ^ 1u);
         if (p == 0) DR4G_TRACE2(0);
         const long long row0 = ((long long)split + (long long)it * job.ncl) * kt;
         const uint32_t full = ptx::smem_u32(&bar_full[s]);
@@ -408,9 +415,9 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
                   l01 = ptx::pack_bf16x2(y0 - __uint_as_float(h01 << 16), y1 - __uint_as_float(h01 & 0xffff0000u));
                   l23 = ptx::pack_bf16x2(y2 - __uint_as_float(h23 << 16), y3 - __uint_as_float(h23 & 0xffff0000u));
                 }
-                const uint32_t o = sx + half_bytes + (uint32_t)(c * NLB + lb) * kSlotBytes + boff[h];
-                asm volatile("st.shared.v2.b32 [%0], {%1,%2};" ::"r"(o), "r"(h01), "r"(h23) : "memory");
-                asm volatile("st.shared.v2.b32 [%0], {%1,%2};" ::"r"(o + 4096u), "r"(l01), "r"(l23) : "memory");
+                // packed results replace the fp32 values in their registers; stored once the operand half is free
+                x[i].x = __uint_as_float(h01); x[i].y = __uint_as_float(h23);
+                x[i].z = __uint_as_float(l01); x[i].w = __uint_as_float(l23);
               } else {
               float4 hi = make_float4(0.f, 0.f, 0.f, 0.f), lo = hi;
               if (ok[i]) {
@@ -427,6 +434,23 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
               asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(a + half_bytes), "f"(lo.x), "f"(lo.y), "f"(lo.z), "f"(lo.w) : "memory");
               }
             }
+        if constexpr (BF16) {
+          // landing half read: hand it back to the TMA producers, then wait for the MMAs that still read the operand half
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&bar_lfree[s]));
+          ptx::mbar_wait(ptx::smem_u32(&bar_empty[s]), ph ^ 1u);
+#pragma unroll
+          for (int c = 0; c < CPS; ++c)
+#pragma unroll
+            for (int lb = 0; lb < NLB; ++lb)
+#pragma unroll
+              for (int h = 0; h < 4; ++h) {
+                const int i = (c * NLB + lb) * 4 + h;
+                const uint32_t o = sx + half_bytes + (uint32_t)(c * NLB + lb) * kSlotBytes + boff[h];
+                asm volatile("st.shared.v2.b32 [%0], {%1,%2};" ::"r"(o), "r"(__float_as_uint(x[i].x)), "r"(__float_as_uint(x[i].y)) : "memory");
+                asm volatile("st.shared.v2.b32 [%0], {%1,%2};" ::"r"(o + 4096u), "r"(__float_as_uint(x[i].z)), "r"(__float_as_uint(x[i].w)) : "memory");
+              }
+        }
       };
       if (trace & 4) {
       } else if (nlb == 1) convert(std::integral_constant<int, 1>{});
