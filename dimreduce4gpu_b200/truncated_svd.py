@@ -40,10 +40,42 @@ def _ptr(x: np.ndarray):
     return x.ctypes.data_as(ctypes.POINTER(ct))
 
 
+def _is_sparse(X) -> bool:
+    return type(X).__module__.startswith("scipy.sparse")
+
+
 def _densify(X):
-    if type(X).__module__.startswith("scipy.sparse"):
-        return X.toarray()  # reference densifies CSR on the host (truncated_svd.py:67-70)
+    if _is_sparse(X):
+        return X.toarray()  # reference densifies CSR on the host (truncated_svd.py:67-70); only tiny inputs come here
     return X
+
+
+class _DeviceCSR:
+    """A scipy sparse matrix as device-resident CSR arrays (int64 indptr, int32 indices, values in `dtype`): the only
+    form in which sparse input crosses PCIe.  Row chunks are expanded on the device (csrc/csr.cu) into the dense tiles
+    the streamed kernels read; the reference densifies the whole matrix on the host first (truncated_svd.py:67-70)."""
+
+    CHUNK_BYTES = 256 << 20
+
+    def __init__(self, X, dtype, device: int) -> None:
+        import torch
+
+        X = X.tocsr()
+        X.sum_duplicates()
+        self.n, self.d = X.shape
+        self.tdt = torch.float32 if dtype == np.float32 else torch.float64
+        dev = f"cuda:{device}"
+        self.indptr = torch.from_numpy(np.ascontiguousarray(X.indptr, dtype=np.int64)).to(dev)
+        self.indices = torch.from_numpy(np.ascontiguousarray(X.indices, dtype=np.int32)).to(dev)
+        self.data = torch.from_numpy(np.ascontiguousarray(X.data, dtype=dtype)).to(dev)
+        self.rows = max(1, min(self.n, self.CHUNK_BYTES // max(1, self.d * self.data.element_size())))
+        self.buf = torch.empty(self.rows, self.d, dtype=self.tdt, device=dev)
+
+    def chunks(self, ctx):
+        """(row0, dense tile) per chunk; the tile aliases one buffer, ordered by the stream."""
+        for r0 in range(0, self.n, self.rows):
+            rows = min(self.rows, self.n - r0)
+            yield r0, ctx.csr_to_dense(self.indptr, self.indices, self.data, r0, rows, self.d, out=self.buf[:rows])
 
 
 class TruncatedSVD:
@@ -120,6 +152,8 @@ class TruncatedSVD:
         self._drop_stream_state()
         if _is_torch_cuda(X):
             return self._fit_device(X, want_scores=True)
+        if _is_sparse(X):
+            return self._fit_csr(X)
         X = np.ascontiguousarray(_densify(X), dtype=self.dtype)
         if X.ndim != 2:
             raise ValueError("X must be 2-D (n_samples, n_features)")
@@ -168,6 +202,40 @@ class TruncatedSVD:
         self.mean_ = res["mean"].cpu().numpy() if self._center else None
         self._U = None
         return Z
+
+    def _fit_csr(self, X):
+        """scipy sparse input: CSR arrays to the device, row chunks expanded there and streamed through
+        the fit's accumulators (dr4g_partial_fit_*), then a second sweep for the scores.  Nothing dense exists on the
+        host, and on the device only one chunk at a time."""
+        import torch
+
+        from .device import DeviceContext
+
+        n, d = X.shape
+        k = min(self.n_components, n, d)
+        with torch.cuda.device(self.gpu_id):
+            ctx = DeviceContext(self.gpu_id)
+            csr = _DeviceCSR(X, self.dtype, self.gpu_id)
+            for _r0, tile in csr.chunks(ctx):
+                ctx.partial_fit(tile, center=self._center)
+            res = ctx.partial_fit_finalize(d, k, self._center, csr.tdt, algorithm=self.algorithm, n_iter=self.n_iter,
+                                           random_state=self.random_state, tol=self.tol, verbose=self.verbose,
+                                           whiten=bool(getattr(self, "whiten", False)))
+            Xt = np.empty((n, k), dtype=self.dtype)
+            U = np.empty((n, k), dtype=self.dtype)
+            for r0, tile in csr.chunks(ctx):
+                Z, Uc = ctx.transform(tile, res["components"], mean=res["mean"], singular_values=res["singular_values"],
+                                      want_u=True)
+                Xt[r0:r0 + tile.shape[0]] = Z.cpu().numpy()
+                U[r0:r0 + tile.shape[0]] = Uc.cpu().numpy()
+            ctx.sync()
+        self._Q = res["components"].cpu().numpy()
+        self._w = res["singular_values"].cpu().numpy()
+        self.explained_variance_ = res["explained_variance"].cpu().numpy()
+        self.explained_variance_ratio_ = res["explained_variance_ratio"].cpu().numpy()
+        self.mean_ = res["mean"].cpu().numpy() if self._center else None
+        self._U = U
+        return Xt
 
     # ------------------------------------------------------------------ streaming fit (SURVEY 8f-1)
     def partial_fit(self, X, y=None):
@@ -244,6 +312,16 @@ class TruncatedSVD:
         select_backend(self.backend)
         Q = self.components_
         tdt = torch.float32 if Q.dtype == np.float32 else torch.float64
+        if _is_sparse(X):
+            ctx = _device_context(self.gpu_id)
+            with torch.cuda.device(self.gpu_id):
+                csr = _DeviceCSR(X, Q.dtype, self.gpu_id)
+                Qd = torch.from_numpy(np.ascontiguousarray(Q)).to(csr.data.device)
+                md = torch.from_numpy(np.ascontiguousarray(self.mean_)).to(csr.data.device) if center and self.mean_ is not None else None
+                out = np.empty((csr.n, Q.shape[0]), dtype=Q.dtype)
+                for r0, tile in csr.chunks(ctx):
+                    out[r0:r0 + tile.shape[0]] = ctx.transform(tile, Qd, mean=md).cpu().numpy()
+            return out
         Xd, on_dev = self._to_device(X, tdt)
         ctx = _device_context(Xd.device.index)
         Qd = torch.from_numpy(np.ascontiguousarray(Q)).to(Xd.device)

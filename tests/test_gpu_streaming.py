@@ -161,3 +161,52 @@ def test_second_device_in_the_same_process():
     est = pkg.PCA(n_components=8, backend="gpu", gpu_id=1)
     Zh = est.fit_transform(_data(3000, 256, 4))
     assert Zh.shape == (3000, 8) and np.isfinite(Zh).all()
+
+
+# ---------------------------------------------------------------------------------------------- CSR input
+@pytest.mark.parametrize("kind,n,d,k,density", [("tsvd", 20000, 300, 12, 0.02), ("pca", 5000, 96, 8, 0.1), ("tsvd", 700, 33, 5, 0.3)])
+def test_csr_input_is_expanded_on_the_device_and_matches_the_dense_reference(kind, n, d, k, density, monkeypatch):
+    """scipy CSR in: only the CSR arrays are uploaded, row chunks are expanded by dr4g_csr_to_dense_* and streamed through
+    partial_fit; the result equals the reference CPU backend on the densified matrix (which is what the reference does on
+    the host, truncated_svd.py:67-70).  Small chunks force several of them."""
+    import scipy.sparse as sp
+
+    import dimreduce4gpu_b200 as pkg
+    from dimreduce4gpu_b200 import truncated_svd as T
+    from oracle import cpu_oracle as O
+
+    rng = np.random.default_rng(n + d)
+    Xs = sp.random(n, d, density=density, format="csr", dtype=np.float32, random_state=rng,
+                   data_rvs=lambda m: rng.standard_normal(m).astype(np.float32) * 2.0 + 1.0)
+    monkeypatch.setattr(T._DeviceCSR, "CHUNK_BYTES", 1 << 20)
+    cls = pkg.PCA if kind == "pca" else pkg.TruncatedSVD
+    est = cls(n_components=k, algorithm="cusolver", backend="gpu")
+    Z = est.fit_transform(Xs)
+    Xd = np.asarray(Xs.todense(), dtype=np.float32)
+    ref = (O.RefLib().pca if kind == "pca" else O.RefLib().tsvd)(Xd, k, "cusolver") if O.REF_SO.is_file() else \
+        (O.restated_pca if kind == "pca" else O.restated_tsvd)(Xd, k)
+    rel = float(np.max(np.abs(est.singular_values_ - ref.singular_values) / ref.singular_values))
+    assert rel < 1e-4, rel
+    Cr, Zr = O.svd_flip_v(ref.components, ref.X_transformed)
+    Co, Zo = O.svd_flip_v(est.components_, Z)
+    assert O.max_principal_angle(Cr, Co) < 1e-2
+    assert np.max(np.abs(np.linalg.norm(Zr, axis=0) - np.linalg.norm(Zo, axis=0)) / ref.singular_values) < 2e-4
+    # sparse transform (reference semantics: no centring) equals the dense one
+    np.testing.assert_allclose(est.transform(Xs), est.transform(Xd), atol=2e-4 * float(ref.singular_values[0]))
+
+
+def test_csr_to_dense_kernel_matches_scipy():
+    import scipy.sparse as sp
+    import torch
+
+    import dimreduce4gpu_b200 as pkg
+
+    rng = np.random.default_rng(0)
+    Xs = sp.random(1000, 77, density=0.05, format="csr", dtype=np.float64, random_state=rng)
+    ctx = pkg.DeviceContext(0)
+    ip = torch.from_numpy(Xs.indptr.astype(np.int64)).cuda()
+    ix = torch.from_numpy(Xs.indices.astype(np.int32)).cuda()
+    dv = torch.from_numpy(Xs.data).cuda()
+    D = ctx.csr_to_dense(ip, ix, dv, 100, 650, 77)
+    ctx.sync()
+    np.testing.assert_array_equal(D.cpu().numpy(), np.asarray(Xs[100:750].todense()))
