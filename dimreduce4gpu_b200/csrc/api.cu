@@ -284,6 +284,7 @@ static void fit_impl(Ctx& c, const T* dX, long long n_local, int d, int k, int c
   DR4G_CUDA(cudaMemsetAsync(packed, 0, packed_count * 8, c.stream));
   if (!center) DR4G_CUDA(cudaMemsetAsync(cnt + 1, 0, (size_t)d * 8, c.stream));
   bool used_tc = false;
+  c.last_gram_kernel = 0;
   if constexpr (sizeof(T) == 4) {
     const float* Xf = reinterpret_cast<const float*>(dX);
     if (want_tc) {

@@ -104,7 +104,7 @@ template <bool BF16>
 __global__ void __launch_bounds__(kThreads, 1)
 gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ PJobTable table, long long n, int d,
                  const float* __restrict__ shift, float* __restrict__ slab, double* __restrict__ osum,
-                 double* __restrict__ osq, int flush_rows, int trace) {
+                 double* __restrict__ osq, int flush_rows, int trace, int* __restrict__ prog, int pace_rows) {
   // ---------------------------------------------------------------- which job / which chunks
   const uint32_t rank = ptx::cluster_ctarank();
   const int cluster = (int)blockIdx.x >> 1;
@@ -144,7 +144,7 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kMaxStages; ++s) {
-      ptx::mbar_init(ptx::smem_u32(&bar_full[s]), kProducers);
+      ptx::mbar_init(ptx::smem_u32(&bar_full[s]), 1);                 // the stage's owner (one producer) + its TMA bytes
       ptx::mbar_init(ptx::smem_u32(&bar_conv[s]), kConvWarps);       // a group of 4 warps per CTA; leader CTA only
       ptx::mbar_init(ptx::smem_u32(&bar_empty[s]), 1);
       ptx::mbar_init(ptx::smem_u32(&bar_lfree[s]), kConvWarps / 2);   // bf16x3: the group of 4 warps that read the landing half
@@ -167,54 +167,69 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
 
   if (warp >= kConvWarps && warp < kMmaWarp) {
     // ================================================================ TMA producers (each CTA its own blocks)
-    // Measured (tools/tma_probe.cu): a thread issues one box per ~700 cycles whatever the box size, so
-    // one issuer with 8 KB boxes streams 3.1 TB/s chip-wide and four issuers 6.5 TB/s.  The boxes of
-    // the stages are dealt round-robin to the kProducers warps; every producer arrives on every
-    // stage's barrier with the bytes it issued (possibly none).
+    // Measured (tools/tma_probe.cu): a thread issues one box per ~700 cycles whatever the box size, so one issuer with
+    // 8 KB boxes streams 3.1 TB/s chip-wide and four issuers 6.5 TB/s.  Stage `it` belongs to producer it % kProducers,
+    // which does everything for it (wait, expect_tx, all boxes): a first version dealt the BOXES round-robin and had
+    // every producer arrive on every stage's barrier - its pipeline trace showed ~750 cycles per stage and producer
+    // whether or not the producer owned a box, so three producers advanced no faster than one (1030 cycles per 16-row
+    // stage at d = 512, the kernel's pace).
+    //
+    // Cross-job pacing.  At d > 256 every column block is read by several jobs (d = 512: two, d = 1024: four).  The jobs
+    // are balanced to finish together but drift apart by a few per cent of n, far more than the L2 holds, so each job
+    // pulled its own copy from HBM: ncu showed dram reads of 2.1x (d = 512) and 3.4x (d = 1024) the matrix, 3.5 TB/s.
+    // Every cluster's leader publishes the rows it has issued (prog[job], a relaxed global add per stage) and, every 8
+    // stages, a producer that is more than `pace_rows` ahead of the slowest unfinished job waits (bounded: after ~60 us
+    // without progress the CTA stops pacing, so a partly resident grid cannot hang) - the followers then hit in L2.
     if (ptx::elect_one()) {
       const int p = warp - kConvWarps;
       ptx::prefetch_tmap(&tmap);
-      int s = 0, pown = 0;   // pown: owner of the next stage's first box
+      int s = 0, owner = 0;
       uint32_t ph = 0;
+      bool pacing = prog != nullptr && table.njobs > 1;
       int blk_of[3];
 #pragma unroll
       for (int lb = 0; lb < 3; ++lb) blk_of[lb] = lb < nlb ? job.bb[lb] + (int)rank : T;
       for (int it = 0; it < my_chunks; ++it) {
-        // 3xTF32: the stage (landing half converted in place + lo half) is free when its MMAs have completed.
-        // bf16x3: the operands live in the other half, so the landing half is free as soon as the converters have read
-        // it (bar_lfree) and the operand half when its MMAs have completed (bar_empty, waited for by the converters):
-        // the pass is bound by bytes in flight (a stage's way round a coupled ring is ~4000 cycles, 192 KB / 8 B per
-        // element / 4000 = 6 elements per cycle and CTA, which is what the first bf16x3 version ran at); decoupled,
-        // every byte of shared memory is held for about half as long.
-        ptx::mbar_wait(ptx::smem_u32(BF16 ? &bar_lfree[s] : &bar_empty[s]), ph ^ 1u);
-        if (p == 0) DR4G_TRACE2(0);
-        const long long row0 = ((long long)split + (long long)it * job.ncl) * kt;
-        const uint32_t full = ptx::smem_u32(&bar_full[s]);
-        const uint32_t sx = smem_base + (uint32_t)s * stage_bytes;
-        // boxes of this stage dealt round-robin: box index q = it * slots + sl, owner q % kProducers
-        int mine = 0;
-        {
-          int own = pown;
-          for (int c = 0, sl = 0; c < cps; ++c)
-            for (int lb = 0; lb < nlb; ++lb, ++sl) {
-              if (own == p && row0 + c * kSlotRows < n && blk_of[lb] < T) ++mine;
-              if (++own == kProducers) own = 0;
+        if (owner == p) {
+          if (pacing && (it & 7) == 0 && it > 0) {
+            // rows this job has issued (all its clusters) against the slowest job that still has rows to issue
+            for (int tries = 0; tries < 48; ++tries) {
+              int mine = 0, slowest = 0x7fffffff;
+              for (int j = 0; j < table.njobs; ++j) {
+                int v;
+                asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(prog + j));
+                if (j == ji) mine = v;
+                if (v < slowest) slowest = v;
+              }
+              if (mine - slowest <= pace_rows) break;
+              if (tries == 47) pacing = false;   // nobody moved for ~60 us: not all jobs are resident, stop waiting for them
+              __nanosleep(1000);
             }
-        }
-        ptx::mbar_arrive_expect_tx(full, (uint32_t)mine * kSlotBytes);
-        {
-          int own = pown;
+          }
+          // 3xTF32: the stage (landing half converted in place + lo half) is free when its MMAs have completed.
+          // bf16x3: the operands live in the other half, so the landing half is free as soon as the converters have
+          // read it (bar_lfree) and the operand half when its MMAs have completed (bar_empty, waited for by the converters).
+          ptx::mbar_wait(ptx::smem_u32(BF16 ? &bar_lfree[s] : &bar_empty[s]), ph ^ 1u);
+          if (p == 0) DR4G_TRACE2(0);
+          const long long row0 = ((long long)split + (long long)it * job.ncl) * kt;
+          const uint32_t full = ptx::smem_u32(&bar_full[s]);
+          const uint32_t sx = smem_base + (uint32_t)s * stage_bytes;
+          int boxes = 0;
+          for (int c = 0; c < cps; ++c)
+            for (int lb = 0; lb < nlb; ++lb)
+              if (row0 + c * kSlotRows < n && blk_of[lb] < T) ++boxes;
+          ptx::mbar_arrive_expect_tx(full, (uint32_t)boxes * kSlotBytes);
           for (int c = 0, sl = 0; c < cps; ++c)
             for (int lb = 0; lb < nlb; ++lb, ++sl) {
-              const bool me = own == p;
-              if (++own == kProducers) own = 0;
               const long long row = row0 + c * kSlotRows;
-              if (!me || row >= n || blk_of[lb] >= T) continue;
+              if (row >= n || blk_of[lb] >= T) continue;
               ptx::tma_load_3d(sx + (uint32_t)sl * kSlotBytes, &tmap, full, 0, (int)row, blk_of[lb] * 4);
             }
-          pown = own;
+          if (prog != nullptr && rank == 0)
+            asm volatile("red.relaxed.gpu.global.add.s32 [%0], %1;" ::"l"(prog + ji), "r"(kt) : "memory");
+          if (p == 0) DR4G_TRACE2(1);
         }
-        if (p == 0) DR4G_TRACE2(1);
+        if (++owner == kProducers) owner = 0;
         if (++s == nstages) { s = 0; ph ^= 1u; }
       }
     }
@@ -736,7 +751,7 @@ bool gram_pair_eligible(const Ctx& c, const float* dX, long long n, int d) {
 }
 
 size_t gram_pair_workspace_bytes(const Ctx& c, int d) {
-  return (size_t)(c.sm_count / 2) * 2 * kSlabFloats * sizeof(float);
+  return (size_t)(c.sm_count / 2) * 2 * kSlabFloats * sizeof(float) + 256;   // + the jobs' progress counters
 }
 
 void launch_gram_pair(Ctx& c, const float* dX, long long n, int d, const float* dshift, double* dG, double* dsum,
@@ -767,6 +782,16 @@ void launch_gram_pair(Ctx& c, const float* dX, long long n, int d, const float* 
   const int flush_rows = c.flush_rows > 0 ? c.flush_rows : 1024;
   const int clusters = tab.job[tab.njobs - 1].cl_begin + tab.job[tab.njobs - 1].ncl;
   float* slab = static_cast<float*>(workspace);
+  // cross-job pacing: progress counters behind the slabs; a job may run ahead of the slowest one by ~24 MB of rows
+  static const int pace_mb = getenv("DR4G_PACE_MB") ? atoi(getenv("DR4G_PACE_MB")) : 24;
+  int* prog = nullptr;
+  int pace_rows = 0;
+  if (pace_mb > 0 && tab.njobs > 1) {
+    prog = reinterpret_cast<int*>(reinterpret_cast<char*>(workspace) + (size_t)(c.sm_count / 2) * 2 * kSlabFloats * sizeof(float));
+    DR4G_CUDA(cudaMemsetAsync(prog, 0, 256, c.stream));
+    pace_rows = (int)(((long long)pace_mb << 20) / ((long long)d * 4));
+    if (pace_rows < 1024) pace_rows = 1024;
+  }
   cudaLaunchConfig_t lc = {};
   lc.gridDim = dim3(2 * clusters, 1, 1);
   lc.blockDim = dim3(kThreads, 1, 1);
@@ -780,9 +805,9 @@ void launch_gram_pair(Ctx& c, const float* dX, long long n, int d, const float* 
   lc.attrs = at;
   lc.numAttrs = 1;
   if (bf16)
-    DR4G_CUDA(cudaLaunchKernelEx(&lc, gram_pair_kernel<true>, tmap, tab, n, d, dshift, slab, dsum, dsumsq, flush_rows, trace));
+    DR4G_CUDA(cudaLaunchKernelEx(&lc, gram_pair_kernel<true>, tmap, tab, n, d, dshift, slab, dsum, dsumsq, flush_rows, trace, prog, pace_rows));
   else
-    DR4G_CUDA(cudaLaunchKernelEx(&lc, gram_pair_kernel<false>, tmap, tab, n, d, dshift, slab, dsum, dsumsq, flush_rows, trace));
+    DR4G_CUDA(cudaLaunchKernelEx(&lc, gram_pair_kernel<false>, tmap, tab, n, d, dshift, slab, dsum, dsumsq, flush_rows, trace, prog, pace_rows));
   c.last_gram_kernel = bf16 ? 3 : 2;
   c.launches++;
   if (trace & 1) {

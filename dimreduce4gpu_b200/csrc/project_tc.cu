@@ -13,16 +13,17 @@
 // tile of A is read from shared memory once.  The epilogue adds the two accumulator halves.
 //
 // Data path (persistent CTA per SM, 13 warps):
-//   warps 0-7   loaders/converters: 128-bit coalesced loads of X straight from global memory into registers (each
-//               element is used by exactly one CTA, so there is nothing for TMA + a landing zone to share; the next
-//               stage's 8 loads per thread are in flight while the current one is converted), subtract the mean, split
-//               into bf16 hi / lo, store into the K-major SWIZZLE_128B operand tiles (128 rows x 64 columns per stage)
+//   warps 0-7   loaders/converters: every thread copies ITS 8 x 16 B of a stage global -> shared with cp.async (L2 only)
+//               into a thread-private landing ring three stages deep (96 KB in flight per SM; a register prefetch of one
+//               stage, 32 KB, left the kernel at 0.64 of HBM), reads them back, subtracts the mean, splits into bf16
+//               hi / lo and stores into the K-major SWIZZLE_128B operand tiles (128 rows x 64 columns per stage).  The
+//               landing data is private to the thread that copied it: no barrier, only cp.async.wait_group
 //   warp 8      one lane: bulk-copies the stage's slice of the pre-split components image (cp.async.bulk, 2 KP rows x
 //               128 B) and issues the tcgen05.mma (kind::f16) of the stage; owns the TMEM allocation
 //   warps 9-12  epilogue: tcgen05.ld of the finished 128 x 2 KP accumulator (double-buffered in TMEM), z = D1 + D2,
 //               128-bit stores of Z and U rows
-// Shared memory per stage: A hi 16 KB + A lo 16 KB + B (2 KP x 128 B); 3-4 stages.  Shared-memory traffic is ~10 B per
-// element of X (4 B converter stores, 4 B operand reads, B slices) against 20 B with a TMA landing zone.
+// Shared memory: operand ring (A hi 16 KB + A lo 16 KB + B 2 KP x 128 B per stage, 2-3 stages) + landing ring
+// (3 x 32 KB).  Shared-memory traffic is ~18 B per element of X (landing write + read, operand write + read, B slices).
 #include "common.cuh"
 #include "ptx_sm100.cuh"
 
@@ -36,6 +37,8 @@ constexpr int PT_MMA_WARP = 8;
 constexpr int PT_EPI_WARPS = 4;
 constexpr int PT_THREADS = (PT_CONV_WARPS + 1 + PT_EPI_WARPS) * 32;   // 416
 constexpr int PT_MAX_STAGES = 4;
+constexpr int PT_PF = 3;                                              // landing ring depth (stages in flight)
+constexpr uint32_t PT_LAND_BYTES = PT_ROWS * PT_KC * 4;              // 32 KB per landing stage
 constexpr uint32_t PT_A_BYTES = PT_ROWS * PT_KC * 2;                  // 16 KB per half
 
 __device__ __forceinline__ void bulk_copy_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
@@ -44,11 +47,12 @@ __device__ __forceinline__ void bulk_copy_g2s(uint32_t dst, const void* src, uin
                : "memory");
 }
 
-__device__ __forceinline__ float4 ldg_stream(const float* p) {
-  float4 v;
-  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
-  return v;
+__device__ __forceinline__ void pt_cp_async16(uint32_t dst, const void* src, int src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
 }
+__device__ __forceinline__ void pt_cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void pt_cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 // Q (k x d fp32) -> per 64-column chunk the shared-memory image of B = [hi rows 0..KP-1 ; lo rows KP..2KP-1], each row
 // 64 bf16 = 128 B, K-major SWIZZLE_128B (row r at (r / 8) * 1024 + (r % 8) * 128, 16-byte chunk c at c ^ (r % 8)).
@@ -127,56 +131,68 @@ project_tc_kernel(const float* __restrict__ X, long long n, int d, int k, const 
       soff[j] = (uint32_t)(row >> 3) * 1024u + (uint32_t)(row & 7) * 128u +
                 (uint32_t)((((c4 >> 1) ^ (row & 7)) << 4) | ((c4 & 1) << 3));
     }
-    float4 cur[8], nxt[8], mu_cur = make_float4(0.f, 0.f, 0.f, 0.f), mu_nxt = mu_cur;
-    bool cur_ok[8], nxt_ok[8];
+    // landing ring behind the operand ring: slot p holds [j][thread] float4 (a warp's 32 x 16 B are contiguous)
+    const uint32_t land_base = smem_base + (uint32_t)nstages * STAGE_BYTES;
     const long long total = my_tiles * nch;
-    auto fetch = [&](long long tile, int c) {
-      const int col = c * PT_KC + c4 * 4;
-      const bool cin = col < d;                          // d % 4 == 0: a float4 is inside or outside as a whole
-      const long long row0 = tile * PT_ROWS + r;
-      const float* base = X + row0 * (long long)d + col;
+    // (tile, chunk) of the next stage to copy
+    long long ftile = blockIdx.x;
+    int fc = 0;
+    long long fit = 0;
+    auto issue = [&]() {
+      if (fit < total) {
+        const int col = fc * PT_KC + c4 * 4;
+        const bool cin = col < d;                          // d % 4 == 0: a float4 is inside or outside as a whole
+        const long long row0 = ftile * PT_ROWS + r;
+        const float* base = X + row0 * (long long)d + (cin ? col : 0);
+        const uint32_t dst = land_base + (uint32_t)(fit % PT_PF) * PT_LAND_BYTES + (uint32_t)tid * 16u;
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        nxt_ok[j] = cin && row0 + 16 * j < n;
-        nxt[j] = nxt_ok[j] ? ldg_stream(base + (long long)(16 * j) * d) : make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int j = 0; j < 8; ++j) {
+          // rows past n / columns past d are zero-filled; a row past n only feeds an output row that is never stored
+          const bool ok = cin && row0 + 16 * j < n;
+          pt_cp_async16(dst + (uint32_t)j * 4096u, ok ? base + (long long)(16 * j) * d : X, ok ? 16 : 0);
+        }
+        if (++fc == nch) { fc = 0; ftile += gridDim.x; }
       }
-      mu_nxt = (mean && cin) ? __ldg(reinterpret_cast<const float4*>(mean + col)) : make_float4(0.f, 0.f, 0.f, 0.f);
+      pt_cp_async_commit();   // one group per stage, possibly empty: keeps the wait count uniform
+      ++fit;
     };
-    long long tile = blockIdx.x;
+#pragma unroll
+    for (int p = 0; p < PT_PF; ++p) issue();
     int c = 0, s = 0;
     uint32_t ph = 0;
-    if (total > 0) fetch(tile, 0);
     for (long long it = 0; it < total; ++it) {
+      pt_cp_async_wait<PT_PF - 1>();                       // this thread's copies of stage `it` have landed
+      const uint32_t src = land_base + (uint32_t)(it % PT_PF) * PT_LAND_BYTES + (uint32_t)tid * 16u;
+      float4 x[8];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) { cur[j] = nxt[j]; cur_ok[j] = nxt_ok[j]; }
-      mu_cur = mu_nxt;
-      // next (tile, chunk) in flight while this one is converted
-      long long ntile = tile;
-      int nc = c + 1;
-      if (nc == nch) { nc = 0; ntile += gridDim.x; }
-      if (it + 1 < total) fetch(ntile, nc);
+      for (int j = 0; j < 8; ++j)
+        asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(x[j].x), "=f"(x[j].y), "=f"(x[j].z), "=f"(x[j].w) : "r"(src + (uint32_t)j * 4096u));
+      const int col = c * PT_KC + c4 * 4;
+      const float4 mu = (mean && col < d) ? __ldg(reinterpret_cast<const float4*>(mean + col)) : make_float4(0.f, 0.f, 0.f, 0.f);
+      uint32_t hp[8][2], lp[8][2];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float y0 = x[j].x - mu.x, y1 = x[j].y - mu.y, y2 = x[j].z - mu.z, y3 = x[j].w - mu.w;
+        hp[j][0] = ptx::pack_bf16x2(y0, y1);
+        hp[j][1] = ptx::pack_bf16x2(y2, y3);
+        lp[j][0] = ptx::pack_bf16x2(y0 - __uint_as_float(hp[j][0] << 16), y1 - __uint_as_float(hp[j][0] & 0xffff0000u));
+        lp[j][1] = ptx::pack_bf16x2(y2 - __uint_as_float(hp[j][1] << 16), y3 - __uint_as_float(hp[j][1] & 0xffff0000u));
+      }
+      issue();                                             // refill this landing slot (its data is in registers now)
       ptx::mbar_wait(ptx::smem_u32(&bar_empty[s]), ph ^ 1u);
       const uint32_t sa = smem_base + (uint32_t)s * STAGE_BYTES;
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        uint32_t h01 = 0u, h23 = 0u, l01 = 0u, l23 = 0u;
-        if (cur_ok[j]) {
-          const float y0 = cur[j].x - mu_cur.x, y1 = cur[j].y - mu_cur.y, y2 = cur[j].z - mu_cur.z, y3 = cur[j].w - mu_cur.w;
-          h01 = ptx::pack_bf16x2(y0, y1);
-          h23 = ptx::pack_bf16x2(y2, y3);
-          l01 = ptx::pack_bf16x2(y0 - __uint_as_float(h01 << 16), y1 - __uint_as_float(h01 & 0xffff0000u));
-          l23 = ptx::pack_bf16x2(y2 - __uint_as_float(h23 << 16), y3 - __uint_as_float(h23 & 0xffff0000u));
-        }
-        asm volatile("st.shared.v2.b32 [%0], {%1,%2};" ::"r"(sa + soff[j]), "r"(h01), "r"(h23) : "memory");
-        asm volatile("st.shared.v2.b32 [%0], {%1,%2};" ::"r"(sa + PT_A_BYTES + soff[j]), "r"(l01), "r"(l23) : "memory");
+        asm volatile("st.shared.v2.b32 [%0], {%1,%2};" ::"r"(sa + soff[j]), "r"(hp[j][0]), "r"(hp[j][1]) : "memory");
+        asm volatile("st.shared.v2.b32 [%0], {%1,%2};" ::"r"(sa + PT_A_BYTES + soff[j]), "r"(lp[j][0]), "r"(lp[j][1]) : "memory");
       }
       ptx::fence_proxy_async_smem();   // generic-proxy stores -> visible to the tensor core's async-proxy reads
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&bar_full[s]));
       if (++s == nstages) { s = 0; ph ^= 1u; }
-      tile = ntile;
-      c = nc;
+      if (++c == nch) c = 0;
     }
+    pt_cp_async_wait<0>();
   } else if (warp == PT_MMA_WARP) {
     // ================================================================ B slices + MMA issue (one lane)
     if (ptx::elect_one()) {
@@ -287,9 +303,10 @@ template <int KP>
 void launch_kp(Ctx& c, const float* dX, long long n, int d, int k, const float* dmean, const uint8_t* img, const float* dw,
                float* dZ, float* dU) {
   constexpr uint32_t stage = 2 * PT_A_BYTES + 2 * KP * 128;
-  int nstages = (int)((200u * 1024u) / stage);
+  constexpr uint32_t land = PT_PF * PT_LAND_BYTES;
+  int nstages = (int)((225u * 1024u - land) / stage);   // 3 / 2 / 2 operand stages at KP = 32 / 64 / 128
   if (nstages > PT_MAX_STAGES) nstages = PT_MAX_STAGES;
-  const size_t smem = (size_t)nstages * stage + 1024;
+  const size_t smem = (size_t)nstages * stage + land + 1024;
   static PerDeviceMax smem_set;
   if (smem_set.need(c.device, smem))
     DR4G_CUDA(cudaFuncSetAttribute(project_tc_kernel<KP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
