@@ -168,7 +168,7 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
   if (warp >= kConvWarps && warp < kMmaWarp) {
     // ================================================================ TMA producers (each CTA its own blocks)
     // Measured (tools/tma_probe.cu): a thread issues one box per ~700 cycles whatever the box size, so one issuer with
-    // 8 KB boxes streams 3.1 TB/s chip-wide and four issuers 6.5 TB/s.  Stage `it` belongs to producer it % kProducers,
+    // 8 KB boxes streams 3.1 TB/s chip-wide and four issuers 6.5 TB/s.  A stage belongs to ONE producer,
     // which does everything for it (wait, expect_tx, all boxes): a first version dealt the BOXES round-robin and had
     // every producer arrive on every stage's barrier - its pipeline trace showed ~750 cycles per stage and producer
     // whether or not the producer owned a box, so three producers advanced no faster than one (1030 cycles per 16-row
@@ -183,6 +183,11 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
     if (ptx::elect_one()) {
       const int p = warp - kConvWarps;
       ptx::prefetch_tmap(&tmap);
+      // a producer owns fixed STAGES of the ring (stage s belongs to producer s % np, np dividing the ring length), so it
+      // waits for every round of its stages in order: with ownership by iteration (it % 3 on a ring of 4) the parity wait
+      // of round r could pass while round r - 2 of that stage was still open (the wait only distinguishes two phases),
+      // and two producers armed the same phase of bar_full (cuda-gdb: Warp Illegal Instruction in arrive.expect_tx)
+      const int np = nstages % 3 == 0 ? 3 : (nstages % 2 == 0 ? 2 : 1);
       int s = 0, owner = 0;
       uint32_t ph = 0;
       bool pacing = prog != nullptr && table.njobs > 1;
@@ -229,8 +234,8 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
             asm volatile("red.relaxed.gpu.global.add.s32 [%0], %1;" ::"l"(prog + ji), "r"(kt) : "memory");
           if (p == 0) DR4G_TRACE2(1);
         }
-        if (++owner == kProducers) owner = 0;
-        if (++s == nstages) { s = 0; ph ^= 1u; }
+        if (++owner == np) owner = 0;
+        if (++s == nstages) { s = 0; ph ^= 1u; owner = 0; }
       }
     }
   } else if (warp == kMmaWarp) {
