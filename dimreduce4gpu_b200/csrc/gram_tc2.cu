@@ -55,8 +55,10 @@ namespace {
 constexpr int kBlk = 128;
 constexpr int kSlotBytes = 8192;         // 16 rows x 128 columns x 4 B
 constexpr int kSlotRows = 16;
-constexpr int kRingBytes = 196608;       // stage ring (hi + lo halves)
-constexpr int kMaxStages = 6;
+constexpr int kRingBytes = 196608;       // 3xTF32: stage ring (hi + lo halves)
+constexpr int kRingBytesBf16 = 229376;   // bf16x3: landing ring + operand ring (224 KB)
+constexpr int kMaxStages = 12;
+constexpr int kMaxStagesTf32 = 6;
 constexpr int kConvWarps = 8;
 constexpr int kConvThreads = kConvWarps * 32;
 constexpr int kEpiWarps = 4;
@@ -92,6 +94,160 @@ __device__ long long g_trace2[kTraceIts * 8];
 
 __device__ __forceinline__ float clear13(float v) { return __uint_as_float(__float_as_uint(v) & 0xffffe000u); }
 
+// ------------------------------------------------------------------------------------------------ converters
+// What the converter warps need to know about the kernel's rings and barriers (all shared-memory addresses).
+struct ConvArgs {
+  uint32_t smem_base, op_base, land_stride, half_bytes;
+  uint32_t bar_full, bar_conv_leader, bar_empty, bar_lfree;   // arrays of 8-byte barriers (bar_conv: in the leader CTA)
+  int NL, NO, my_chunks, ncl, split, kt, trace;
+  long long n;
+};
+
+// One group of 4 converter warps (grp = 0 / 1 takes the even / odd stages).  The whole loop is instantiated per
+// <operand split, column blocks per stage, column statistics>, so that an off-diagonal job does not carry the fp64
+// statistics registers and every variant keeps all of a stage's loads in flight (the first version was one loop for
+// every job type: ptxas serialised its eight 128-bit loads into four round trips to fit 120 registers, and the eight
+// converter warps - two per scheduler - ran at ~2.5 cycles per instruction, 350 instructions per thread and stage).
+// Thread -> fixed position inside a 16-row x 128-column slot: 4 columns (32-column group g, 16-byte chunk lc) and the
+// rows rg + 4 h, h = 0..3.  Landing layout (TMA, SWIZZLE_128B_ATOM_32B): [g][row][128 B], 32-byte chunks XOR row % 4.
+// bf16 operand layout of a slot: hi 4 KB then lo 4 KB, each [64-column group g >> 1][8-row atom][8 rows][128 B], 16-byte
+// chunks XOR row % 8 (SWIZZLE_128B); a thread's 4 columns are 8 bytes.
+template <bool BF16, int NLB, bool STATS>
+__device__ __forceinline__ void converter_loop(const ConvArgs& a, const int grp, const float4 (&sh)[3], const bool (&col_ok)[3],
+                                               const int col0, double* __restrict__ osum, double* __restrict__ osq) {
+  constexpr int CPS = NLB == 1 ? 2 : 1;
+  constexpr int NS = CPS * NLB;                    // slots per stage
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int lc = tid & 7, g = (tid >> 3) & 3, rg = warp & 3;
+  const int trace = a.trace;
+  // r = rg + 4 h: r % 4 = rg for every h, so the landing offset is toff0 + 512 h
+  const uint32_t toff0 = (uint32_t)g * 2048u + (uint32_t)rg * 128u + (uint32_t)(((((lc >> 1) ^ rg) << 1) | (lc & 1)) << 4);
+  // r % 8 = rg + 4 (h & 1), r / 8 = h >> 1: operand offset boff[h & 1] + 1024 (h >> 1)
+  uint32_t boff[2];
+#pragma unroll
+  for (int e = 0; e < 2; ++e) {
+    const int r7 = rg + 4 * e;
+    boff[e] = (uint32_t)(g >> 1) * 2048u + (uint32_t)r7 * 128u + (uint32_t)((((((g & 1) << 2) | (lc >> 1)) ^ r7) << 4) | ((lc & 1) << 3));
+  }
+  bool cols_ok = true;
+#pragma unroll
+  for (int lb = 0; lb < NLB; ++lb) cols_ok = cols_ok && col_ok[lb];
+  const bool stat_owner = STATS && col_ok[0] && osum != nullptr;
+  double ds[4] = {0, 0, 0, 0}, dq[4] = {0, 0, 0, 0};
+  float fs[4] = {0.f, 0.f, 0.f, 0.f}, fq[4] = {0.f, 0.f, 0.f, 0.f};
+  int s = grp, so = grp, pending = 0;              // landing slot / operand slot of this group's next stage (NL, NO even)
+  uint32_t ph = 0, pho = 0;
+
+  for (int it = grp; it < a.my_chunks; it += 2) {
+    if (lane == 0 && rg == 0) DR4G_TRACE2(7);
+    ptx::mbar_wait(a.bar_full + (uint32_t)s * 8u, ph);
+    if (lane == 0 && rg == 0) DR4G_TRACE2(2);
+    if constexpr (BF16) {
+      // operand slot free (its MMAs of NO stages ago have completed; normally long ago)
+      ptx::mbar_wait(a.bar_empty + (uint32_t)so * 8u, pho ^ 1u);
+      if ((trace & 16) && lane == 0 && rg == 0) DR4G_TRACE2(1);
+    }
+    const long long row0 = ((long long)a.split + (long long)it * a.ncl) * a.kt;
+    const uint32_t sx = a.smem_base + (uint32_t)s * a.land_stride + toff0;
+    const uint32_t ox = a.op_base + (uint32_t)so * a.land_stride + boff[0];
+    const uint32_t bdelta = boff[1] - boff[0];
+    const bool fast = cols_ok && row0 + a.kt <= a.n;     // every element of the stage is a real one
+
+    auto body = [&](auto masked_c) {
+      constexpr bool MASKED = decltype(masked_c)::value;
+      float4 x[NS * 4];
+#pragma unroll
+      for (int sl = 0; sl < NS; ++sl)
+#pragma unroll
+        for (int h = 0; h < 4; ++h)
+          asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
+                       : "=f"(x[sl * 4 + h].x), "=f"(x[sl * 4 + h].y), "=f"(x[sl * 4 + h].z), "=f"(x[sl * 4 + h].w)
+                       : "r"(sx + (uint32_t)sl * kSlotBytes + (uint32_t)h * 512u));
+#pragma unroll
+      for (int sl = 0; sl < NS; ++sl) {
+        const int lb = sl % NLB, c = sl / NLB;
+#pragma unroll
+        for (int h = 0; h < 4; ++h) {
+          const float4 v = x[sl * 4 + h];
+          float y0 = v.x - sh[lb].x, y1 = v.y - sh[lb].y, y2 = v.z - sh[lb].z, y3 = v.w - sh[lb].w;
+          if constexpr (MASKED) {
+            if (!(col_ok[lb] && row0 + c * kSlotRows + rg + 4 * h < a.n)) { y0 = 0.f; y1 = 0.f; y2 = 0.f; y3 = 0.f; }
+          }
+          if constexpr (STATS) {
+            if (lb == 0) {
+              fs[0] += y0; fs[1] += y1; fs[2] += y2; fs[3] += y3;
+              fq[0] = fmaf(y0, y0, fq[0]); fq[1] = fmaf(y1, y1, fq[1]);
+              fq[2] = fmaf(y2, y2, fq[2]); fq[3] = fmaf(y3, y3, fq[3]);
+            }
+          }
+          if constexpr (BF16) {
+            const uint32_t h01 = ptx::pack_bf16x2(y0, y1), h23 = ptx::pack_bf16x2(y2, y3);
+            // y - bf16(y) is exact in fp32; its bf16 rounding is the second term
+            const uint32_t l01 = ptx::pack_bf16x2(y0 - __uint_as_float(h01 << 16), y1 - __uint_as_float(h01 & 0xffff0000u));
+            const uint32_t l23 = ptx::pack_bf16x2(y2 - __uint_as_float(h23 << 16), y3 - __uint_as_float(h23 & 0xffff0000u));
+            const uint32_t o = ox + (uint32_t)sl * kSlotBytes + (uint32_t)(h >> 1) * 1024u + ((h & 1) ? bdelta : 0u);
+            asm volatile("st.shared.v2.b32 [%0], {%1,%2};" ::"r"(o), "r"(h01), "r"(h23) : "memory");
+            asm volatile("st.shared.v2.b32 [%0], {%1,%2};" ::"r"(o + 4096u), "r"(l01), "r"(l23) : "memory");
+          } else {
+            float4 hi, lo;
+            hi.x = clear13(y0); hi.y = clear13(y1); hi.z = clear13(y2); hi.w = clear13(y3);
+            lo.x = clear13(y0 - hi.x); lo.y = clear13(y1 - hi.y); lo.z = clear13(y2 - hi.z); lo.w = clear13(y3 - hi.w);
+            const uint32_t o = sx + (uint32_t)sl * kSlotBytes + (uint32_t)h * 512u;   // hi in place, lo in the second half
+            asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(o), "f"(hi.x), "f"(hi.y), "f"(hi.z), "f"(hi.w) : "memory");
+            asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(o + a.half_bytes), "f"(lo.x), "f"(lo.y), "f"(lo.z), "f"(lo.w) : "memory");
+          }
+        }
+      }
+    };
+    if (trace & 4) {          // probe: no conversion, the barriers still cycle
+    } else if (fast) body(std::false_type{});
+    else body(std::true_type{});
+    if constexpr (BF16) {
+      // every load of the landing slot has been consumed: hand it back to its TMA producer
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(a.bar_lfree + (uint32_t)s * 8u);
+    }
+    if constexpr (STATS) {
+      // fp32 partial sums of at most 16 stages x 8 rows, then fp64 (fp64 conversions and adds are slow enough on B200
+      // to double the conversion time when done per stage: measured)
+      if (stat_owner && (++pending == 16 || it + 2 >= a.my_chunks)) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          ds[j] += (double)fs[j]; dq[j] += (double)fq[j];
+          fs[j] = 0.f; fq[j] = 0.f;
+        }
+        pending = 0;
+      }
+    }
+    if (lane == 0 && rg == 0) DR4G_TRACE2(3);
+    // the MMA that reads this stage is issued by the leader CTA but reads THIS CTA's shared memory: make the writes
+    // visible to the async proxy (the fence also waits for the stores queued behind the MMA's operand reads), then
+    // arrive on the leader's barrier.  After the fence the stores are complete and the data's consumer is this CTA's
+    // own tensor core, so the arrive is relaxed (a release at cluster scope cost 1000-3000 cycles here, measured).
+    ptx::fence_proxy_async_smem();
+    __syncwarp();
+    if (lane == 0) {
+      if (trace & 8) ptx::mbar_arrive_cluster(a.bar_conv_leader + (uint32_t)so * 8u);
+      else ptx::mbar_arrive_cluster_relaxed(a.bar_conv_leader + (uint32_t)so * 8u);
+    }
+    if (lane == 0 && rg == 0) DR4G_TRACE2(4);
+    s += 2;
+    if (s >= a.NL) { s -= a.NL; ph ^= 1u; }
+    so += 2;
+    if (so >= a.NO) { so -= a.NO; pho ^= 1u; }
+  }
+  if constexpr (STATS) {
+    if (stat_owner) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        atomicAdd(&osum[col0 + j], ds[j]);
+        atomicAdd(&osq[col0 + j], dq[j]);
+      }
+    }
+  }
+}
+
+
 // BF16 = false: 3xTF32 (kind::tf32, hi/lo = two 11-bit halves, fp32-exact products except lo*lo).
 // BF16 = true:  bf16x3 (kind::f16, twice the multiply rate, K = 16 per instruction): y = b1 + b2 + (|rest| <= 2^-18 |y|)
 //   with b1 = bf16(y), b2 = bf16(y - b1), both rounded to nearest so the dropped parts have zero mean; products
@@ -104,7 +260,7 @@ template <bool BF16>
 __global__ void __launch_bounds__(kThreads, 1)
 gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ PJobTable table, long long n, int d,
                  const float* __restrict__ shift, float* __restrict__ slab, double* __restrict__ osum,
-                 double* __restrict__ osq, int flush_rows, int trace, int* __restrict__ prog, int pace_rows) {
+                 double* __restrict__ osq, int flush_rows, int trace, int* __restrict__ prog, int pace_rows, int op_stages) {
   // ---------------------------------------------------------------- which job / which chunks
   const uint32_t rank = ptx::cluster_ctarank();
   const int cluster = (int)blockIdx.x >> 1;
@@ -121,7 +277,18 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
   const int slots = cps * nlb;
   const uint32_t half_bytes = (uint32_t)slots * kSlotBytes;   // hi half, then lo half
   const uint32_t stage_bytes = 2u * half_bytes;
-  const int nstages = (int)(kRingBytes / stage_bytes) < kMaxStages ? (int)(kRingBytes / stage_bytes) : kMaxStages;
+  // 3xTF32: ONE ring of stages (landing half converted in place = hi, lo half behind it): NL = NO.
+  // bf16x3: TWO rings.  The operands (hi + lo bf16 = 4 B per element) go to their own ring of NO `half_bytes` slots and
+  // the fp32 landing slots form a ring of NL.  A landing slot is held from the TMA issue to the converters' read (free ->
+  // issue ~1000 cycles -> landed 1500-4000 -> read ~600: measured with the trace hook), an operand slot only from the
+  // converters' store to the end of its MMAs (~1500), and the pass ran at the pace of the landing ring (6 x 16 KB in
+  // flight per SM against that latency: ~1000 cycles per stage, tensor pipe 35 % active, smem and HBM under 50 %).  So
+  // nearly all of the shared memory is landing ring (12 x 16 KB or 6 x 24 KB in flight) and the operand ring is short.
+  const int NO = BF16 ? op_stages : ((int)(kRingBytes / stage_bytes) < kMaxStagesTf32 ? (int)(kRingBytes / stage_bytes) : kMaxStagesTf32);
+  int nl_ = BF16 ? (((int)(kRingBytesBf16 / half_bytes) - NO) & ~1) : NO;   // even: a converter group always meets the same slots
+  const int NL = nl_ > kMaxStages ? kMaxStages : nl_;
+  const uint32_t land_stride = BF16 ? half_bytes : stage_bytes;
+  const uint32_t op_stride = land_stride;
   const long long n_chunks = (n + kt - 1) / kt;
   if (split >= job.ncl || split >= n_chunks) return;    // both CTAs of a pair take the same branch
   const int my_chunks = (int)((n_chunks - split + job.ncl - 1) / job.ncl);
@@ -136,6 +303,7 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
 
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t op_base = BF16 ? smem_base + (uint32_t)NL * half_bytes : smem_base;   // 3xTF32: hi in place, lo at + half_bytes
   __shared__ __align__(8) uint64_t bar_full[kMaxStages], bar_conv[kMaxStages], bar_empty[kMaxStages], bar_lfree[kMaxStages];
   __shared__ __align__(8) uint64_t bar_acc_full[2], bar_acc_empty[2];
   __shared__ uint32_t tmem_base_slot;
@@ -187,7 +355,7 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
       // waits for every round of its stages in order: with ownership by iteration (it % 3 on a ring of 4) the parity wait
       // of round r could pass while round r - 2 of that stage was still open (the wait only distinguishes two phases),
       // and two producers armed the same phase of bar_full (cuda-gdb: Warp Illegal Instruction in arrive.expect_tx)
-      const int np = nstages % 3 == 0 ? 3 : (nstages % 2 == 0 ? 2 : 1);
+      const int np = NL % 3 == 0 ? 3 : (NL % 2 == 0 ? 2 : 1);
       int s = 0, owner = 0;
       uint32_t ph = 0;
       bool pacing = prog != nullptr && table.njobs > 1;
@@ -215,10 +383,10 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
           // bf16x3: the operands live in the other half, so the landing half is free as soon as the converters have
           // read it (bar_lfree) and the operand half when its MMAs have completed (bar_empty, waited for by the converters).
           ptx::mbar_wait(ptx::smem_u32(BF16 ? &bar_lfree[s] : &bar_empty[s]), ph ^ 1u);
-          if (p == 0) DR4G_TRACE2(0);
+          if (p == 0 && !(trace & 16)) DR4G_TRACE2(0);
           const long long row0 = ((long long)split + (long long)it * job.ncl) * kt;
           const uint32_t full = ptx::smem_u32(&bar_full[s]);
-          const uint32_t sx = smem_base + (uint32_t)s * stage_bytes;
+          const uint32_t sx = smem_base + (uint32_t)s * land_stride;
           int boxes = 0;
           for (int c = 0; c < cps; ++c)
             for (int lb = 0; lb < nlb; ++lb)
@@ -232,10 +400,10 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
             }
           if (prog != nullptr && rank == 0)
             asm volatile("red.relaxed.gpu.global.add.s32 [%0], %1;" ::"l"(prog + ji), "r"(kt) : "memory");
-          if (p == 0) DR4G_TRACE2(1);
+          if (p == 0 && !(trace & 16)) DR4G_TRACE2(1);
         }
         if (++owner == np) owner = 0;
-        if (++s == nstages) { s = 0; ph ^= 1u; owner = 0; }
+        if (++s == NL) { s = 0; ph ^= 1u; owner = 0; }
       }
     }
   } else if (warp == kMmaWarp) {
@@ -252,7 +420,7 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
                                   : ptx::make_smem_desc(0, 2048, 512, ptx::kLayoutSw128Base32);
       int s = 0, window = 0, wpos = stagger, set = 0;
       uint32_t ph = 0, racc = 0u;
-      uint32_t sx = smem_base;
+      uint32_t sx = op_base;
       bool window_start = true;
       for (int it = 0; it < my_chunks; ++it) {
         if (window_start && window >= nacc) {
@@ -268,7 +436,7 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
         if constexpr (BF16) {
           // one K = 16 instruction per product and 16-row slot; hi at the slot's offset in the second half of the
           // stage, lo 4 KB behind it
-          uint32_t row = sx + half_bytes;
+          uint32_t row = sx;
 #pragma unroll 1
           for (int ks = 0; ks < nks; ks += 2) {
             const uint64_t a_hi = desc0 | (uint64_t)((row >> 4) & 0x3FFF);
@@ -339,20 +507,16 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
           window_start = true;
           if (nacc == 2) set ^= 1;
         }
-        sx += stage_bytes;
-        if (++s == nstages) { s = 0; ph ^= 1u; sx = smem_base; }
+        sx += op_stride;
+        if (++s == NO) { s = 0; ph ^= 1u; sx = op_base; }
       }
     }
   } else if (warp < kConvWarps) {
-    // ================================================================ converters (+ column statistics)
-    // Two groups of 4 warps convert alternate stages, so that one group's store drain (the proxy
-    // fence waits for the stores queued behind the MMA's operand reads, ~1000-2000 cycles) overlaps the
-    // other group's loads.  thread -> fixed position inside a slot: 4 columns (group g, 16-byte chunk
-    // lc) and rows rg + 4 h, h = 0..3
+    // ================================================================ converters (+ column statistics): converter_loop above
+    // Two groups of 4 warps convert alternate stages, so that one group's store drain (the proxy fence waits for the
+    // stores queued behind the MMA's operand reads) overlaps the other group's loads.
     const int tid = threadIdx.x;
-    const int grp = warp >> 2;
-    const int lc = tid & 7, g = (tid >> 3) & 3, rg = warp & 3;
-    const uint32_t conv_leader = ptx::mapa(ptx::smem_u32(&bar_conv[0]), 0);
+    const int lc = tid & 7, g = (tid >> 3) & 3;
     float4 sh[3];
     bool col_ok[3];
     int col0[3];
@@ -363,149 +527,18 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
       col_ok[lb] = col0[lb] < d;
       if (col_ok[lb] && shift) sh[lb] = *reinterpret_cast<const float4*>(shift + col0[lb]);
     }
-    const bool stat_owner = job.stats && col_ok[0] && osum != nullptr;
-    double ds[4] = {0, 0, 0, 0}, dq[4] = {0, 0, 0, 0};
-    // 32-byte chunks XOR (row % 4): the BASE32B swizzle, as TMA (SWIZZLE_128B_ATOM_32B) laid it out
-    uint32_t toff[4];
-#pragma unroll
-    for (int h = 0; h < 4; ++h) {
-      const int r = rg + 4 * h;
-      toff[h] = (uint32_t)g * 2048u + (uint32_t)r * 128u + (uint32_t)(((((lc >> 1) ^ (r & 3)) << 1) | (lc & 1)) << 4);
-    }
-    // bf16 operand layout of a slot (second half of the stage): hi 4 KB then lo 4 KB, each [64-column group
-    // g >> 1][8-row atom][8 rows][128 B], 16-byte chunks XOR (row % 8) = SWIZZLE_128B; this thread's 4 columns are 8 B
-    uint32_t boff[4];
-#pragma unroll
-    for (int h = 0; h < 4; ++h) {
-      const int r = rg + 4 * h;
-      boff[h] = (uint32_t)(g >> 1) * 2048u + (uint32_t)(r >> 3) * 1024u + (uint32_t)(r & 7) * 128u +
-                (uint32_t)((((((g & 1) << 2) | (lc >> 1)) ^ (r & 7)) << 4) | ((lc & 1) << 3));
-    }
-    int s = 0, pending = 0;
-    uint32_t ph = 0;
-    float fs[4] = {0.f, 0.f, 0.f, 0.f}, fq[4] = {0.f, 0.f, 0.f, 0.f};
-    for (int it = 0; it < my_chunks; ++it) {
-      if ((it & 1) != grp) {
-        if (++s == nstages) { s = 0; ph ^= 1u; }
-        continue;
-      }
-      ptx::mbar_wait(ptx::smem_u32(&bar_full[s]), ph);
-      if (lane == 0 && rg == 0) DR4G_TRACE2(2);
-      const long long row0 = ((long long)split + (long long)it * job.ncl) * kt;
-      const uint32_t sx = smem_base + (uint32_t)s * stage_bytes;
-      // one stage = CPS x NLB slots, four float4 per slot and thread; all loads are issued before
-      // the first store so that the shared-memory latency (long beside the MMA's operand reads)
-      // is paid once per stage, not once per slot
-      auto convert = [&](auto nlb_c) {
-        constexpr int NLB = decltype(nlb_c)::value;
-        constexpr int CPS = NLB == 1 ? 2 : 1;
-        float4 x[CPS * NLB * 4];
-        bool ok[CPS * NLB * 4];
-#pragma unroll
-        for (int c = 0; c < CPS; ++c)
-#pragma unroll
-          for (int lb = 0; lb < NLB; ++lb)
-#pragma unroll
-            for (int h = 0; h < 4; ++h) {
-              const int i = (c * NLB + lb) * 4 + h;
-              const uint32_t a = sx + (uint32_t)(c * NLB + lb) * kSlotBytes + toff[h];
-              ok[i] = col_ok[lb] && row0 + c * kSlotRows + rg + 4 * h < n;
-              asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(x[i].x), "=f"(x[i].y), "=f"(x[i].z), "=f"(x[i].w) : "r"(a));
-            }
-#pragma unroll
-        for (int c = 0; c < CPS; ++c)
-#pragma unroll
-          for (int lb = 0; lb < NLB; ++lb)
-#pragma unroll
-            for (int h = 0; h < 4; ++h) {
-              const int i = (c * NLB + lb) * 4 + h;
-              const uint32_t a = sx + (uint32_t)(c * NLB + lb) * kSlotBytes + toff[h];
-              if constexpr (BF16) {
-                uint32_t h01 = 0u, h23 = 0u, l01 = 0u, l23 = 0u;
-                if (ok[i]) {
-                  const float y0 = x[i].x - sh[lb].x, y1 = x[i].y - sh[lb].y, y2 = x[i].z - sh[lb].z, y3 = x[i].w - sh[lb].w;
-                  if (lb == 0) {
-                    fs[0] += y0; fs[1] += y1; fs[2] += y2; fs[3] += y3;
-                    fq[0] = fmaf(y0, y0, fq[0]); fq[1] = fmaf(y1, y1, fq[1]);
-                    fq[2] = fmaf(y2, y2, fq[2]); fq[3] = fmaf(y3, y3, fq[3]);
-                  }
-                  h01 = ptx::pack_bf16x2(y0, y1);
-                  h23 = ptx::pack_bf16x2(y2, y3);
-                  // y - bf16(y) is exact in fp32; its bf16 rounding is the second term
-                  l01 = ptx::pack_bf16x2(y0 - __uint_as_float(h01 << 16), y1 - __uint_as_float(h01 & 0xffff0000u));
-                  l23 = ptx::pack_bf16x2(y2 - __uint_as_float(h23 << 16), y3 - __uint_as_float(h23 & 0xffff0000u));
-                }
-                // packed results replace the fp32 values in their registers; stored once the operand half is free
-                x[i].x = __uint_as_float(h01); x[i].y = __uint_as_float(h23);
-                x[i].z = __uint_as_float(l01); x[i].w = __uint_as_float(l23);
-              } else {
-              float4 hi = make_float4(0.f, 0.f, 0.f, 0.f), lo = hi;
-              if (ok[i]) {
-                const float y0 = x[i].x - sh[lb].x, y1 = x[i].y - sh[lb].y, y2 = x[i].z - sh[lb].z, y3 = x[i].w - sh[lb].w;
-                if (lb == 0) {
-                  fs[0] += y0; fs[1] += y1; fs[2] += y2; fs[3] += y3;
-                  fq[0] = fmaf(y0, y0, fq[0]); fq[1] = fmaf(y1, y1, fq[1]);
-                  fq[2] = fmaf(y2, y2, fq[2]); fq[3] = fmaf(y3, y3, fq[3]);
-                }
-                hi.x = clear13(y0); hi.y = clear13(y1); hi.z = clear13(y2); hi.w = clear13(y3);
-                lo.x = clear13(y0 - hi.x); lo.y = clear13(y1 - hi.y); lo.z = clear13(y2 - hi.z); lo.w = clear13(y3 - hi.w);
-              }
-              asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(a), "f"(hi.x), "f"(hi.y), "f"(hi.z), "f"(hi.w) : "memory");
-              asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(a + half_bytes), "f"(lo.x), "f"(lo.y), "f"(lo.z), "f"(lo.w) : "memory");
-              }
-            }
-        if constexpr (BF16) {
-          // landing half read: hand it back to the TMA producers, then wait for the MMAs that still read the operand half
-          __syncwarp();
-          if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&bar_lfree[s]));
-          ptx::mbar_wait(ptx::smem_u32(&bar_empty[s]), ph ^ 1u);
-#pragma unroll
-          for (int c = 0; c < CPS; ++c)
-#pragma unroll
-            for (int lb = 0; lb < NLB; ++lb)
-#pragma unroll
-              for (int h = 0; h < 4; ++h) {
-                const int i = (c * NLB + lb) * 4 + h;
-                const uint32_t o = sx + half_bytes + (uint32_t)(c * NLB + lb) * kSlotBytes + boff[h];
-                asm volatile("st.shared.v2.b32 [%0], {%1,%2};" ::"r"(o), "r"(__float_as_uint(x[i].x)), "r"(__float_as_uint(x[i].y)) : "memory");
-                asm volatile("st.shared.v2.b32 [%0], {%1,%2};" ::"r"(o + 4096u), "r"(__float_as_uint(x[i].z)), "r"(__float_as_uint(x[i].w)) : "memory");
-              }
-        }
-      };
-      if (trace & 4) {
-      } else if (nlb == 1) convert(std::integral_constant<int, 1>{});
-      else if (nlb == 2) convert(std::integral_constant<int, 2>{});
-      else convert(std::integral_constant<int, 3>{});
-      // fp32 partial sums of at most 16 stages x 8 rows, then fp64 (fp64 conversions and adds are slow
-      // enough on B200 to double the conversion time when done per stage: measured)
-      if (stat_owner && (++pending == 16 || it + 2 >= my_chunks)) {
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          ds[j] += (double)fs[j]; dq[j] += (double)fq[j];
-          fs[j] = 0.f; fq[j] = 0.f;
-        }
-        pending = 0;
-      }
-      if (lane == 0 && rg == 0) DR4G_TRACE2(3);
-      // the MMA that reads this stage is issued by the leader CTA but reads THIS CTA's shared memory:
-      // make the writes visible to the async proxy (the fence also waits for the stores queued behind
-      // the MMA's operand reads), then arrive (release at cluster scope) on the leader's barrier
-      ptx::fence_proxy_async_smem();
-      __syncwarp();
-      if (lane == 0) {
-        if (trace & 8) ptx::mbar_arrive_cluster(conv_leader + (uint32_t)s * 8u);
-        else ptx::mbar_arrive_cluster_relaxed(conv_leader + (uint32_t)s * 8u);
-      }
-      if (lane == 0 && rg == 0) DR4G_TRACE2(4);
-      if (++s == nstages) { s = 0; ph ^= 1u; }
-    }
-    if (stat_owner) {
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        atomicAdd(&osum[col0[0] + j], ds[j]);
-        atomicAdd(&osq[col0[0] + j], dq[j]);
-      }
-    }
+    ConvArgs ca;
+    ca.smem_base = smem_base; ca.op_base = op_base; ca.land_stride = land_stride; ca.half_bytes = half_bytes;
+    ca.bar_full = ptx::smem_u32(&bar_full[0]); ca.bar_conv_leader = ptx::mapa(ptx::smem_u32(&bar_conv[0]), 0);
+    ca.bar_empty = ptx::smem_u32(&bar_empty[0]); ca.bar_lfree = ptx::smem_u32(&bar_lfree[0]);
+    ca.NL = NL; ca.NO = NO; ca.my_chunks = my_chunks; ca.ncl = job.ncl; ca.split = split; ca.kt = kt; ca.trace = trace;
+    ca.n = n;
+    const int grp = warp >> 2;
+    if (nlb == 1) {
+      if (job.stats) converter_loop<BF16, 1, true>(ca, grp, sh, col_ok, col0[0], osum, osq);
+      else converter_loop<BF16, 1, false>(ca, grp, sh, col_ok, col0[0], osum, osq);
+    } else if (nlb == 2) converter_loop<BF16, 2, false>(ca, grp, sh, col_ok, col0[0], osum, osq);
+    else converter_loop<BF16, 3, false>(ca, grp, sh, col_ok, col0[0], osum, osq);
   } else {
     // ================================================================ epilogue: TMEM -> this CTA's slab
     // slab [chunk][accumulator lane m (128)][256 columns] fp32, L2 resident.  First window: store;
@@ -776,7 +809,9 @@ void launch_gram_pair(Ctx& c, const float* dX, long long n, int d, const float* 
       CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) fail("cuTensorMapEncodeTiled (3-D) failed (%d) for n=%lld d=%d", (int)r, n, d);
 
-  const int smem = kRingBytes + 1024;
+  const int smem = (bf16 ? kRingBytesBf16 : kRingBytes) + 1024;
+  static const int op_env = getenv("DR4G_OP_STAGES") ? atoi(getenv("DR4G_OP_STAGES")) : 2;   // operand ring of the bf16x3 kernel (even)
+  const int op_stages = op_env >= 4 ? 4 : 2;
   static PerDeviceMax smem_set[2];
   if (smem_set[bf16 ? 1 : 0].need(c.device, (size_t)smem)) {
     if (bf16) DR4G_CUDA(cudaFuncSetAttribute(gram_pair_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
@@ -788,7 +823,7 @@ void launch_gram_pair(Ctx& c, const float* dX, long long n, int d, const float* 
   const int clusters = tab.job[tab.njobs - 1].cl_begin + tab.job[tab.njobs - 1].ncl;
   float* slab = static_cast<float*>(workspace);
   // cross-job pacing: progress counters behind the slabs; a job may run ahead of the slowest one by ~24 MB of rows
-  static const int pace_mb = getenv("DR4G_PACE_MB") ? atoi(getenv("DR4G_PACE_MB")) : 24;
+  static const int pace_mb = getenv("DR4G_PACE_MB") ? atoi(getenv("DR4G_PACE_MB")) : 0;
   int* prog = nullptr;
   int pace_rows = 0;
   if (pace_mb > 0 && tab.njobs > 1) {
@@ -810,9 +845,9 @@ void launch_gram_pair(Ctx& c, const float* dX, long long n, int d, const float* 
   lc.attrs = at;
   lc.numAttrs = 1;
   if (bf16)
-    DR4G_CUDA(cudaLaunchKernelEx(&lc, gram_pair_kernel<true>, tmap, tab, n, d, dshift, slab, dsum, dsumsq, flush_rows, trace, prog, pace_rows));
+    DR4G_CUDA(cudaLaunchKernelEx(&lc, gram_pair_kernel<true>, tmap, tab, n, d, dshift, slab, dsum, dsumsq, flush_rows, trace, prog, pace_rows, op_stages));
   else
-    DR4G_CUDA(cudaLaunchKernelEx(&lc, gram_pair_kernel<false>, tmap, tab, n, d, dshift, slab, dsum, dsumsq, flush_rows, trace, prog, pace_rows));
+    DR4G_CUDA(cudaLaunchKernelEx(&lc, gram_pair_kernel<false>, tmap, tab, n, d, dshift, slab, dsum, dsumsq, flush_rows, trace, prog, pace_rows, op_stages));
   c.last_gram_kernel = bf16 ? 3 : 2;
   c.launches++;
   if (trace & 1) {
@@ -820,10 +855,11 @@ void launch_gram_pair(Ctx& c, const float* dX, long long n, int d, const float* 
     DR4G_CUDA(cudaStreamSynchronize(c.stream));
     DR4G_CUDA(cudaMemcpyFromSymbol(h, g_trace2, sizeof(h)));
     fprintf(stderr, "gram_pair trace (CTA 0, clocks relative to chunk 0 'stage free'; n=%lld d=%d)\n", n, d);
-    fprintf(stderr, "  it  tma_free tma_issued  landed converted  arrived  mma_ready mma_issued\n");
+    fprintf(stderr, (trace & 16) ? "  it  alu_done  op_free    landed converted  arrived  mma_ready mma_issued  loop_top\n"
+                                 : "  it  tma_free tma_issued  landed converted  arrived  mma_ready mma_issued  loop_top\n");
     for (int it = 0; it < kTraceIts; ++it) {
       fprintf(stderr, "%4d", it);
-      for (int e = 0; e < 7; ++e) fprintf(stderr, " %9lld", h[it * 8 + e] ? h[it * 8 + e] - h[0] : -1ll);
+      for (int e = 0; e < 8; ++e) fprintf(stderr, " %9lld", h[it * 8 + e] ? h[it * 8 + e] - h[0] : -1ll);
       fprintf(stderr, "\n");
     }
   }
