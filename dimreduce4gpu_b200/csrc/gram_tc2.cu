@@ -688,8 +688,8 @@ namespace {
 // 24 + 24 + 24 + 6 x 8 = 120 KB (tensor time 256 / 384 / 768 cycles): 20 : 36 : 60.  DR4G_OCOST_BF16 / DR4G_OCOST2_BF16 override.
 int job_cost(const PJob& j, bool bf16) {
   static const int ocost = getenv("DR4G_OCOST") ? atoi(getenv("DR4G_OCOST")) : 40;  // 26..42 swept on B200: 40 is best at d = 512 and 1024
-  static const int ocost_b = getenv("DR4G_OCOST_BF16") ? atoi(getenv("DR4G_OCOST_BF16")) : 36;
-  static const int ocost2_b = getenv("DR4G_OCOST2_BF16") ? atoi(getenv("DR4G_OCOST2_BF16")) : 60;
+  static const int ocost_b = getenv("DR4G_OCOST_BF16") ? atoi(getenv("DR4G_OCOST_BF16")) : 40;
+  static const int ocost2_b = getenv("DR4G_OCOST2_BF16") ? atoi(getenv("DR4G_OCOST2_BF16")) : 56;
   if (j.diag) return 20;
   if (bf16) return j.nchunk == 2 ? ocost2_b : ocost_b;
   return ocost * j.nchunk;
@@ -810,7 +810,7 @@ void launch_gram_pair(Ctx& c, const float* dX, long long n, int d, const float* 
   if (r != CUDA_SUCCESS) fail("cuTensorMapEncodeTiled (3-D) failed (%d) for n=%lld d=%d", (int)r, n, d);
 
   const int smem = (bf16 ? kRingBytesBf16 : kRingBytes) + 1024;
-  static const int op_env = getenv("DR4G_OP_STAGES") ? atoi(getenv("DR4G_OP_STAGES")) : 2;   // operand ring of the bf16x3 kernel (even)
+  static const int op_env = getenv("DR4G_OP_STAGES") ? atoi(getenv("DR4G_OP_STAGES")) : 4;   // operand ring of the bf16x3 kernel (even)
   const int op_stages = op_env >= 4 ? 4 : 2;
   static PerDeviceMax smem_set[2];
   if (smem_set[bf16 ? 1 : 0].need(c.device, (size_t)smem)) {
