@@ -489,7 +489,10 @@ def run_also(torch, dist, ctx, keys, rank, world, dev, peaks) -> dict:
             tb = wl["n"] * (wl["d"] + wl["k"]) * X.element_size()
             entry["transform"] = dict(ms=tms, rows_per_s=wl["n"] / (tms * 1e-3), achieved_gbs=tb / (tms * 1e-3) / 1e9,
                                       hbm_frac=tb / (tms * 1e-3) / 1e9 / peaks["hbm_gbs"],
-                                      algorithmic_bytes=tb)
+                                      algorithmic_bytes=tb, kernel=ctx.last_proj_path)
+            if heavy:   # fp64: AI ~ k/4 flop/B puts the projection on the fp64 pipe, not on HBM
+                tf = 2.0 * wl["n"] * wl["d"] * wl["k"] / (tms * 1e-3) / 1e12
+                entry["transform"].update(bound="tensor (FP64 DMMA)", achieved_tflops=tf, frac=tf / peaks["fp64_tflops"])
             res[key] = entry
             del X, Z, r, o
         except Exception as e:  # noqa: BLE001 - a secondary workload must not take the headline line down

@@ -90,7 +90,7 @@ struct Ctx {
   void* proj_buf = nullptr;
   size_t proj_cap = 0;
   int proj_path = 0;          // 0 auto (tcgen05 where eligible), 1 CUDA-core kernels only
-  int last_proj_path = 0;     // 1 CUDA cores, 2 tcgen05
+  int last_proj_path = 0;     // 1 CUDA cores, 2 tcgen05, 3 fp64 DMMA
   // tensor-map encoder (driver entry point fetched lazily)
   void* encode_tiled = nullptr;
 };
@@ -109,6 +109,10 @@ void launch_mirror_upper(Ctx& c, double* dG, int d);
 
 // Gram, fp64 input (gram_f64.cu): 128 x 128 DMMA tiles, cp.async ring, persistent schedule, fixed summation order.
 // Writes the upper block triangle (by 128) of dG; mirror_upper() completes it.
+// K7, fp64 input (project_f64.cu): 128-row tiles on the DMMA pipe, k <= 128
+bool project_f64_eligible(const Ctx& c, const double* dX, long long n, int d, int k, const double* dQ);
+void launch_project_f64(Ctx& c, const double* dX, long long n, int d, int k, const double* dQ, const double* dmean,
+                        const double* dw, double* dZ, double* dU);
 bool gram_f64_eligible(const Ctx& c, const double* dX, long long n, int d);
 size_t gram_f64_workspace_bytes(const Ctx& c, long long n, int d);
 void launch_gram_f64(Ctx& c, const double* dX, long long n, int d, const double* dshift, double* dG, void* workspace);

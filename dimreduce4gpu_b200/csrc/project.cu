@@ -275,6 +275,13 @@ void launch_project(Ctx& c, const T* dX, long long n, int d, int k, const T* dQ,
       return;
     }
   }
+  if constexpr (sizeof(T) == 8) {
+    if (c.proj_path != 1 && project_f64_eligible(c, dX, n, d, k, dQ)) {
+      launch_project_f64(c, dX, n, d, k, dQ, dmean, dw, dZ, dU);
+      c.last_proj_path = 3;
+      return;
+    }
+  }
   const long long blocks = (n + RT - 1) / RT;
   rowgemm_kernel<T><<<(unsigned)blocks, 256, 0, c.stream>>>(dX, n, d, d, dmean, dQ, (long long)d, 1LL, k, nullptr,
                                                             dw, dZ, (dU && dw) ? dU : nullptr, k);

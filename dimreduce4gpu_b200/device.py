@@ -348,7 +348,7 @@ class DeviceContext:
 
     @property
     def last_proj_path(self) -> str:
-        return {0: "none", 1: "cuda_cores", 2: "tcgen05"}[int(self._lib.dr4g_last_proj_path(self._h))]
+        return {0: "none", 1: "cuda_cores", 2: "tcgen05", 3: "dmma_f64"}[int(self._lib.dr4g_last_proj_path(self._h))]
 
     @property
     def launch_count(self) -> int:
