@@ -307,10 +307,13 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
   __shared__ __align__(8) uint64_t bar_full[kMaxStages], bar_conv[kMaxStages], bar_empty[kMaxStages], bar_lfree[kMaxStages];
   __shared__ __align__(8) uint64_t bar_acc_full[2], bar_acc_empty[2];
   __shared__ uint32_t tmem_base_slot;
+  __shared__ volatile int pace_hold, pace_it;   // cross-job pacing: written by the pair's monitor / by producer 0
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
+    pace_hold = 0;
+    pace_it = 0;
     for (int s = 0; s < kMaxStages; ++s) {
       ptx::mbar_init(ptx::smem_u32(&bar_full[s]), 1);                 // the stage's owner (one producer) + its TMA bytes
       ptx::mbar_init(ptx::smem_u32(&bar_conv[s]), kConvWarps);       // a group of 4 warps per CTA; leader CTA only
@@ -345,9 +348,13 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
     // Cross-job pacing.  At d > 256 every column block is read by several jobs (d = 512: two, d = 1024: four).  The jobs
     // are balanced to finish together but drift apart by a few per cent of n, far more than the L2 holds, so each job
     // pulled its own copy from HBM: ncu showed dram reads of 2.1x (d = 512) and 3.4x (d = 1024) the matrix, 3.5 TB/s.
-    // Every cluster's leader publishes the rows it has issued (prog[job], a relaxed global add per stage) and, every 8
-    // stages, a producer that is more than `pace_rows` ahead of the slowest unfinished job waits (bounded: after ~60 us
-    // without progress the CTA stops pacing, so a partly resident grid cannot hang) - the followers then hit in L2.
+    // A first version had the producers themselves publish their progress (a global RED per stage) and poll the other
+    // jobs' counters every 8 stages: the polling round trips stalled the TMA issue and the pass got slower whatever
+    // the window (5.6 against 4.6 ms at d = 512).  Now the otherwise idle MMA warp of the pair's second CTA is the
+    // MONITOR: every ~1 us it adds the stages producer 0 has issued to prog[job], reads the other jobs' counters and
+    // raises `pace_hold` in both CTAs while this job is more than `pace_rows` ahead of the slowest one; a producer only
+    // reads that shared-memory flag.  The monitor gives up when the slowest job has not moved for ~100 polls (a partly
+    // resident grid cannot hang).
     if (ptx::elect_one()) {
       const int p = warp - kConvWarps;
       ptx::prefetch_tmap(&tmap);
@@ -358,26 +365,15 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
       const int np = NL % 3 == 0 ? 3 : (NL % 2 == 0 ? 2 : 1);
       int s = 0, owner = 0;
       uint32_t ph = 0;
-      bool pacing = prog != nullptr && table.njobs > 1;
+      const bool pacing = prog != nullptr && table.njobs > 1;
       int blk_of[3];
 #pragma unroll
       for (int lb = 0; lb < 3; ++lb) blk_of[lb] = lb < nlb ? job.bb[lb] + (int)rank : T;
       for (int it = 0; it < my_chunks; ++it) {
         if (owner == p) {
-          if (pacing && (it & 7) == 0 && it > 0) {
-            // rows this job has issued (all its clusters) against the slowest job that still has rows to issue
-            for (int tries = 0; tries < 48; ++tries) {
-              int mine = 0, slowest = 0x7fffffff;
-              for (int j = 0; j < table.njobs; ++j) {
-                int v;
-                asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(prog + j));
-                if (j == ji) mine = v;
-                if (v < slowest) slowest = v;
-              }
-              if (mine - slowest <= pace_rows) break;
-              if (tries == 47) pacing = false;   // nobody moved for ~60 us: not all jobs are resident, stop waiting for them
-              __nanosleep(1000);
-            }
+          if (pacing) {
+            while (pace_hold) __nanosleep(200);
+            if (p == 0) pace_it = it;
           }
           // 3xTF32: the stage (landing half converted in place + lo half) is free when its MMAs have completed.
           // bf16x3: the operands live in the other half, so the landing half is free as soon as the converters have
@@ -398,15 +394,50 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
               if (row >= n || blk_of[lb] >= T) continue;
               ptx::tma_load_3d(sx + (uint32_t)sl * kSlotBytes, &tmap, full, 0, (int)row, blk_of[lb] * 4);
             }
-          if (prog != nullptr && rank == 0)
-            asm volatile("red.relaxed.gpu.global.add.s32 [%0], %1;" ::"l"(prog + ji), "r"(kt) : "memory");
           if (p == 0 && !(trace & 16)) DR4G_TRACE2(1);
         }
         if (++owner == np) owner = 0;
         if (++s == NL) { s = 0; ph ^= 1u; owner = 0; }
       }
+      if (pacing && p == 0) pace_it = my_chunks;   // tells the monitor that this pair has issued everything
     }
   } else if (warp == kMmaWarp) {
+    if (rank == 1 && prog != nullptr && table.njobs > 1 && ptx::elect_one()) {
+      // ============================================================== pacing monitor (second CTA of the pair)
+      const uint32_t hold_here = ptx::smem_u32(const_cast<int*>(&pace_hold));
+      const uint32_t hold_leader = ptx::mapa(hold_here, 0);
+      int last = 0, held = 0, slow_prev = -1, same = 0;
+      bool on = true;
+      for (;;) {
+        const int cur = pace_it;
+        if (cur != last) {
+          asm volatile("red.relaxed.gpu.global.add.s32 [%0], %1;" ::"l"(prog + ji), "r"((cur - last) * kt) : "memory");
+          last = cur;
+        }
+        if (cur >= my_chunks) break;
+        int mine = 0, slowest = 0x7fffffff;
+        for (int j = 0; j < table.njobs; ++j) {
+          int v;
+          asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(prog + j));
+          if (j == ji) mine = v;
+          if (v < slowest) slowest = v;
+        }
+        same = slowest == slow_prev ? same + 1 : 0;
+        slow_prev = slowest;
+        if (same > 100) on = false;               // the slowest job is not running: stop waiting for it
+        const int want = (on && mine - slowest > pace_rows) ? 1 : 0;
+        if (want != held) {
+          held = want;
+          asm volatile("st.shared::cluster.u32 [%0], %1;" ::"r"(hold_leader), "r"(want) : "memory");
+          pace_hold = want;
+        }
+        __nanosleep(1000);
+      }
+      if (held) {
+        asm volatile("st.shared::cluster.u32 [%0], %1;" ::"r"(hold_leader), "r"(0) : "memory");
+        pace_hold = 0;
+      }
+    }
     // ================================================================ MMA issuer (leader CTA, one lane)
     if (rank == 0 && ptx::elect_one()) {
       // One thread feeds the tensor pipe: no divisions, no constant-bank indexing inside the loop
@@ -822,8 +853,9 @@ void launch_gram_pair(Ctx& c, const float* dX, long long n, int d, const float* 
   const int flush_rows = c.flush_rows > 0 ? c.flush_rows : 1024;
   const int clusters = tab.job[tab.njobs - 1].cl_begin + tab.job[tab.njobs - 1].ncl;
   float* slab = static_cast<float*>(workspace);
-  // cross-job pacing: progress counters behind the slabs; a job may run ahead of the slowest one by ~24 MB of rows
-  static const int pace_mb = getenv("DR4G_PACE_MB") ? atoi(getenv("DR4G_PACE_MB")) : 0;
+  // cross-job pacing: progress counters behind the slabs; a job may run ahead of the slowest one by ~8 MB of rows (measured:
+  // dram reads 1.9x -> 1.55x of the matrix at d = 512, 3.3x -> 1.8x at d = 1024, 8.2 -> 7.7 ms there; DR4G_PACE_MB=0 switches it off)
+  static const int pace_mb = getenv("DR4G_PACE_MB") ? atoi(getenv("DR4G_PACE_MB")) : 8;
   int* prog = nullptr;
   int pace_rows = 0;
   if (pace_mb > 0 && tab.njobs > 1) {
