@@ -624,10 +624,18 @@ bisect_kernel(const double* __restrict__ diag, const double* __restrict__ off, i
 }
 
 // ---------------------------------------------------------------- T3: eigenvectors by inverse iteration
-// One CTA per cluster of close eigenvalues (gap < 1e-3 ||T||, LAPACK dstein's criterion): the CTA of
-// the first member computes the cluster's vectors one after the other, re-orthogonalising against
-// the earlier ones inside every iteration.  Z: k x d (rows), unit vectors of T.
+// Two tiers of closeness (LAPACK dstein has one: gap < 1e-3 ||T|| -> sequential modified Gram-Schmidt):
+//   * TIGHT cluster, gap <= 1e-7 ||T|| (degenerate or nearly so): the CTA of the first member computes the cluster's
+//     vectors one after the other, re-orthogonalising against the earlier ones inside every iteration, as dstein does.
+//   * LOOSE cluster, 1e-7 ||T|| < gap <= 1e-3 ||T||: every member (every tight sub-cluster) gets its own CTA.  Their
+//     residuals are ~eps ||T||, so two of these vectors are orthogonal to ~2 eps ||T|| / gap <= 2e-9 already; one
+//     classical Gram-Schmidt step against the ORIGINAL earlier members (invit_orth_kernel, all members in parallel)
+//     leaves errors of second order (the p = i term of z_i' . z_j' cancels E_ij exactly).  A PCA spectrum with thousands
+//     of samples per feature is one big loose cluster (config 5: 100 eigenvalues 3e-4 ||T|| apart): processed
+//     sequentially the stage took 180 ms at d = 4096.
+// Z: k x d (rows), unit vectors of T.
 constexpr int kInvThreads = 128;
+constexpr double kTightGap = 1e-7, kLooseGap = 1e-3;
 
 __device__ __forceinline__ double inv_block_sum(double v, double* red) {
 #pragma unroll
@@ -653,7 +661,7 @@ invit_kernel(const double* __restrict__ diag, const double* __restrict__ off, in
              double* __restrict__ Z) {
   const int j0 = blockIdx.x;
   const double tnorm = info[0];
-  const double ortol = 1e-3 * tnorm;
+  const double ortol = kTightGap * tnorm;
   if (j0 > 0 && fabs(lam[j0 - 1] - lam[j0]) <= ortol) return;  // not the head of a cluster
   int j1 = j0 + 1;
   while (j1 < k && fabs(lam[j1 - 1] - lam[j1]) <= ortol) ++j1;
@@ -791,6 +799,52 @@ invit_kernel(const double* __restrict__ diag, const double* __restrict__ off, in
     __threadfence_block();
     __syncthreads();
   }
+}
+
+// Second half of T3: one classical Gram-Schmidt step inside every LOOSE cluster.  CTA j: z_j' = z_j - sum_p (z_p . z_j) z_p
+// over the earlier members p of its loose cluster (original vectors, read from Zin), normalised, written to Zout; the
+// other vectors are copied.  grid = k, block = 256.
+__global__ void __launch_bounds__(256)
+invit_orth_kernel(const double* __restrict__ lam, const double* __restrict__ info, int d, int k,
+                  const double* __restrict__ Zin, double* __restrict__ Zout) {
+  extern __shared__ double io_sm[];
+  double* coef = io_sm;                 // k coefficients
+  __shared__ double red[8];
+  const int j = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const double ltol = kLooseGap * info[0];
+  int L = j;
+  while (L > 0 && fabs(lam[L - 1] - lam[L]) <= ltol) --L;
+  const double* zj = Zin + (size_t)j * d;
+  if (L == j) {
+    for (int i = tid; i < d; i += 256) Zout[(size_t)j * d + i] = zj[i];
+    return;
+  }
+  // dots: one warp per earlier member
+  for (int p = L + warp; p < j; p += 8) {
+    const double* zp = Zin + (size_t)p * d;
+    double dot = 0.0;
+    for (int i = lane; i < d; i += 32) dot = fma(zp[i], zj[i], dot);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
+    if (lane == 0) coef[p - L] = dot;
+  }
+  __syncthreads();
+  double ss = 0.0;
+  for (int i = tid; i < d; i += 256) {
+    double z = zj[i];
+    for (int p = L; p < j; ++p) z = fma(-coef[p - L], Zin[(size_t)p * d + i], z);
+    Zout[(size_t)j * d + i] = z;
+    ss = fma(z, z, ss);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+  if (lane == 0) red[warp] = ss;
+  __syncthreads();
+  double t = 0.0;
+#pragma unroll
+  for (int w = 0; w < 8; ++w) t += red[w];
+  const double rn = t > 0.0 ? rsqrt(t) : 0.0;
+  for (int i = tid; i < d; i += 256) Zout[(size_t)j * d + i] *= rn;
 }
 
 // ---------------------------------------------------------------- T4: v = H_0 H_1 ... H_{d-3} z
@@ -1013,6 +1067,7 @@ size_t eigh_topk_workspace_bytes(int d, int k) {
          + 3 * tri_r256((size_t)d * 8)    // diag, off, tau
          + tri_r256((size_t)4 * d * 8)    // p' / published-row exchange
          + tri_r256((size_t)k * 8)        // lam
+         + tri_r256((size_t)k * d * 8)    // inverse-iteration vectors before the loose-cluster Gram-Schmidt step
          + 256 + 256;                     // info, ctrl
 }
 
@@ -1028,6 +1083,7 @@ void launch_eigh_topk(Ctx& c, double* dA, int d, int k, double* dW, double* dVt,
   double* info = reinterpret_cast<double*>(take(256));
   TriCtrl* ctrl = reinterpret_cast<TriCtrl*>(take(256));
   double* lam = reinterpret_cast<double*>(take((size_t)k * 8));
+  double* Zraw = reinterpret_cast<double*>(take((size_t)k * d * 8));
   DR4G_CUDA(cudaMemsetAsync(ctrl, 0, sizeof(TriCtrl), c.stream));
 
   // T1: d <= 512 runs inside one thread-block cluster (hardware barrier, DSMEM exchange); larger d uses
@@ -1105,13 +1161,14 @@ void launch_eigh_topk(Ctx& c, double* dA, int d, int k, double* dW, double* dVt,
   static PerDeviceMax iv_smem_set;
   if (iv_smem > 48 * 1024 && iv_smem_set.need(c.device, iv_smem))
     DR4G_CUDA(cudaFuncSetAttribute(invit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)iv_smem));
-  invit_kernel<<<k, kInvThreads, iv_smem, c.stream>>>(diag, off, d, k, lam, info, dW, dVt);
+  invit_kernel<<<k, kInvThreads, iv_smem, c.stream>>>(diag, off, d, k, lam, info, dW, Zraw);
+  invit_orth_kernel<<<k, 256, (size_t)k * sizeof(double), c.stream>>>(lam, info, d, k, Zraw, dVt);
   // T4
   const size_t bt_smem = (size_t)d * sizeof(double);
   if (d <= 256) backtransform_pair_kernel<8><<<(k + 3) / 4, 128, 0, c.stream>>>(Vh, tau, d, k, dVt);
   else if (d <= 512) backtransform_warp_kernel<16><<<(k + 3) / 4, 128, 0, c.stream>>>(Vh, tau, d, k, dVt);
   else backtransform_kernel<<<k, 256, bt_smem, c.stream>>>(Vh, tau, d, k, dVt);
-  c.launches += 4;
+  c.launches += 5;
   DR4G_CUDA(cudaGetLastError());
 }
 
