@@ -889,9 +889,11 @@ void launch_gram_pair(Ctx& c, const float* dX, long long n, int d, const float* 
     fprintf(stderr, "gram_pair trace (CTA 0, clocks relative to chunk 0 'stage free'; n=%lld d=%d)\n", n, d);
     fprintf(stderr, (trace & 16) ? "  it  alu_done  op_free    landed converted  arrived  mma_ready mma_issued  loop_top\n"
                                  : "  it  tma_free tma_issued  landed converted  arrived  mma_ready mma_issued  loop_top\n");
+    long long base = 0;
+    for (int e = 0; e < kTraceIts * 8; ++e) if (h[e] && (base == 0 || h[e] < base)) base = h[e];
     for (int it = 0; it < kTraceIts; ++it) {
       fprintf(stderr, "%4d", it);
-      for (int e = 0; e < 8; ++e) fprintf(stderr, " %9lld", h[it * 8 + e] ? h[it * 8 + e] - h[0] : -1ll);
+      for (int e = 0; e < 8; ++e) fprintf(stderr, " %9lld", h[it * 8 + e] ? h[it * 8 + e] - base : -1ll);
       fprintf(stderr, "\n");
     }
   }
