@@ -284,7 +284,7 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
   // converters' store to the end of its MMAs (~1500), and the pass ran at the pace of the landing ring (6 x 16 KB in
   // flight per SM against that latency: ~1000 cycles per stage, tensor pipe 35 % active, smem and HBM under 50 %).  So
   // nearly all of the shared memory is landing ring (12 x 16 KB or 6 x 24 KB in flight) and the operand ring is short.
-  const int NO = BF16 ? op_stages : ((int)(kRingBytes / stage_bytes) < kMaxStagesTf32 ? (int)(kRingBytes / stage_bytes) : kMaxStagesTf32);
+  const int NO = BF16 ? ((int)(kRingBytesBf16 / half_bytes) - op_stages >= 4 ? op_stages : 4) : ((int)(kRingBytes / stage_bytes) < kMaxStagesTf32 ? (int)(kRingBytes / stage_bytes) : kMaxStagesTf32);
   int nl_ = BF16 ? (((int)(kRingBytesBf16 / half_bytes) - NO) & ~1) : NO;   // even: a converter group always meets the same slots
   const int NL = nl_ > kMaxStages ? kMaxStages : nl_;
   const uint32_t land_stride = BF16 ? half_bytes : stage_bytes;
@@ -842,7 +842,7 @@ void launch_gram_pair(Ctx& c, const float* dX, long long n, int d, const float* 
 
   const int smem = (bf16 ? kRingBytesBf16 : kRingBytes) + 1024;
   static const int op_env = getenv("DR4G_OP_STAGES") ? atoi(getenv("DR4G_OP_STAGES")) : 4;   // operand ring of the bf16x3 kernel (even)
-  const int op_stages = op_env >= 4 ? 4 : 2;
+  const int op_stages = op_env >= 8 ? 8 : (op_env >= 6 ? 6 : (op_env >= 4 ? 4 : 2));
   static PerDeviceMax smem_set[2];
   if (smem_set[bf16 ? 1 : 0].need(c.device, (size_t)smem)) {
     if (bf16) DR4G_CUDA(cudaFuncSetAttribute(gram_pair_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));

@@ -14,6 +14,9 @@ shapes = sys.argv[3] if len(sys.argv) > 3 else "1000000,256;4194304,512;2097152,
 ctx = pkg.DeviceContext(0)
 ctx.set_option("gram_path", 2)
 ctx.set_option("gram_split", split)
+import os
+if os.environ.get("FLUSH_ROWS"):
+    ctx.set_option("flush_rows", int(os.environ["FLUSH_ROWS"]))
 for spec in shapes.split(";"):
     n, d = map(int, spec.split(","))
     g = torch.Generator(device="cuda").manual_seed(n * 7 + d)
