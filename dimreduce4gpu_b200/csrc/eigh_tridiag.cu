@@ -183,6 +183,20 @@ tridiag_kernel(double* __restrict__ A, int d, double* __restrict__ diag, double*
       if (!kRowsInSmem) {
         // rows in L2 / HBM (d > ~1000): four independent loads in flight per lane - the one-load-per-iteration loop
         // paid the full memory latency 128 times per row at d = 4096 (100 us per column, measured)
+        // (round 2: sixteen per lane - with four, 8 warps x 1 KB in flight per SM is ~1.2 TB/s chip-wide at ~1 us of L2
+        // latency, and the sweep of a 45 MB trailing matrix took 32 us)
+        for (; c + 32 * 15 < d; c += 32 * 16) {
+          double a[16];
+#pragma unroll
+          for (int u = 0; u < 16; ++u) a[u] = __ldcg(&Ai[c + 32 * u]);
+#pragma unroll
+          for (int u = 0; u < 16; ++u) {
+            a[u] = a[u] - vi * w[c + 32 * u] - wi * v[c + 32 * u];
+            __stcg(&Ai[c + 32 * u], a[u]);
+            if (pub) __stcg(&pub[c + 32 * u], a[u]);
+            dot = fma(a[u], vn[c + 32 * u], dot);
+          }
+        }
         for (; c + 96 < d; c += 128) {
           double a[4];
 #pragma unroll

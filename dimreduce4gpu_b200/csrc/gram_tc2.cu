@@ -89,8 +89,10 @@ struct PJobTable {
 
 constexpr int kTraceIts = 96;
 __device__ long long g_trace2[kTraceIts * 8];
+__device__ unsigned long long g_cta_time[2 * 160];   // DR4G_GRAM_TRACE bit 32: %globaltimer at the start and end of every CTA
 #define DR4G_TRACE2(ev) \
-  do { if ((trace & 1) && (int)blockIdx.x == (trace >> 8) && it < kTraceIts) g_trace2[it * 8 + (ev)] = clock64(); } while (0)
+  do { if ((trace & 1) && (int)blockIdx.x == ((trace >> 8) & 0xff) && it >= (trace >> 16) * 64 && it < (trace >> 16) * 64 + kTraceIts) \
+         g_trace2[(it - (trace >> 16) * 64) * 8 + (ev)] = clock64(); } while (0)
 
 __device__ __forceinline__ float clear13(float v) { return __uint_as_float(__float_as_uint(v) & 0xffffe000u); }
 
@@ -335,6 +337,11 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
   ptx::cluster_sync();   // the peer's barriers exist before anything arrives on them
   ptx::tc_fence_after_sync();
   const uint32_t tmem_base = tmem_base_slot;
+  if ((trace & 32) && threadIdx.x == 0 && blockIdx.x < 160) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    g_cta_time[2 * blockIdx.x] = t;
+  }
 
   if (warp >= kConvWarps && warp < kMmaWarp) {
     // ================================================================ TMA producers (each CTA its own blocks)
@@ -633,6 +640,11 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
   __syncthreads();
   ptx::cluster_sync();   // no CTA of the pair leaves while the other may still signal it or read its smem
   if (warp == kMmaWarp) ptx::tmem_dealloc_pair(tmem_base, kTmemCols);
+  if ((trace & 32) && threadIdx.x == 0 && blockIdx.x < 160) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    g_cta_time[2 * blockIdx.x + 1] = t;
+  }
 }
 
 // G (fp64, full symmetric) <- sum over a job's clusters of the slabs of CTA rank r, in a fixed
@@ -849,7 +861,7 @@ void launch_gram_pair(Ctx& c, const float* dX, long long n, int d, const float* 
     else DR4G_CUDA(cudaFuncSetAttribute(gram_pair_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   }
 
-  static const int trace = getenv("DR4G_GRAM_TRACE") ? atoi(getenv("DR4G_GRAM_TRACE")) : 0;  // bit 0 trace (CTA = value >> 8), 2 no MMA, 4 no conversion
+  static const int trace = getenv("DR4G_GRAM_TRACE") ? atoi(getenv("DR4G_GRAM_TRACE")) : 0;  // bit 0 trace (CTA = bits 8-15, first iteration = bits 16.. x 64), 2 no MMA, 4 no conversion, 16 converter stamps, 32 per-job end times
   const int flush_rows = c.flush_rows > 0 ? c.flush_rows : 1024;
   const int clusters = tab.job[tab.njobs - 1].cl_begin + tab.job[tab.njobs - 1].ncl;
   float* slab = static_cast<float*>(workspace);
@@ -882,6 +894,23 @@ void launch_gram_pair(Ctx& c, const float* dX, long long n, int d, const float* 
     DR4G_CUDA(cudaLaunchKernelEx(&lc, gram_pair_kernel<false>, tmap, tab, n, d, dshift, slab, dsum, dsumsq, flush_rows, trace, prog, pace_rows, op_stages));
   c.last_gram_kernel = bf16 ? 3 : 2;
   c.launches++;
+  if (trace & 32) {
+    static unsigned long long ht[2 * 160];
+    DR4G_CUDA(cudaStreamSynchronize(c.stream));
+    DR4G_CUDA(cudaMemcpyFromSymbol(ht, g_cta_time, sizeof(ht)));
+    unsigned long long t0 = ~0ull;
+    for (int b = 0; b < 2 * clusters; ++b) if (ht[2 * b] < t0) t0 = ht[2 * b];
+    fprintf(stderr, "gram_pair job times (us after the first CTA started; n=%lld d=%d)\n", n, d);
+    for (int j = 0; j < tab.njobs; ++j) {
+      double lo = 1e30, hi = 0, sum = 0;
+      for (int cl = tab.job[j].cl_begin; cl < tab.job[j].cl_begin + tab.job[j].ncl; ++cl) {
+        const double e = (double)(ht[2 * (2 * cl) + 1] - t0) * 1e-3;
+        lo = e < lo ? e : lo; hi = e > hi ? e : hi; sum += e;
+      }
+      fprintf(stderr, "  job %2d I=%d diag=%d chunks=%d clusters=%2d: end min %8.1f mean %8.1f max %8.1f\n", j, tab.job[j].I,
+              tab.job[j].diag, tab.job[j].nchunk, tab.job[j].ncl, lo, sum / tab.job[j].ncl, hi);
+    }
+  }
   if (trace & 1) {
     static long long h[kTraceIts * 8];
     DR4G_CUDA(cudaStreamSynchronize(c.stream));
