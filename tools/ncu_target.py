@@ -1,6 +1,7 @@
 #!/usr/bin/env python
 """Small deterministic target for ncu captures: `python tools/ncu_target.py gram N D [split]` runs the tcgen05 Gram 3 times,
-`python tools/ncu_target.py project N D K` the tcgen05 projection 3 times, `... gram64 N D` the fp64 DMMA Gram twice."""
+`python tools/ncu_target.py project N D K` the tcgen05 projection 3 times, `... gram64 N D` the fp64 DMMA Gram twice,
+`... project64 N D K` the fp64 DMMA projection 3 times."""
 import sys
 from pathlib import Path
 
@@ -12,7 +13,7 @@ import dimreduce4gpu_b200 as pkg  # noqa: E402
 what, n, d = sys.argv[1], int(sys.argv[2]), int(sys.argv[3])
 ctx = pkg.DeviceContext(0)
 g = torch.Generator(device="cuda").manual_seed(1)
-dt = torch.float64 if what == "gram64" else torch.float32
+dt = torch.float64 if what in ("gram64", "project64") else torch.float32
 X = torch.empty(n, d, device="cuda", dtype=dt)
 slab = max(1, (256 << 20) // (X.element_size() * d))
 for r0 in range(0, n, slab):
@@ -31,7 +32,7 @@ if what in ("gram", "gram64"):
     print(what, n, d, ctx.last_gram_path, float(G[0, 0]))
 else:
     k = int(sys.argv[4])
-    Q, _ = torch.linalg.qr(torch.randn(d, k, device="cuda", generator=g))
+    Q, _ = torch.linalg.qr(torch.randn(d, k, device="cuda", generator=g, dtype=dt))
     Q = Q.T.contiguous()
     for _ in range(3):
         Z = ctx.transform(X, Q, mean=shift)
