@@ -292,7 +292,10 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
   const uint32_t land_stride = BF16 ? half_bytes : stage_bytes;
   const uint32_t op_stride = land_stride;
   const long long n_chunks = (n + kt - 1) / kt;
-  if (split >= job.ncl || split >= n_chunks) return;    // both CTAs of a pair take the same branch
+  if (split >= job.ncl || split >= n_chunks) {          // both CTAs of a pair take the same branch
+    if (prog != nullptr && threadIdx.x == 0 && rank == 0) prog[cluster] = 0x7fffffff;   // pacing: nothing to wait for here
+    return;
+  }
   const int my_chunks = (int)((n_chunks - split + job.ncl - 1) / job.ncl);
   // Stages per flush window.  `flush_rows` is calibrated for three accumulating MMAs per 8 rows; P of a
   // diagonal job takes one (R, 2^-11 of P, is never flushed before the end), so its window is 4x longer.
@@ -358,10 +361,11 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
     // A first version had the producers themselves publish their progress (a global RED per stage) and poll the other
     // jobs' counters every 8 stages: the polling round trips stalled the TMA issue and the pass got slower whatever
     // the window (5.6 against 4.6 ms at d = 512).  Now the otherwise idle MMA warp of the pair's second CTA is the
-    // MONITOR: every ~1 us it adds the stages producer 0 has issued to prog[job], reads the other jobs' counters and
-    // raises `pace_hold` in both CTAs while this job is more than `pace_rows` ahead of the slowest one; a producer only
-    // reads that shared-memory flag.  The monitor gives up when the slowest job has not moved for ~100 polls (a partly
-    // resident grid cannot hang).
+    // MONITOR: every ~1 us it publishes the pair's row frontier (stages issued x rows per stage of its job) in prog[cluster],
+    // reads the frontiers of all clusters and raises `pace_hold` in both CTAs while this pair is more than `pace_rows`
+    // ahead of the slowest one; a producer only reads that shared-memory flag.  (Per JOB totals were not enough: over a
+    // long pass the clusters of one job drift apart as well, and at 2^24 rows the dram reads stayed at 1.93x.)  The
+    // monitor gives up when the slowest frontier has not moved for ~100 polls (a partly resident grid cannot hang).
     if (ptx::elect_one()) {
       const int p = warp - kConvWarps;
       ptx::prefetch_tmap(&tmap);
@@ -413,25 +417,24 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant
       // ============================================================== pacing monitor (second CTA of the pair)
       const uint32_t hold_here = ptx::smem_u32(const_cast<int*>(&pace_hold));
       const uint32_t hold_leader = ptx::mapa(hold_here, 0);
-      int last = 0, held = 0, slow_prev = -1, same = 0;
+      int held = 0, slow_prev = -1, same = 0;
       bool on = true;
+      const int nclus = (int)gridDim.x >> 1;
+      const int step_rows = job.ncl * kt;       // rows the job's frontier moves per stage of this cluster
       for (;;) {
         const int cur = pace_it;
-        if (cur != last) {
-          asm volatile("red.relaxed.gpu.global.add.s32 [%0], %1;" ::"l"(prog + ji), "r"((cur - last) * kt) : "memory");
-          last = cur;
-        }
+        const int mine = cur >= my_chunks ? 0x7fffffff : cur * step_rows;
+        asm volatile("st.relaxed.gpu.global.s32 [%0], %1;" ::"l"(prog + cluster), "r"(mine) : "memory");
         if (cur >= my_chunks) break;
-        int mine = 0, slowest = 0x7fffffff;
-        for (int j = 0; j < table.njobs; ++j) {
+        int slowest = 0x7fffffff;
+        for (int j = 0; j < nclus; ++j) {
           int v;
           asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(prog + j));
-          if (j == ji) mine = v;
           if (v < slowest) slowest = v;
         }
         same = slowest == slow_prev ? same + 1 : 0;
         slow_prev = slowest;
-        if (same > 100) on = false;               // the slowest job is not running: stop waiting for it
+        if (same > 100) on = false;               // the slowest cluster is not running: stop waiting for it
         const int want = (on && mine - slowest > pace_rows) ? 1 : 0;
         if (want != held) {
           held = want;
@@ -832,7 +835,7 @@ bool gram_pair_eligible(const Ctx& c, const float* dX, long long n, int d) {
 }
 
 size_t gram_pair_workspace_bytes(const Ctx& c, int d) {
-  return (size_t)(c.sm_count / 2) * 2 * kSlabFloats * sizeof(float) + 256;   // + the jobs' progress counters
+  return (size_t)(c.sm_count / 2) * 2 * kSlabFloats * sizeof(float) + 1024;   // + the clusters' row frontiers (pacing)
 }
 
 void launch_gram_pair(Ctx& c, const float* dX, long long n, int d, const float* dshift, double* dG, double* dsum,
@@ -865,14 +868,15 @@ void launch_gram_pair(Ctx& c, const float* dX, long long n, int d, const float* 
   const int flush_rows = c.flush_rows > 0 ? c.flush_rows : 1024;
   const int clusters = tab.job[tab.njobs - 1].cl_begin + tab.job[tab.njobs - 1].ncl;
   float* slab = static_cast<float*>(workspace);
-  // cross-job pacing: progress counters behind the slabs; a job may run ahead of the slowest one by ~8 MB of rows (measured:
-  // dram reads 1.9x -> 1.55x of the matrix at d = 512, 3.3x -> 1.8x at d = 1024, 8.2 -> 7.7 ms there; DR4G_PACE_MB=0 switches it off)
-  static const int pace_mb = getenv("DR4G_PACE_MB") ? atoi(getenv("DR4G_PACE_MB")) : 8;
+  // cross-job pacing: the clusters' row frontiers live behind the slabs; a pair may run ahead of the slowest one by 48 MB
+  // of rows (swept 8..96 MB on B200: 8 and 16 MB stall the pipelines - 2x the time at 2^23 x 512 -, 48..96 MB cost
+  // nothing; dram reads 2.0x -> 1.16x of the matrix at d = 512, 3.6x -> 1.3x at d = 1024; DR4G_PACE_MB=0 switches it off)
+  static const int pace_mb = getenv("DR4G_PACE_MB") ? atoi(getenv("DR4G_PACE_MB")) : 48;
   int* prog = nullptr;
   int pace_rows = 0;
   if (pace_mb > 0 && tab.njobs > 1) {
     prog = reinterpret_cast<int*>(reinterpret_cast<char*>(workspace) + (size_t)(c.sm_count / 2) * 2 * kSlabFloats * sizeof(float));
-    DR4G_CUDA(cudaMemsetAsync(prog, 0, 256, c.stream));
+    DR4G_CUDA(cudaMemsetAsync(prog, 0, 1024, c.stream));
     pace_rows = (int)(((long long)pace_mb << 20) / ((long long)d * 4));
     if (pace_rows < 1024) pace_rows = 1024;
   }
