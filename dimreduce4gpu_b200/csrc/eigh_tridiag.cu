@@ -1104,7 +1104,9 @@ void launch_eigh_topk(Ctx& c, double* dA, int d, int k, double* dW, double* dVt,
   // the cooperative grid with an atomic barrier, rows in shared memory whenever they fit
   if (d <= 512 && d % 2 == 0 && c.eig_solver != 2) {   // the cluster kernel sweeps rows in aligned column pairs
     static const int cs_env = getenv("DR4G_TRI_CS") ? atoi(getenv("DR4G_TRI_CS")) : 0;  // tuning hook
-    const int cs = cs_env > 0 ? cs_env : (d <= 128 ? 1 : 16);  // 16 beats 8 at d = 256 (1.16 vs 1.28 ms, measured)
+    // 16 beats 8 at d = 256 (1.16 vs 1.28 ms); 8 beats 1 for 32 < d <= 128 (whole eigensolve, round-2 sweep on B200:
+    // d = 64: 0.273 -> 0.210 ms, d = 100: 0.482 -> 0.303, d = 128 k = 32: 0.698 -> 0.415; 16 is no better than 8 there)
+    const int cs = cs_env > 0 ? cs_env : (d <= 32 ? 1 : (d <= 128 ? 8 : 16));
     const size_t smem = ((size_t)7 * d + (size_t)((d + cs - 1) / cs) * d) * sizeof(double);
     static PerDeviceMax smem_set, nonportable_set;
     if (smem > 48 * 1024 && smem_set.need(c.device, smem)) {
