@@ -21,6 +21,8 @@
 #include <mutex>
 #include <map>
 #include <memory>
+#include <thread>
+#include <vector>
 
 #include "common.cuh"
 #include "nccl_dyn.h"
@@ -108,8 +110,76 @@ struct StreamFit {
   }
 };
 
+// Pageable host memory <-> device through pinned bounce buffers.  cudaMemcpyAsync on a pageable pointer is staged by
+// the driver on ONE thread (~6-12 GB/s measured through the estimator's numpy arrays, against ~55 GB/s of the PCIe
+// link from pinned memory), and the reference's wrapper hands the library exactly such arrays
+// (dimreduce4gpu/truncated_svd.py:72-86).  Here a few host threads fill a ring of pinned 32 MB buffers while the
+// previous buffers are in flight on the copy engine.
+struct HostStage {
+  static constexpr int NB = 3;
+  static constexpr size_t kSub = (size_t)32 << 20;
+  void* buf[NB] = {nullptr, nullptr, nullptr};
+  cudaEvent_t done[NB] = {nullptr, nullptr, nullptr};
+  bool busy[NB] = {false, false, false};
+  int next = 0;
+  // a D2H sub-chunk that is in flight into buf[b] and still has to be copied out to the caller's array
+  struct Out { void* dst; size_t bytes; } out[NB] = {};
+  void ensure() {
+    for (int b = 0; b < NB; ++b) {
+      if (!buf[b]) DR4G_CUDA(cudaHostAlloc(&buf[b], kSub, cudaHostAllocDefault));
+      if (!done[b]) DR4G_CUDA(cudaEventCreateWithFlags(&done[b], cudaEventDisableTiming));
+    }
+  }
+  void release() {
+    for (int b = 0; b < NB; ++b) {
+      if (buf[b]) cudaFreeHost(buf[b]);
+      if (done[b]) cudaEventDestroy(done[b]);
+      buf[b] = nullptr; done[b] = nullptr; busy[b] = false; out[b] = Out{};
+    }
+  }
+};
+
+static int stage_threads() {
+  static const int n = [] {
+    const char* e = getenv("DR4G_STAGE_THREADS");
+    int v = e ? atoi(e) : 0;
+    if (v <= 0) {
+      const unsigned hc = std::thread::hardware_concurrency();
+      v = hc >= 16 ? 6 : (hc >= 8 ? 4 : 2);
+    }
+    return v > 16 ? 16 : v;
+  }();
+  return n;
+}
+
+static void parallel_memcpy(void* dst, const void* src, size_t bytes) {
+  const int nt = bytes < ((size_t)4 << 20) ? 1 : stage_threads();
+  if (nt <= 1) { std::memcpy(dst, src, bytes); return; }
+  const size_t per = ((bytes + nt - 1) / nt + 4095) & ~(size_t)4095;
+  std::vector<std::thread> th;
+  th.reserve(nt - 1);
+  for (int t = 1; t < nt; ++t) {
+    const size_t off = (size_t)t * per;
+    if (off >= bytes) break;
+    const size_t len = bytes - off < per ? bytes - off : per;
+    th.emplace_back([=] { std::memcpy(static_cast<char*>(dst) + off, static_cast<const char*>(src) + off, len); });
+  }
+  std::memcpy(dst, src, per < bytes ? per : bytes);
+  for (auto& t : th) t.join();
+}
+
+static bool is_pageable_host(const void* p) {
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+    cudaGetLastError();
+    return true;
+  }
+  return a.type == cudaMemoryTypeUnregistered;
+}
+
 struct CtxFull : Ctx {
   std::mutex mu;
+  HostStage stage;
   Arena io;  // device copies of inputs/outputs for the legacy host-pointer symbols
   StreamFit sf;
   cudaStream_t copy_stream = nullptr, out_stream = nullptr;  // H2D / D2H of the out-of-core legacy path
@@ -145,6 +215,7 @@ static void ctx_delete(CtxFull* c) {
   c->arena.release();
   c->io.release();
   if (c->proj_buf) cudaFree(c->proj_buf);
+  c->stage.release();
   c->sf.release();
   if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
   if (c->out_stream) cudaStreamDestroy(c->out_stream);
@@ -407,6 +478,60 @@ static void partial_fit_finalize_impl(CtxFull& c, int k, const params& p, T* dQ,
   fit_impl<T>(c, nullptr, sf.rows, sf.d, k, sf.center, p, dQ, dw, dev, devr, dmean, &sf, 2);
 }
 
+// Copy-outs of staged D2H sub-chunks that have completed (all of them when `all`), oldest first.
+static void stage_drain(HostStage& st, bool all) {
+  for (int i = 0; i < HostStage::NB; ++i) {
+    const int b = (st.next + i) % HostStage::NB;
+    if (!st.busy[b]) continue;
+    if (!all && i > 0) break;               // only the buffer that is about to be reused has to be free
+    DR4G_CUDA(cudaEventSynchronize(st.done[b]));
+    if (st.out[b].dst) parallel_memcpy(st.out[b].dst, st.buf[b], st.out[b].bytes);
+    st.out[b] = HostStage::Out{};
+    st.busy[b] = false;
+  }
+}
+
+// host -> device; pageable sources go through the pinned ring
+static void h2d_copy(CtxFull& c, void* dst, const void* src, size_t bytes, bool pageable, cudaStream_t s) {
+  if (!pageable) {
+    DR4G_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, s));
+    return;
+  }
+  HostStage& st = c.stage;
+  st.ensure();
+  for (size_t off = 0; off < bytes; off += HostStage::kSub) {
+    const size_t len = bytes - off < HostStage::kSub ? bytes - off : HostStage::kSub;
+    const int b = st.next;
+    stage_drain(st, false);
+    parallel_memcpy(st.buf[b], static_cast<const char*>(src) + off, len);
+    DR4G_CUDA(cudaMemcpyAsync(static_cast<char*>(dst) + off, st.buf[b], len, cudaMemcpyHostToDevice, s));
+    DR4G_CUDA(cudaEventRecord(st.done[b], s));
+    st.busy[b] = true;
+    st.next = (b + 1) % HostStage::NB;
+  }
+}
+
+// device -> host; pageable destinations go through the pinned ring (the copy-out of a sub-chunk happens when its buffer
+// comes round again, or in stage_drain(all) at the end)
+static void d2h_copy(CtxFull& c, void* dst, const void* src, size_t bytes, bool pageable, cudaStream_t s) {
+  if (!pageable) {
+    DR4G_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, s));
+    return;
+  }
+  HostStage& st = c.stage;
+  st.ensure();
+  for (size_t off = 0; off < bytes; off += HostStage::kSub) {
+    const size_t len = bytes - off < HostStage::kSub ? bytes - off : HostStage::kSub;
+    const int b = st.next;
+    stage_drain(st, false);
+    DR4G_CUDA(cudaMemcpyAsync(st.buf[b], static_cast<const char*>(src) + off, len, cudaMemcpyDeviceToHost, s));
+    DR4G_CUDA(cudaEventRecord(st.done[b], s));
+    st.busy[b] = true;
+    st.out[b] = HostStage::Out{static_cast<char*>(dst) + off, len};
+    st.next = (b + 1) % HostStage::NB;
+  }
+}
+
 // Two sweeps over a host-resident X in row chunks: [1] H2D (copy stream) overlapped with the chunk's Gram pass
 // (partial fit), then the eigensolve; [2] H2D again, projection, D2H of the scores (third stream), all three
 // overlapped through two chunk buffers.  Device footprint: 2 chunks of X and of the two score matrices.
@@ -417,6 +542,12 @@ static void legacy_pipelined(CtxFull& c, bool is_pca, bool resident, const T* X,
   // chunk i+1, the D2H of the scores of chunk i under the projection of chunk i+1); else two chunk buffers.
   if (!c.copy_stream) DR4G_CUDA(cudaStreamCreateWithFlags(&c.copy_stream, cudaStreamNonBlocking));
   if (!c.out_stream) DR4G_CUDA(cudaStreamCreateWithFlags(&c.out_stream, cudaStreamNonBlocking));
+  static const bool no_stage = getenv("DR4G_NO_STAGING") != nullptr;
+  // small arrays stay on the driver's own pageable path (pinning the ring costs ~10 ms per buffer, once per process)
+  const size_t stage_min = (size_t)16 << 20;
+  const bool x_pageable = !no_stage && (size_t)n * d * sizeof(T) >= stage_min && is_pageable_host(X);
+  const bool z_pageable = !no_stage && Xt && (size_t)n * k * sizeof(T) >= stage_min && is_pageable_host(Xt);
+  const bool u_pageable = !no_stage && U && (size_t)n * k * sizeof(T) >= stage_min && is_pageable_host(U);
   const size_t cx = (size_t)(resident ? n : 2 * chunk) * d * sizeof(T), cz = (size_t)(resident ? n : 2 * chunk) * k * sizeof(T);
   c.io.reserve(up256(cx) + 2 * up256(cz) + up256((size_t)k * d * sizeof(T)) + 3 * up256((size_t)k * sizeof(T)) +
                up256((size_t)d * sizeof(T)) + 8192);
@@ -464,7 +595,7 @@ static void legacy_pipelined(CtxFull& c, bool is_pca, bool resident, const T* X,
       const int b = (int)(i & 1);
       const long long r0 = i * chunk, rows = n - r0 < chunk ? n - r0 : chunk;
       if (!resident && i >= 2) DR4G_CUDA(cudaStreamWaitEvent(c.copy_stream, xfree[b], 0));
-      DR4G_CUDA(cudaMemcpyAsync(xbuf(r0, b), X + (size_t)r0 * d, (size_t)rows * d * sizeof(T), cudaMemcpyDefault, c.copy_stream));
+      h2d_copy(c, xbuf(r0, b), X + (size_t)r0 * d, (size_t)rows * d * sizeof(T), x_pageable, c.copy_stream);
       DR4G_CUDA(cudaEventRecord(loaded[b], c.copy_stream));
       DR4G_CUDA(cudaStreamWaitEvent(c.stream, loaded[b], 0));
       partial_fit_impl<T>(c, xbuf(r0, b), rows, d, is_pca ? 1 : 0);
@@ -477,7 +608,7 @@ static void legacy_pipelined(CtxFull& c, bool is_pca, bool resident, const T* X,
       const long long r0 = i * chunk, rows = n - r0 < chunk ? n - r0 : chunk;
       if (!resident) {
         DR4G_CUDA(cudaStreamWaitEvent(c.copy_stream, xfree[b], 0));   // last reader: the pass or the projection of chunk i-2
-        DR4G_CUDA(cudaMemcpyAsync(xbuf(r0, b), X + (size_t)r0 * d, (size_t)rows * d * sizeof(T), cudaMemcpyDefault, c.copy_stream));
+        h2d_copy(c, xbuf(r0, b), X + (size_t)r0 * d, (size_t)rows * d * sizeof(T), x_pageable, c.copy_stream);
         DR4G_CUDA(cudaEventRecord(loaded[b], c.copy_stream));
         DR4G_CUDA(cudaStreamWaitEvent(c.stream, loaded[b], 0));
         if (i >= 2) DR4G_CUDA(cudaStreamWaitEvent(c.stream, zfree[b], 0));
@@ -486,8 +617,8 @@ static void legacy_pipelined(CtxFull& c, bool is_pca, bool resident, const T* X,
       DR4G_CUDA(cudaEventRecord(projected[b], c.stream));
       if (!resident) DR4G_CUDA(cudaEventRecord(xfree[b], c.stream));
       DR4G_CUDA(cudaStreamWaitEvent(c.out_stream, projected[b], 0));
-      DR4G_CUDA(cudaMemcpyAsync(Xt + (size_t)r0 * k, zbuf(r0, b), (size_t)rows * k * sizeof(T), cudaMemcpyDefault, c.out_stream));
-      if (U) DR4G_CUDA(cudaMemcpyAsync(U + (size_t)r0 * k, ubuf(r0, b), (size_t)rows * k * sizeof(T), cudaMemcpyDefault, c.out_stream));
+      d2h_copy(c, Xt + (size_t)r0 * k, zbuf(r0, b), (size_t)rows * k * sizeof(T), z_pageable, c.out_stream);
+      if (U) d2h_copy(c, U + (size_t)r0 * k, ubuf(r0, b), (size_t)rows * k * sizeof(T), u_pageable, c.out_stream);
       if (!resident) DR4G_CUDA(cudaEventRecord(zfree[b], c.out_stream));
     }
     auto out = [&](T* dst, const T* src, size_t count) {
@@ -498,10 +629,12 @@ static void legacy_pipelined(CtxFull& c, bool is_pca, bool resident, const T* X,
     out(ev, dev, k);
     out(evr, devr, k);
     if (is_pca) out(mean, dmean, d);
+    stage_drain(c.stage, true);   // copy-outs of the last staged score sub-chunks
     DR4G_CUDA(cudaStreamSynchronize(c.copy_stream));
     DR4G_CUDA(cudaStreamSynchronize(c.stream));
     DR4G_CUDA(cudaStreamSynchronize(c.out_stream));
   } catch (...) {
+    for (int b = 0; b < HostStage::NB; ++b) { c.stage.busy[b] = false; c.stage.out[b] = HostStage::Out{}; }
     cudaStreamSynchronize(c.copy_stream);
     cudaStreamSynchronize(c.stream);
     cudaStreamSynchronize(c.out_stream);
