@@ -269,15 +269,32 @@ __device__ __forceinline__ void st_async_f64(double* local_ptr, uint64_t* local_
                : "memory");
 }
 
+// Bulk copy of `bytes` (multiple of 16, 16-byte aligned) from this CTA's shared memory into the shared memory of CTA
+// `cta`, counted on that CTA's mbarrier: one instruction per destination instead of one st.async per element.
+__device__ __forceinline__ void bulk_push(double* dst_local, const double* src_local, unsigned bytes, uint64_t* bar_local,
+                                          unsigned cta) {
+  const unsigned ls = static_cast<unsigned>(__cvta_generic_to_shared(src_local));
+  const unsigned ld = static_cast<unsigned>(__cvta_generic_to_shared(dst_local));
+  const unsigned lb = static_cast<unsigned>(__cvta_generic_to_shared(bar_local));
+  unsigned rd, rb;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(rd) : "r"(ld), "r"(cta));
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(rb) : "r"(lb), "r"(cta));
+  asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(rd),
+               "r"(ls), "r"(bytes), "r"(rb)
+               : "memory");
+}
+
 // Debug aid (DR4G_TRI_TRACE=1): clock64() of CTA 0, thread 0 at the phase boundaries of steps 100..103.
 __device__ long long g_tri_trace[4 * 16];
 #define TRI_TRACE(ev) \
   do { if ((trace & 1) && rank == 0 && tid == 0 && s >= 100 && s < 104) g_tri_trace[(s - 100) * 16 + (ev)] = clock64(); } while (0)
 
-// REG: d <= 256 in a 16-CTA cluster -> at most two own rows per warp; they stay in registers (lane: columns
-// 2 lane + 64 j) with a fixed row -> warp assignment, because the rows phase was bound by shared-memory bandwidth
-// (7 x 512 B per warp and 64 columns: 224 cycles per iteration for the CTA; only w, v, v' remain: 96).
-template <bool REG>
+// RW > 0: at most RW own rows per warp (d <= 128 RW in a 16-CTA cluster: RW = 2 up to d = 256, RW = 4 up to d = 512);
+// they stay in registers (lane: columns 2 lane + 64 j, j < 2 RW) with a fixed row -> warp assignment, because the rows
+// phase was bound by shared-memory bandwidth (per element of an own row: the row read and written back plus w, v, v'
+// = 40 B; with the rows in registers only w, v, v' remain and they are shared by the warp's RW rows).  d = 512, step
+// 100: rows phase 5900 of 11000 cycles with the rows in shared memory.  RW = 0: rows in shared memory.
+template <int RW>
 __global__ void __launch_bounds__(kTriThreads)
 tridiag_cluster_kernel(const double* __restrict__ A, int d, double* __restrict__ diag, double* __restrict__ off,
                        double* __restrict__ tau, double* __restrict__ Vh, double* __restrict__ xbuf, int trace) {
@@ -308,13 +325,15 @@ tridiag_cluster_kernel(const double* __restrict__ A, int d, double* __restrict__
     rowp[c] = A[c];            // row 0
     rowp[d + c] = 0.0;
   }
-  double2 rr[2][4];   // REG: slot q = warp + 8 k, columns 2 lane + 64 j
+  constexpr bool REG = RW > 0;
+  constexpr int NR = REG ? RW : 1, NJ = REG ? 2 * RW : 1;
+  double2 rr[NR][NJ];   // REG: slot q = warp + 8 k, columns 2 lane + 64 j
   if constexpr (REG) {
 #pragma unroll
-    for (int k = 0; k < 2; ++k) {
+    for (int k = 0; k < NR; ++k) {
       const int i = rank + cs * (warp + kTriWarps * k);
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
+      for (int j = 0; j < NJ; ++j) {
         const int c = 2 * lane + 64 * j;
         rr[k][j] = (i < d && c < d) ? *reinterpret_cast<const double2*>(A + (size_t)i * d + c) : make_double2(0.0, 0.0);
       }
@@ -341,7 +360,9 @@ tridiag_cluster_kernel(const double* __restrict__ A, int d, double* __restrict__
       __syncthreads();
     }
     const bool last = s == d - 2;      // nothing is exchanged after the last step
-    if (tid == 0 && !last) ptx::mbar_arrive_expect_tx(ptx::smem_u32(&xbar[(s + 1) & 1]), (uint32_t)(16 * (d - s - 1)));
+    // bytes of step s+1: p' entries s+1.. (8 each) and row s+1 from the even column (s+1) & ~1 (16-byte aligned bulk copy)
+    if (tid == 0 && !last)
+      ptx::mbar_arrive_expect_tx(ptx::smem_u32(&xbar[(s + 1) & 1]), (uint32_t)(8 * (d - s - 1) + 8 * (d - ((s + 1) & ~1))));
     // row s arrived in this CTA's shared memory before the last cluster barrier (an L2 round trip through a
     // published global copy cost ~1100 cycles per step here)
     double* row = rowp + (size_t)(s & 1) * d;
@@ -390,18 +411,30 @@ tridiag_cluster_kernel(const double* __restrict__ A, int d, double* __restrict__
     while (rank + cs * qfirst <= s) ++qfirst;
     const int cbeg = (s + 1) & ~63;          // lanes take aligned pairs of columns: c = cbeg + 2 lane + 64 j
     if constexpr (REG) {
-      const int i0 = rank + cs * warp, i1 = i0 + cs * kTriWarps;
-      const bool act0 = i0 > s && i0 < d, act1 = i1 > s && i1 < d;
-      if (act0 || act1) {                       // warp-uniform
-        const double vi0 = act0 ? v[i0] : 0.0, wi0 = act0 ? w[i0] : 0.0;
-        const double vi1 = act1 ? v[i1] : 0.0, wi1 = act1 ? w[i1] : 0.0;
+      int irow[NR];
+      bool act[NR];
+      bool any = false;
+#pragma unroll
+      for (int k = 0; k < NR; ++k) {
+        irow[k] = rank + cs * (warp + kTriWarps * k);
+        act[k] = irow[k] > s && irow[k] < d;
+        any = any || act[k];
+      }
+      if (any) {                                // warp-uniform
+        double vi[NR], wi[NR], dx[NR], dy[NR];
+#pragma unroll
+        for (int k = 0; k < NR; ++k) {
+          vi[k] = act[k] ? v[irow[k]] : 0.0;
+          wi[k] = act[k] ? w[irow[k]] : 0.0;
+          dx[k] = 0.0;
+          dy[k] = 0.0;
+        }
         // Branch-free over the lanes: columns <= s of an own row are dead (never read again) and v' is exactly zero
         // there, so every lane updates its pair and adds it to the dot; an inactive row has vi = wi = 0 and stays
         // as it is.  (Per-lane tests compiled to divergent regions: ~290 cycles per 64 columns.)
-        double d0x = 0.0, d0y = 0.0, d1x = 0.0, d1y = 0.0;
         const int jbeg = (s + 1) >> 6;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
+        for (int j = 0; j < NJ; ++j) {
           const int c = 2 * lane + 64 * j;
           if (j >= jbeg && 64 * j < d) {          // warp-uniform
             const bool inb = c < d;
@@ -411,39 +444,45 @@ tridiag_cluster_kernel(const double* __restrict__ A, int d, double* __restrict__
             double2 nv = *reinterpret_cast<const double2*>(vn + cc);
             nv.x = inb ? nv.x : 0.0;
             nv.y = inb ? nv.y : 0.0;
-            double2 a = rr[0][j], b = rr[1][j];
-            a.x = fma(-wi0, vv.x, fma(-vi0, wv.x, a.x));
-            a.y = fma(-wi0, vv.y, fma(-vi0, wv.y, a.y));
-            b.x = fma(-wi1, vv.x, fma(-vi1, wv.x, b.x));
-            b.y = fma(-wi1, vv.y, fma(-vi1, wv.y, b.y));
-            d0x = fma(a.x, nv.x, d0x);
-            d0y = fma(a.y, nv.y, d0y);
-            d1x = fma(b.x, nv.x, d1x);
-            d1y = fma(b.y, nv.y, d1y);
-            if (inb) { rr[0][j] = a; rr[1][j] = b; }
+#pragma unroll
+            for (int k = 0; k < NR; ++k) {
+              double2 a = rr[k][j];
+              a.x = fma(-wi[k], vv.x, fma(-vi[k], wv.x, a.x));
+              a.y = fma(-wi[k], vv.y, fma(-vi[k], wv.y, a.y));
+              dx[k] = fma(a.x, nv.x, dx[k]);
+              dy[k] = fma(a.y, nv.y, dy[k]);
+              if (inb) rr[k][j] = a;
+            }
           }
         }
-        double dot0 = d0x + d0y, dot1 = d1x + d1y;
+        double dot[NR];
+#pragma unroll
+        for (int k = 0; k < NR; ++k) dot[k] = dx[k] + dy[k];
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
-          dot0 += __shfl_xor_sync(0xffffffffu, dot0, o);
-          dot1 += __shfl_xor_sync(0xffffffffu, dot1, o);
+#pragma unroll
+          for (int k = 0; k < NR; ++k) dot[k] += __shfl_xor_sync(0xffffffffu, dot[k], o);
         }
         if (lane < cs && !last) {
-          if (act0) st_async_f64(&pnext[i0], &xbar[(s + 1) & 1], (unsigned)lane, t * dot0);
-          if (act1) st_async_f64(&pnext[i1], &xbar[(s + 1) & 1], (unsigned)lane, t * dot1);
+#pragma unroll
+          for (int k = 0; k < NR; ++k)
+            if (act[k]) st_async_f64(&pnext[irow[k]], &xbar[(s + 1) & 1], (unsigned)lane, t * dot[k]);
         }
       }
-      // the warp that holds row s+1 stages it in shared memory for the push below
-      if (rank == (owner + 1 == cs ? 0 : owner + 1) && !last) {
+      // the warp that holds row s+1 stages it in shared memory for the push below (after the last step: for diag[d-1])
+      if (rank == (owner + 1 == cs ? 0 : owner + 1)) {
         const int os = owner + 1 == cs ? oslot + 1 : oslot;     // slot of row s+1
         if ((os & (kTriWarps - 1)) == warp) {
-          const bool hi = os >= kTriWarps;
+          const int kk = os / kTriWarps;
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
+          for (int j = 0; j < NJ; ++j) {
             const int c = 2 * lane + 64 * j;
-            if (c < d) *reinterpret_cast<double2*>(R + c) = hi ? rr[1][j] : rr[0][j];
+            double2 e = rr[0][j];
+#pragma unroll
+            for (int k = 1; k < NR; ++k) if (k == kk) e = rr[k][j];
+            if (c < d) *reinterpret_cast<double2*>(R + c) = e;
           }
+          ptx::fence_proxy_async_smem();   // the bulk copy below reads R through the async proxy
         }
       }
     } else {
@@ -494,13 +533,14 @@ tridiag_cluster_kernel(const double* __restrict__ A, int d, double* __restrict__
     if (++owner == cs) { owner = 0; ++oslot; }
     // the owner of row s+1 pushes it (columns > s) into every CTA of the cluster, all its threads sharing the stores
     if (owner == rank && !last) {
+      if constexpr (!REG) ptx::fence_proxy_async_smem();   // the row was updated in R by generic stores of several warps
       __syncthreads();
       const double* Rs = REG ? R : R + (size_t)oslot * d;
       double* dst = rowp + (size_t)((s + 1) & 1) * d;
-      for (int c = s + 1 + tid; c < d; c += kTriThreads) {
-        const double val = Rs[c];
-        for (int r = 0; r < cs; ++r) st_async_f64(dst + c, &xbar[(s + 1) & 1], (unsigned)r, val);
-      }
+      // one bulk copy per destination CTA (round 1 pushed element by element: 16 x (d - s) st.async from one CTA,
+      // ~2700 cycles of the step at d = 512); the extra element at an odd s + 1 lands in a dead slot of the buffer
+      const int c0 = (s + 1) & ~1;
+      if (tid < cs) bulk_push(dst + c0, Rs + c0, (unsigned)(8 * (d - c0)), &xbar[(s + 1) & 1], (unsigned)tid);
     }
     TRI_TRACE(5);
     TRI_TRACE(6);   // pushes issued; the wait for the next step's operands is event 1 of the next step
@@ -509,16 +549,11 @@ tridiag_cluster_kernel(const double* __restrict__ A, int d, double* __restrict__
   if (d == 1) {
     if (tid == 0) { diag[0] = A[0]; off[0] = 0.0; tau[0] = 0.0; }
   } else if (REG) {
-    const int sl = d - 1, q = sl / cs;
-    if (sl % cs == rank && (q & (kTriWarps - 1)) == warp && lane == ((sl & 63) >> 1)) {
-      const int j = sl >> 6;
-      double2 e = make_double2(0.0, 0.0);
-#pragma unroll
-      for (int jj = 0; jj < 4; ++jj)
-        if (jj == j) e = q >= kTriWarps ? rr[1][jj] : rr[0][jj];
-      diag[sl] = (sl & 1) ? e.y : e.x;
-      off[sl] = 0.0;
-      tau[sl] = 0.0;
+    // row d-1 was staged in R by its owner during the last step (the cluster barrier above orders the store)
+    if ((d - 1) % cs == rank && tid == 0) {
+      diag[d - 1] = R[d - 1];
+      off[d - 1] = 0.0;
+      tau[d - 1] = 0.0;
     }
   } else if ((d - 1) % cs == rank && tid == 0) {
     const int s = d - 1;
@@ -1110,12 +1145,14 @@ void launch_eigh_topk(Ctx& c, double* dA, int d, int k, double* dW, double* dVt,
     const size_t smem = ((size_t)7 * d + (size_t)((d + cs - 1) / cs) * d) * sizeof(double);
     static PerDeviceMax smem_set, nonportable_set;
     if (smem > 48 * 1024 && smem_set.need(c.device, smem)) {
-      DR4G_CUDA(cudaFuncSetAttribute(tridiag_cluster_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      DR4G_CUDA(cudaFuncSetAttribute(tridiag_cluster_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      DR4G_CUDA(cudaFuncSetAttribute(tridiag_cluster_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      DR4G_CUDA(cudaFuncSetAttribute(tridiag_cluster_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      DR4G_CUDA(cudaFuncSetAttribute(tridiag_cluster_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     }
     if (cs > 8 && nonportable_set.need(c.device, 1)) {
-      DR4G_CUDA(cudaFuncSetAttribute(tridiag_cluster_kernel<false>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
-      DR4G_CUDA(cudaFuncSetAttribute(tridiag_cluster_kernel<true>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+      DR4G_CUDA(cudaFuncSetAttribute(tridiag_cluster_kernel<0>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+      DR4G_CUDA(cudaFuncSetAttribute(tridiag_cluster_kernel<2>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+      DR4G_CUDA(cudaFuncSetAttribute(tridiag_cluster_kernel<4>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
     }
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(cs);
@@ -1131,11 +1168,14 @@ void launch_eigh_topk(Ctx& c, double* dA, int d, int k, double* dW, double* dVt,
     cfg.numAttrs = 1;
     static const int tri_trace = getenv("DR4G_TRI_TRACE") ? atoi(getenv("DR4G_TRI_TRACE")) : 0;
     static const int no_reg = getenv("DR4G_TRI_NOREG") ? atoi(getenv("DR4G_TRI_NOREG")) : 0;
-    const bool reg = !no_reg && d <= 256 && (d + cs - 1) / cs <= 2 * kTriWarps;   // at most two own rows per warp
-    if (reg)
-      DR4G_CUDA(cudaLaunchKernelEx(&cfg, tridiag_cluster_kernel<true>, (const double*)dA, d, diag, off, tau, Vh, xbuf, tri_trace));
+    const int own = (d + cs - 1) / cs;   // own rows per CTA
+    const int rw = no_reg ? 0 : (d <= 256 && own <= 2 * kTriWarps ? 2 : (d <= 512 && own <= 4 * kTriWarps ? 4 : 0));
+    if (rw == 2)
+      DR4G_CUDA(cudaLaunchKernelEx(&cfg, tridiag_cluster_kernel<2>, (const double*)dA, d, diag, off, tau, Vh, xbuf, tri_trace));
+    else if (rw == 4)
+      DR4G_CUDA(cudaLaunchKernelEx(&cfg, tridiag_cluster_kernel<4>, (const double*)dA, d, diag, off, tau, Vh, xbuf, tri_trace));
     else
-      DR4G_CUDA(cudaLaunchKernelEx(&cfg, tridiag_cluster_kernel<false>, (const double*)dA, d, diag, off, tau, Vh, xbuf, tri_trace));
+      DR4G_CUDA(cudaLaunchKernelEx(&cfg, tridiag_cluster_kernel<0>, (const double*)dA, d, diag, off, tau, Vh, xbuf, tri_trace));
     if (tri_trace & 1) {
       long long h[64];
       DR4G_CUDA(cudaStreamSynchronize(c.stream));
