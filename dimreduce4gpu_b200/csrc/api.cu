@@ -183,6 +183,7 @@ struct CtxFull : Ctx {
   Arena io;  // device copies of inputs/outputs for the legacy host-pointer symbols
   StreamFit sf;
   cudaStream_t copy_stream = nullptr, out_stream = nullptr;  // H2D / D2H of the out-of-core legacy path
+  cudaEvent_t switch_ev = nullptr;                            // orders a newly selected stream behind the old one
 };
 
 static CtxFull* ctx_new(int device) {
@@ -216,6 +217,7 @@ static void ctx_delete(CtxFull* c) {
   c->io.release();
   if (c->proj_buf) cudaFree(c->proj_buf);
   c->stage.release();
+  if (c->switch_ev) cudaEventDestroy(c->switch_ev);
   c->sf.release();
   if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
   if (c->out_stream) cudaStreamDestroy(c->out_stream);
@@ -815,7 +817,17 @@ void dr4g_ctx_destroy(dr4g_ctx* ctx) { ctx_delete(ctx); }
 int dr4g_ctx_set_stream(dr4g_ctx* ctx, void* cuda_stream) {
   DR4G_API_BEGIN
   if (!ctx) fail("null context");
-  ctx->stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  const cudaStream_t next = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
+  if (next != ctx->stream) {
+    // the arena and the accumulators are reused by whatever runs next: order the new stream behind the work that is
+    // still queued on the old one
+    DeviceGuard g(ctx->device);
+    if (!ctx->switch_ev) DR4G_CUDA(cudaEventCreateWithFlags(&ctx->switch_ev, cudaEventDisableTiming));
+    DR4G_CUDA(cudaEventRecord(ctx->switch_ev, ctx->stream));
+    DR4G_CUDA(cudaStreamWaitEvent(next, ctx->switch_ev, 0));
+    ctx->stream = next;
+  }
   DR4G_API_END
 }
 

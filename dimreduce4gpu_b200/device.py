@@ -10,6 +10,8 @@ packed [Gram | column sums | sums of squares | row count] once."""
 from __future__ import annotations
 
 import ctypes
+import functools
+import threading
 from typing import Optional
 
 import numpy as np
@@ -41,6 +43,17 @@ def _need_cuda_contig(t, name: str, device: int):
     return t
 
 
+def _serialized(fn):
+    """Stream selection and launch are one critical section per context: the estimators share one cached context per
+    GPU, and dr4g_ctx_set_stream followed by a launch from two Python threads could otherwise interleave (the C entry
+    points take the context's mutex one by one)."""
+    @functools.wraps(fn)
+    def wrapper(self, *a, **kw):
+        with self._lock:
+            return fn(self, *a, **kw)
+    return wrapper
+
+
 class DeviceContext:
     """Persistent per-device context (stream, workspace arena, optional NCCL communicator)."""
 
@@ -51,6 +64,7 @@ class DeviceContext:
         if not self._h:
             raise RuntimeError(f"dr4g_ctx_create({device}) failed: {last_error()}")
         self.rank, self.world = 0, 1
+        self._lock = threading.RLock()
 
     # ------------------------------------------------------------------ lifecycle
     def close(self) -> None:
@@ -109,6 +123,7 @@ class DeviceContext:
             self.init_comm(uid[0], rank, world)
 
     # ------------------------------------------------------------------ fit / transform
+    @_serialized
     def fit(self, X, n_components: int, center: bool, algorithm: str = "cusolver", n_iter: int = 5,
             random_state: int = 0, tol: float = 1e-5, verbose: bool = False, out: Optional[dict] = None,
             whiten: bool = False) -> dict:
@@ -141,6 +156,7 @@ class DeviceContext:
         _check(rc, f"dr4g_fit_{sfx}")
         return out
 
+    @_serialized
     def fit_transform_host(self, X: np.ndarray, n_components: int, center: bool, algorithm: str = "cusolver",
                            n_iter: int = 5, random_state: int = 0, tol: float = 1e-5, verbose: bool = False,
                            whiten: bool = False, want_u: bool = True, out: Optional[dict] = None) -> dict:
@@ -169,6 +185,7 @@ class DeviceContext:
         return out
 
     # ------------------------------------------------------------------ streaming fit
+    @_serialized
     def partial_fit(self, X, center: bool) -> None:
         """Accumulate one device-resident row chunk (n, d) into the context's [G|s|q|n]; asynchronous on the
         current torch stream (keep X alive until later work on that stream has finished)."""
@@ -187,6 +204,7 @@ class DeviceContext:
     def partial_fit_reset(self) -> None:
         _check(self._lib.dr4g_partial_fit_reset(self._h), "dr4g_partial_fit_reset")
 
+    @_serialized
     def partial_fit_finalize(self, n_features: int, n_components: int, center: bool, dtype, algorithm: str = "cusolver",
                              n_iter: int = 5, random_state: int = 0, tol: float = 1e-5, verbose: bool = False,
                              whiten: bool = False) -> dict:
@@ -216,6 +234,7 @@ class DeviceContext:
         _check(rc, f"dr4g_partial_fit_finalize_{sfx}")
         return out
 
+    @_serialized
     def transform(self, X, components, mean=None, singular_values=None, want_u: bool = False, out=None, out_u=None):
         """Z = (X - mean) @ components.T on this rank's rows (no communication); optionally U = Z / sigma."""
         import torch
@@ -240,6 +259,7 @@ class DeviceContext:
         _check(rc, f"dr4g_transform_{sfx}")
         return (Z, U) if want_u else Z
 
+    @_serialized
     def inverse_transform(self, Z, components, mean=None, out=None):
         import torch
 
@@ -258,6 +278,7 @@ class DeviceContext:
         _check(rc, f"dr4g_inverse_transform_{sfx}")
         return X
 
+    @_serialized
     def csr_to_dense(self, indptr, indices, data, row0: int, rows: int, d: int, out=None):
         """Rows [row0, row0 + rows) of a device-resident CSR matrix (int64 indptr, int32 indices, fp32/fp64 data CUDA
         tensors) expanded into a dense (rows, d) CUDA tensor (dr4g_csr_to_dense_*)."""
@@ -275,6 +296,7 @@ class DeviceContext:
         return D
 
     # ------------------------------------------------------------------ building blocks
+    @_serialized
     def colstats(self, X, shift=None):
         import torch
 
@@ -288,6 +310,7 @@ class DeviceContext:
         _check(rc, "dr4g_colstats")
         return s, q
 
+    @_serialized
     def gram(self, X, shift=None):
         import torch
 
@@ -300,6 +323,7 @@ class DeviceContext:
         _check(rc, "dr4g_gram")
         return G
 
+    @_serialized
     def eigh(self, A):
         """Symmetric eigendecomposition (fp64, blocked Jacobi).  Returns (w unsorted, V columns)."""
         import torch
@@ -315,6 +339,7 @@ class DeviceContext:
         _check(self._lib.dr4g_eigh_double(self._h, work.data_ptr(), d, w.data_ptr(), V.data_ptr()), "dr4g_eigh_double")
         return w, V
 
+    @_serialized
     def eigh_topk(self, A, k: int):
         """k largest eigenpairs of a symmetric fp64 matrix (the exact fit's solver).  Returns
         (w descending (k,), Vt (k, d) unit eigenvectors in rows)."""

@@ -210,3 +210,50 @@ def test_csr_to_dense_kernel_matches_scipy():
     D = ctx.csr_to_dense(ip, ix, dv, 100, 650, 77)
     ctx.sync()
     np.testing.assert_array_equal(D.cpu().numpy(), np.asarray(Xs[100:750].todense()))
+
+
+def test_stream_switch_orders_arena_reuse_and_threads_share_one_context():
+    """the estimators share one cached context per GPU.  (a) A call on another torch stream reuses the
+    arena the previous call's kernels may still be reading: dr4g_ctx_set_stream orders the new stream behind the old
+    one.  (b) Two Python threads calling through the same context: stream selection + launch is one critical section."""
+    import threading
+
+    import torch
+
+    import dimreduce4gpu_b200 as pkg
+
+    ctx = pkg.DeviceContext(0)
+    g = torch.Generator(device="cuda").manual_seed(3)
+    X1 = torch.randn(300_000, 256, device="cuda", generator=g) * torch.linspace(1, 3, 256, device="cuda")
+    X2 = torch.randn(200_000, 512, device="cuda", generator=g) * torch.linspace(1, 2, 512, device="cuda")
+    ref1 = {k: v.clone() for k, v in ctx.fit(X1, 16, center=True).items()}
+    ref2 = {k: v.clone() for k, v in ctx.fit(X2, 8, center=True).items()}
+    torch.cuda.synchronize()
+    s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+    for _ in range(3):
+        with torch.cuda.stream(s1):
+            o1 = {k: v.clone() for k, v in ctx.fit(X1, 16, center=True).items()}
+        with torch.cuda.stream(s2):          # no synchronisation in between: same arena, other stream
+            o2 = {k: v.clone() for k, v in ctx.fit(X2, 8, center=True).items()}
+        torch.cuda.synchronize()
+        assert torch.equal(o1["singular_values"], ref1["singular_values"]) and torch.equal(o1["components"], ref1["components"])
+        assert torch.equal(o2["singular_values"], ref2["singular_values"]) and torch.equal(o2["components"], ref2["components"])
+
+    errs = []
+
+    def worker(X, k, ref, stream):
+        try:
+            with torch.cuda.stream(stream):
+                for _ in range(5):
+                    o = ctx.fit(X, k, center=True)
+                    sv = o["singular_values"].clone()
+                    stream.synchronize()
+                    if not torch.equal(sv, ref["singular_values"]):
+                        errs.append("mismatch")
+        except Exception as e:  # noqa: BLE001
+            errs.append(repr(e))
+
+    t1 = threading.Thread(target=worker, args=(X1, 16, ref1, s1))
+    t2 = threading.Thread(target=worker, args=(X2, 8, ref2, s2))
+    t1.start(); t2.start(); t1.join(); t2.join()
+    assert not errs, errs
