@@ -436,7 +436,7 @@ size_t gram_tc_workspace_bytes(const Ctx& c, int d) {
     const int grid = tab.job[tab.njobs - 1].cta_begin + tab.job[tab.njobs - 1].ncta;
     single = (size_t)grid * 4 * kBlk * kBlk * sizeof(float);
   }
-  const size_t pair = (d > kBlk && d % 32 == 0) ? gram_pair_workspace_bytes(c, d) : 0;
+  const size_t pair = (d > kBlk && d % 4 == 0) ? gram_pair_workspace_bytes(c, d) : 0;
   return single > pair ? single : pair;
 }
 

@@ -725,6 +725,28 @@ symmetrize_diag_kernel(double* __restrict__ G, int d, unsigned pr_mask) {
   }
 }
 
+// G += y y^T, s += y, q += y^2 for a few trailing rows (y = x - c in fp32 like the converters, products in fp64).
+// grid = (ceil(d / 256), d), block = 256: thread (j, blockIdx.y = i).
+__global__ void __launch_bounds__(256)
+gram_tail_rows_kernel(const float* __restrict__ X, long long rows, int d, const float* __restrict__ shift, double* __restrict__ G,
+                      double* __restrict__ osum, double* __restrict__ osq) {
+  const int j = (int)(blockIdx.x * 256 + threadIdx.x), i = (int)blockIdx.y;
+  if (j >= d) return;
+  const float ci = shift ? shift[i] : 0.f, cj = shift ? shift[j] : 0.f;
+  double acc = 0.0, s = 0.0, q = 0.0;
+  for (long long r = 0; r < rows; ++r) {
+    const double yi = (double)(X[(size_t)r * d + i] - ci), yj = (double)(X[(size_t)r * d + j] - cj);
+    acc += yi * yj;
+    s += yj;
+    q += yj * yj;
+  }
+  G[(size_t)i * d + j] += acc;
+  if (i == 0 && osum != nullptr) {
+    atomicAdd(&osum[j], s);
+    atomicAdd(&osq[j], q);
+  }
+}
+
 }  // namespace
 
 // ---------------------------------------------------------------- host side
@@ -855,7 +877,8 @@ using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t
 }  // namespace
 
 bool gram_pair_eligible(const Ctx& c, const float* dX, long long n, int d) {
-  if (n < 1 || d <= kBlk || (d % 32) != 0) return false;           // 3-D map: whole 32-column groups
+  if (n < 1 || d <= kBlk || (d % 4) != 0) return false;            // TMA: 16-byte row pitch
+  if ((d % 32) != 0 && n < 2) return false;                         // ragged d: the last row goes through gram_tail_rows_kernel
   if ((reinterpret_cast<uintptr_t>(dX) & 15) != 0) return false;    // TMA: 16-byte base
   if (n >= (1ll << 31)) return false;                               // TMA coordinates are int32
   if (c.sm_count < 2) return false;
@@ -874,7 +897,13 @@ void launch_gram_pair(Ctx& c, const float* dX, long long n, int d, const float* 
   if (!build_pair_jobs(d, c.sm_count, bf16, tab)) fail("gram_pair: d=%d does not fit the job table", d);
   // X as a 3-D tensor: (column within a 32-column group, row, column group); one box = 32 x 16 x 4
   CUtensorMap tmap;
-  const cuuint64_t gdim[3] = {32, (cuuint64_t)n, (cuuint64_t)(d / 32)};
+  // d % 32 != 0 (784, 1000, ...): the last 32-column group is only partly inside a row; its other columns are the first
+  // columns of the NEXT row (in bounds, masked by the converters) - except in the very last row, which therefore stays
+  // out of the tensor map and is added by gram_tail_rows_kernel.  (These shapes used to fall to the single-CTA kernel:
+  // 0.15 TB/s at 500,000 x 516.)
+  const long long n_all = n;
+  if ((d % 32) != 0) n = n - 1;
+  const cuuint64_t gdim[3] = {32, (cuuint64_t)n, (cuuint64_t)((d + 31) / 32)};
   const cuuint64_t gstride[2] = {(cuuint64_t)d * sizeof(float), 32 * sizeof(float)};
   const cuuint32_t box[3] = {32, (cuuint32_t)kSlotRows, 4};
   const cuuint32_t estride[3] = {1, 1, 1};
@@ -965,6 +994,10 @@ void launch_gram_pair(Ctx& c, const float* dX, long long n, int d, const float* 
   symmetrize_diag_kernel<<<dim3(36, (d + 255) / 256), 256, 0, c.stream>>>(dG, d, pr_mask);
   c.launches++;
   c.launches++;
+  if (n < n_all) {
+    gram_tail_rows_kernel<<<dim3((d + 255) / 256, d), 256, 0, c.stream>>>(dX + (size_t)n * d, n_all - n, d, dshift, dG, dsum, dsumsq);
+    c.launches++;
+  }
   DR4G_CUDA(cudaGetLastError());
 }
 

@@ -47,7 +47,10 @@ def _rel_err(G, Xd):
 # (320, 384), several flush windows of the diagonal jobs (600000 x 256: 8108 rows per cluster, window 4096)
 SHAPES = [(1, 4), (3, 8), (64, 128), (200, 128), (4099, 100), (5000, 256), (3001, 320), (2500, 384),
           (8192, 512), (3000, 516), (4096, 1024), (300000, 256), (70000, 512),
-          (10, 256), (33, 512), (1000, 768), (600000, 256), (20000, 2048)]
+          (10, 256), (33, 512), (1000, 768), (600000, 256), (20000, 2048),
+          # ragged d through the pair kernel (d % 32 != 0: the last row goes through gram_tail_rows_kernel): MNIST's 784,
+          # 1000, a partial last 128-block with a partial last group, two rows only
+          (30000, 784), (12345, 1000), (5000, 132), (2, 516), (70000, 300)]
 
 
 @pytest.mark.parametrize("n,d", SHAPES)
