@@ -82,7 +82,7 @@ template <int KP>
 __global__ void __launch_bounds__(PT_THREADS, 1)
 project_tc_kernel(const float* __restrict__ X, long long n, int d, int k, const float* __restrict__ mean,
                   const uint8_t* __restrict__ bimg, const float* __restrict__ sigma, float* __restrict__ Z,
-                  float* __restrict__ U, int nstages) {
+                  float* __restrict__ U, int nstages, int vec4) {
   constexpr uint32_t B_BYTES = 2 * KP * 128;                  // [hi ; lo] slice of the components image
   constexpr uint32_t STAGE_BYTES = 2 * PT_A_BYTES + B_BYTES;
   constexpr uint32_t ACC_COLS = 2 * KP;                       // one accumulator buffer: [a1 b1 + a2 b1 | a1 b2]
@@ -276,13 +276,21 @@ project_tc_kernel(const float* __restrict__ X, long long n, int d, int k, const 
             float z1 = __uint_as_float(v[j + 1]) + __uint_as_float(w[j + 1]);
             float z2 = __uint_as_float(v[j + 2]) + __uint_as_float(w[j + 2]);
             float z3 = __uint_as_float(v[j + 3]) + __uint_as_float(w[j + 3]);
-            if (m + 3 < k) {   // k % 4 == 0 on this path
+            if (vec4) {        // k % 4 == 0 and 16-byte aligned outputs: m + 3 < k
               *reinterpret_cast<float4*>(zr + j) = make_float4(z0, z1, z2, z3);
               if (ur) {
                 const float4 sg = __ldg(reinterpret_cast<const float4*>(sigma + m));
                 *reinterpret_cast<float4*>(ur + j) = make_float4(sg.x != 0.f ? z0 / sg.x : 0.f, sg.y != 0.f ? z1 / sg.y : 0.f,
                                                                  sg.z != 0.f ? z2 / sg.z : 0.f, sg.w != 0.f ? z3 / sg.w : 0.f);
               }
+            } else {           // any k (2, 3, 10, 50, ...): the row pitch is not a multiple of 16 bytes
+              const float zz[4] = {z0, z1, z2, z3};
+#pragma unroll
+              for (int e = 0; e < 4; ++e)
+                if (m + e < k) {
+                  zr[j + e] = zz[e];
+                  if (ur) { const float sg = __ldg(sigma + m + e); ur[j + e] = sg != 0.f ? zz[e] / sg : 0.f; }
+                }
             }
           }
         }
@@ -312,16 +320,18 @@ void launch_kp(Ctx& c, const float* dX, long long n, int d, int k, const float* 
     DR4G_CUDA(cudaFuncSetAttribute(project_tc_kernel<KP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const long long ntiles = (n + PT_ROWS - 1) / PT_ROWS;
   const int grid = (int)(ntiles < c.sm_count ? ntiles : c.sm_count);
-  project_tc_kernel<KP><<<grid, PT_THREADS, smem, c.stream>>>(dX, n, d, k, dmean, img, dw, dZ, dU, nstages);
+  const int vec4 = (k % 4) == 0 && (reinterpret_cast<uintptr_t>(dZ) & 15) == 0 && (!dU || (reinterpret_cast<uintptr_t>(dU) & 15) == 0) &&
+                   (!dw || (reinterpret_cast<uintptr_t>(dw) & 15) == 0);
+  project_tc_kernel<KP><<<grid, PT_THREADS, smem, c.stream>>>(dX, n, d, k, dmean, img, dw, dZ, dU, nstages, vec4);
 }
 
 }  // namespace
 
 bool project_tc_eligible(const Ctx& c, const float* dX, long long n, int d, int k, const float* dZ, const float* dU) {
-  if (n < 1 || d < 4 || (d % 4) != 0 || k < 4 || (k % 4) != 0 || k > 128) return false;
-  if ((reinterpret_cast<uintptr_t>(dX) & 15) != 0 || (reinterpret_cast<uintptr_t>(dZ) & 15) != 0) return false;
-  if (dU && (reinterpret_cast<uintptr_t>(dU) & 15) != 0) return false;
-  return true;
+  (void)dZ;
+  (void)dU;
+  if (n < 1 || d < 4 || (d % 4) != 0 || k < 1 || k > 128) return false;     // any k: unaligned output rows take scalar stores
+  return (reinterpret_cast<uintptr_t>(dX) & 15) == 0;
 }
 
 void launch_project_tc(Ctx& c, const float* dX, long long n, int d, int k, const float* dQ, const float* dmean,

@@ -30,7 +30,9 @@ def _problem(n, d, k, seed):
 
 # one tile, ragged last tile, fewer rows than a tile, d not a multiple of 64, k = 4 .. 128, more tiles than SMs
 SHAPES = [(128, 64, 32), (1, 8, 4), (100, 100, 12), (5000, 256, 32), (70001, 512, 32), (3000, 1024, 64), (2000, 320, 100),
-          (999, 132, 128), (40000, 64, 8), (300000, 256, 32)]
+          (999, 132, 128), (40000, 64, 8), (300000, 256, 32),
+          # k % 4 != 0 (scalar stores of the score rows): the usual small k of a PCA for plotting, C1's k = 10, k = 50
+          (20000, 256, 2), (5000, 100, 10), (7777, 512, 3), (30000, 784, 50), (1000, 64, 1), (2048, 128, 127)]
 
 
 @pytest.mark.parametrize("n,d,k", SHAPES)
@@ -70,7 +72,7 @@ def test_ineligible_shapes_fall_back():
     import torch
 
     ctx = _ctx()
-    X, Q, mean, sigma = _problem(500, 48, 6, 1)   # k % 4 != 0
+    X, Q, mean, sigma = _problem(500, 50, 6, 1)   # d % 4 != 0: rows of X are not 16-byte aligned
     Z = ctx.transform(X, Q, mean=mean)
     ctx.sync()
     assert ctx.last_proj_path == "cuda_cores"
