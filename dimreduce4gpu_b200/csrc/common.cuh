@@ -149,6 +149,10 @@ int jacobi_padded_dim(int d);
 size_t jacobi_workspace_bytes(int dp);
 void launch_jacobi(Ctx& c, double* dA, double* dV, int dp, double* dW, void* workspace, double tol, int max_sweeps);
 void launch_pad_copy(Ctx& c, const double* src, int d, double* dst, int dp);
+template <typename T>
+void launch_pad_rows(Ctx& c, const T* src, long long rows, int d, int dp, T* dst);   // rows x d -> rows x dp, zero pad
+void launch_unpad_moments(Ctx& c, const double* Gp, const double* sp, const double* qp, int d, int dp, double* G, double* s,
+                          double* q);
 
 // K4 (exact path): top-k eigenpairs via Householder tridiagonalisation + Sturm multisection +
 // inverse iteration + back-transformation.  dA (d x d, symmetric, row-major) is destroyed; dW gets

@@ -165,6 +165,44 @@ void launch_rebase_sum(Ctx& c, const double* gathered, int world, int d, double*
   DR4G_CUDA(cudaGetLastError());
 }
 
+// rows x d -> rows x dp (dp >= d, zero in the pad columns): the chunk copy that gives the TMA / cp.async kernels the
+// 16-byte row pitch and base they need when d % 4 != 0 (fp32) or d is odd (fp64) or the caller's pointer is unaligned
+template <typename T>
+__global__ void pad_rows_kernel(const T* __restrict__ src, long long rows, int d, int dp, T* __restrict__ dst) {
+  const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= rows * dp) return;
+  const long long r = e / dp;
+  const int cidx = (int)(e - r * dp);
+  dst[e] = cidx < d ? src[r * d + cidx] : T(0);
+}
+
+template <typename T>
+void launch_pad_rows(Ctx& c, const T* src, long long rows, int d, int dp, T* dst) {
+  const long long total = rows * dp;
+  pad_rows_kernel<T><<<(unsigned)((total + 255) / 256), 256, 0, c.stream>>>(src, rows, d, dp, dst);
+  c.launches++;
+  DR4G_CUDA(cudaGetLastError());
+}
+template void launch_pad_rows<float>(Ctx&, const float*, long long, int, int, float*);
+template void launch_pad_rows<double>(Ctx&, const double*, long long, int, int, double*);
+
+// [G_p (dp x dp) | s_p | q_p] of the padded problem -> G (d x d), s, q
+__global__ void unpad_moments_kernel(const double* __restrict__ Gp, const double* __restrict__ sp, const double* __restrict__ qp,
+                                     int d, int dp, double* __restrict__ G, double* __restrict__ s, double* __restrict__ q) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+  if (j >= d) return;
+  G[(size_t)i * d + j] = Gp[(size_t)i * dp + j];
+  if (i == 0) { s[j] = sp[j]; q[j] = qp[j]; }
+}
+
+void launch_unpad_moments(Ctx& c, const double* Gp, const double* sp, const double* qp, int d, int dp, double* G, double* s,
+                          double* q) {
+  dim3 grid(ceil_div(d, 128), d);
+  unpad_moments_kernel<<<grid, 128, 0, c.stream>>>(Gp, sp, qp, d, dp, G, s, q);
+  c.launches++;
+  DR4G_CUDA(cudaGetLastError());
+}
+
 void launch_pad_copy(Ctx& c, const double* src, int d, double* dst, int dp) {
   dim3 grid(ceil_div(dp, 128), dp);
   pad_copy_kernel<<<grid, 128, 0, c.stream>>>(src, d, dst, dp);

@@ -79,3 +79,9 @@ def test_fit_double_uses_the_new_kernel_and_odd_d_falls_back():
     assert ctx.last_gram_path == "generic_dmma"
     s = torch.linalg.svdvals(Xo - Xo.mean(0))[:5]
     np.testing.assert_allclose(r["singular_values"].cpu().numpy(), s.cpu().numpy(), rtol=1e-11)
+    Xp = _make(3000, 333, 7)   # odd d > 128: zero-padded chunk copies through the 128 x 128 DMMA kernel
+    r = ctx.fit(Xp, 5, center=True)
+    ctx.sync()
+    assert ctx.last_gram_path == "dmma_f64_128"
+    s = torch.linalg.svdvals(Xp - Xp.mean(0))[:5]
+    np.testing.assert_allclose(r["singular_values"].cpu().numpy(), s.cpu().numpy(), rtol=1e-11)

@@ -135,7 +135,10 @@ def test_power_default_iterations_meet_reference_criteria():
 
 
 @pytest.mark.parametrize("kind,n,d,k", [("pca", 20000, 256, 32), ("tsvd", 30000, 100, 10), ("pca", 5000, 96, 12),
-                                        ("tsvd", 4097, 130, 7), ("pca", 777, 33, 5), ("pca", 3, 5, 3)])
+                                        ("tsvd", 4097, 130, 7), ("pca", 777, 33, 5), ("pca", 3, 5, 3),
+                                        # d % 4 != 0: zero-padded chunk copies through the tensor-core kernels (api.cu: dpad)
+                                        ("pca", 6000, 99, 10), ("tsvd", 3000, 1001, 16), ("pca", 20000, 50, 5),
+                                        ("pca", 2500, 254, 20), ("tsvd", 9, 7, 3)])
 def test_live_oracle_fp32(kind, n, d, k):
     """Seeded anisotropic inputs, reference CPU backend run live beside the GPU."""
     rng = np.random.default_rng(100 + n)
@@ -149,7 +152,8 @@ def test_live_oracle_fp32(kind, n, d, k):
                    ref.explained_variance_ratio, ref.mean, ref.X_transformed, TOL32, n)
 
 
-@pytest.mark.parametrize("kind,n,d,k", [("pca", 6000, 192, 20), ("tsvd", 5000, 70, 9), ("pca", 300, 40, 40)])
+@pytest.mark.parametrize("kind,n,d,k", [("pca", 6000, 192, 20), ("tsvd", 5000, 70, 9), ("pca", 300, 40, 40),
+                                        ("pca", 4000, 99, 10), ("tsvd", 1500, 1001, 12)])   # odd d: padded chunk copies
 def test_live_oracle_fp64(kind, n, d, k):
     """pca_double / truncated_svd_double vs the fp64 restatement at 1e-10 relative."""
     rng = np.random.default_rng(7 + n)
