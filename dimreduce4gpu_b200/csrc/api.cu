@@ -216,6 +216,7 @@ static void ctx_delete(CtxFull* c) {
   c->arena.release();
   c->io.release();
   if (c->proj_buf) cudaFree(c->proj_buf);
+  if (c->pad_buf) cudaFree(c->pad_buf);
   c->stage.release();
   if (c->switch_ev) cudaEventDestroy(c->switch_ev);
   c->sf.release();

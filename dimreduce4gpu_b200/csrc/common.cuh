@@ -89,6 +89,8 @@ struct Ctx {
   // K7 on tcgen05: pre-split components image (grow-only, private to the projection)
   void* proj_buf = nullptr;
   size_t proj_cap = 0;
+  void* pad_buf = nullptr;    // K7: zero-padded chunk copy of X + padded components / mean (shapes without a 16-byte row pitch)
+  size_t pad_cap = 0;
   int proj_path = 0;          // 0 auto (tcgen05 where eligible), 1 CUDA-core kernels only
   int last_proj_path = 0;     // 1 CUDA cores, 2 tcgen05, 3 fp64 DMMA
   // tensor-map encoder (driver entry point fetched lazily)
@@ -112,7 +114,7 @@ void launch_mirror_upper(Ctx& c, double* dG, int d);
 // K7, fp64 input (project_f64.cu): 128-row tiles on the DMMA pipe, k <= 128
 bool project_f64_eligible(const Ctx& c, const double* dX, long long n, int d, int k, const double* dQ);
 void launch_project_f64(Ctx& c, const double* dX, long long n, int d, int k, const double* dQ, const double* dmean,
-                        const double* dw, double* dZ, double* dU);
+                        const double* dw, double* dZ, double* dU, int ldz = 0);   // ldz: row pitch of Z / U (0 = k)
 bool gram_f64_eligible(const Ctx& c, const double* dX, long long n, int d);
 size_t gram_f64_workspace_bytes(const Ctx& c, long long n, int d);
 void launch_gram_f64(Ctx& c, const double* dX, long long n, int d, const double* dshift, double* dG, void* workspace);
@@ -176,10 +178,10 @@ void launch_postproc(Ctx& c, const double* dW, int nw, const double* dV, int ldv
 template <typename T>
 void launch_project(Ctx& c, const T* dX, long long n, int d, int k, const T* dQ, const T* dmean,
                     const T* dw, T* dZ, T* dU);
-// tcgen05 projection (project_tc.cu): fp32, k <= 128, k % 4 == 0, d % 4 == 0, 16-byte aligned X / Z / U.
+// tcgen05 projection (project_tc.cu): fp32, k <= 128 per launch, d % 4 == 0, 16-byte aligned X.
 bool project_tc_eligible(const Ctx& c, const float* dX, long long n, int d, int k, const float* dZ, const float* dU);
 void launch_project_tc(Ctx& c, const float* dX, long long n, int d, int k, const float* dQ, const float* dmean,
-                       const float* dw, float* dZ, float* dU);
+                       const float* dw, float* dZ, float* dU, int ldz = 0);      // ldz: row pitch of Z / U (0 = k)
 template <typename T>
 void launch_inverse(Ctx& c, const T* dZ, long long n, int d, int k, const T* dQ, const T* dmean, T* dX);
 

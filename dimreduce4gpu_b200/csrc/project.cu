@@ -253,11 +253,74 @@ void launch_project_f32(Ctx& c, const float* dX, long long n, int d, int k, cons
 
 }  // namespace
 
+static inline size_t up256(size_t b) { return (b + 255) / 256 * 256; }
+
 template <typename T>
 void launch_project(Ctx& c, const T* dX, long long n, int d, int k, const T* dQ, const T* dmean, const T* dw,
                     T* dZ, T* dU) {
   if (n <= 0) return;
   c.last_proj_path = 1;
+  // Tensor-core / DMMA kernels: at most 128 components per launch - wider k goes through in column slices of the score
+  // matrices (row pitch k), X being re-read from HBM once per slice; shapes whose rows have no 16-byte pitch (fp32
+  // d % 4 != 0, fp64 odd d, unaligned base) go through zero-padded chunk copies of X (pad_rows_kernel) with the
+  // components and the mean padded alike.  Both used to fall to the CUDA-core kernels below (0.16 TB/s at k = 200,
+  // 0.55 TB/s at d = 1001).
+  if (c.proj_path != 1 && k >= 1 && d >= 2 && (long long)n * d >= (1ll << 16)) {
+    constexpr int q4 = sizeof(T) == 4 ? 4 : 2;
+    const bool in_place = (d % q4) == 0 && (reinterpret_cast<uintptr_t>(dX) & 15) == 0 && (reinterpret_cast<uintptr_t>(dQ) & 15) == 0;
+    const int dp = (d + q4 - 1) / q4 * q4;
+    const T* Xs = dX;
+    const T* Qs = dQ;
+    const T* ms = dmean;
+    long long chunk = n;
+    T* Xp = nullptr;
+    if (!in_place) {
+      chunk = (long long)(((size_t)128 << 20) / ((size_t)dp * sizeof(T)));
+      if (chunk < 1024) chunk = 1024;
+      if (chunk > n) chunk = n;
+      const size_t need = up256((size_t)chunk * dp * sizeof(T)) + up256((size_t)k * dp * sizeof(T)) + up256((size_t)dp * sizeof(T));
+      if (need > c.pad_cap) {
+        if (c.pad_buf) {
+          DR4G_CUDA(cudaStreamSynchronize(c.stream));
+          DR4G_CUDA(cudaFree(c.pad_buf));
+          c.pad_buf = nullptr;
+          c.pad_cap = 0;
+        }
+        DR4G_CUDA(cudaMalloc(&c.pad_buf, need));
+        c.pad_cap = need;
+      }
+      char* base = static_cast<char*>(c.pad_buf);
+      Xp = reinterpret_cast<T*>(base);
+      T* Qp = reinterpret_cast<T*>(base + up256((size_t)chunk * dp * sizeof(T)));
+      T* mp = reinterpret_cast<T*>(base + up256((size_t)chunk * dp * sizeof(T)) + up256((size_t)k * dp * sizeof(T)));
+      launch_pad_rows<T>(c, dQ, k, d, dp, Qp);
+      Qs = Qp;
+      if (dmean) {
+        launch_pad_rows<T>(c, dmean, 1, d, dp, mp);
+        ms = mp;
+      }
+    }
+    for (long long r0 = 0; r0 < n; r0 += chunk) {
+      const long long rows = n - r0 < chunk ? n - r0 : chunk;
+      if (!in_place) {
+        launch_pad_rows<T>(c, dX + (size_t)r0 * d, rows, d, dp, Xp);
+        Xs = Xp;
+      } else {
+        Xs = dX + (size_t)r0 * d;
+      }
+      for (int k0 = 0; k0 < k; k0 += 128) {
+        const int kc = k - k0 < 128 ? k - k0 : 128;
+        T* zs = dZ + (size_t)r0 * k + k0;
+        T* us = (dU && dw) ? dU + (size_t)r0 * k + k0 : nullptr;
+        if constexpr (sizeof(T) == 4)
+          launch_project_tc(c, Xs, rows, dp, kc, Qs + (size_t)k0 * dp, ms, dw ? dw + k0 : nullptr, zs, us, k);
+        else
+          launch_project_f64(c, Xs, rows, dp, kc, Qs + (size_t)k0 * dp, ms, dw ? dw + k0 : nullptr, zs, us, k);
+      }
+    }
+    c.last_proj_path = sizeof(T) == 4 ? 2 : 3;
+    return;
+  }
   if constexpr (sizeof(T) == 4) {
     if (c.proj_path != 1 && project_tc_eligible(c, dX, n, d, k, dZ, (dU && dw) ? dU : nullptr)) {
       launch_project_tc(c, dX, n, d, k, dQ, dmean, dw, dZ, dU);

@@ -57,7 +57,7 @@ template <int NJ>
 __global__ void __launch_bounds__(PTHREADS, 1)
 project_f64_kernel(const double* __restrict__ X, long long n, int d, int k, const double* __restrict__ Q,
                    const double* __restrict__ mq, const double* __restrict__ sigma, double* __restrict__ Z,
-                   double* __restrict__ U) {
+                   double* __restrict__ U, int ldz) {
   constexpr int KP = NJ * 8;
   constexpr int kXs = PR * PPITCH, kQs = KP * PPITCH;          // doubles per stage
   constexpr int kStage = kXs + kQs;
@@ -145,8 +145,8 @@ project_f64_kernel(const double* __restrict__ X, long long n, int d, int k, cons
       const long long r = r0 + rr;
       if (r >= n) break;
       const double z = out[rr * OP + c];
-      Z[(size_t)r * k + c] = z;
-      if (U) { const double sg = sigma[c]; U[(size_t)r * k + c] = sg != 0.0 ? z / sg : 0.0; }   // sigma == 0 -> U column 0 (reference src/tsvd.cu:171-175)
+      Z[(size_t)r * ldz + c] = z;      // ldz: row pitch of Z / U (>= k: a column slice of wider scores)
+      if (U) { const double sg = sigma[c]; U[(size_t)r * ldz + c] = sg != 0.0 ? z / sg : 0.0; }   // sigma == 0 -> U column 0 (reference src/tsvd.cu:171-175)
     }
     __syncthreads();                   // the staging tile is read before the next tile's copies land on it
   }
@@ -154,7 +154,7 @@ project_f64_kernel(const double* __restrict__ X, long long n, int d, int k, cons
 
 template <int NJ>
 void launch_nj(Ctx& c, const double* dX, long long n, int d, int k, const double* dQ, const double* mq, const double* dw,
-               double* dZ, double* dU) {
+               double* dZ, double* dU, int ldz) {
   constexpr size_t smem = (size_t)PSTAGES * (PR + NJ * 8) * PPITCH * sizeof(double);
   static_assert(smem >= (size_t)PR * (NJ * 8 + 2) * sizeof(double), "the staging tile fits the ring");
   static PerDeviceMax smem_set;
@@ -162,7 +162,7 @@ void launch_nj(Ctx& c, const double* dX, long long n, int d, int k, const double
     DR4G_CUDA(cudaFuncSetAttribute(project_f64_kernel<NJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const long long ntiles = (n + PR - 1) / PR;
   const int grid = (int)(ntiles < c.sm_count ? ntiles : c.sm_count);
-  project_f64_kernel<NJ><<<grid, PTHREADS, smem, c.stream>>>(dX, n, d, k, dQ, mq, dw, dZ, dU);
+  project_f64_kernel<NJ><<<grid, PTHREADS, smem, c.stream>>>(dX, n, d, k, dQ, mq, dw, dZ, dU, ldz);
 }
 
 }  // namespace
@@ -173,7 +173,8 @@ bool project_f64_eligible(const Ctx& c, const double* dX, long long n, int d, in
 }
 
 void launch_project_f64(Ctx& c, const double* dX, long long n, int d, int k, const double* dQ, const double* dmean,
-                        const double* dw, double* dZ, double* dU) {
+                        const double* dw, double* dZ, double* dU, int ldz) {
+  if (ldz <= 0) ldz = k;
   double* mq = nullptr;
   if (dmean) {
     const size_t need = 128 * sizeof(double);
@@ -195,7 +196,7 @@ void launch_project_f64(Ctx& c, const double* dX, long long n, int d, int k, con
   double* du = (dU && dw) ? dU : nullptr;
   const int nj = (k + 7) / 8;
   switch (nj) {
-#define DR4G_NJ(N) case N: launch_nj<N>(c, dX, n, d, k, dQ, mq, sg, dZ, du); break;
+#define DR4G_NJ(N) case N: launch_nj<N>(c, dX, n, d, k, dQ, mq, sg, dZ, du, ldz); break;
     DR4G_NJ(1) DR4G_NJ(2) DR4G_NJ(3) DR4G_NJ(4) DR4G_NJ(5) DR4G_NJ(6) DR4G_NJ(7) DR4G_NJ(8)
     DR4G_NJ(9) DR4G_NJ(10) DR4G_NJ(11) DR4G_NJ(12) DR4G_NJ(13) DR4G_NJ(14) DR4G_NJ(15) DR4G_NJ(16)
 #undef DR4G_NJ

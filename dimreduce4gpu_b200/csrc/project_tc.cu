@@ -82,7 +82,7 @@ template <int KP>
 __global__ void __launch_bounds__(PT_THREADS, 1)
 project_tc_kernel(const float* __restrict__ X, long long n, int d, int k, const float* __restrict__ mean,
                   const uint8_t* __restrict__ bimg, const float* __restrict__ sigma, float* __restrict__ Z,
-                  float* __restrict__ U, int nstages, int vec4) {
+                  float* __restrict__ U, int nstages, int vec4, int ldz) {
   constexpr uint32_t B_BYTES = 2 * KP * 128;                  // [hi ; lo] slice of the components image
   constexpr uint32_t STAGE_BYTES = 2 * PT_A_BYTES + B_BYTES;
   constexpr uint32_t ACC_COLS = 2 * KP;                       // one accumulator buffer: [a1 b1 + a2 b1 | a1 b2]
@@ -266,8 +266,8 @@ project_tc_kernel(const float* __restrict__ X, long long n, int d, int k, const 
         ptx::tmem_ld_32x32(tbase + (uint32_t)(KP + part * 32), w);
         ptx::tmem_ld_wait();
         if (row < n) {
-          float* zr = Z + row * (long long)k + part * 32;
-          float* ur = U ? U + row * (long long)k + part * 32 : nullptr;
+          float* zr = Z + row * (long long)ldz + part * 32;      // ldz: row pitch of Z / U (>= k: a column slice of wider scores)
+          float* ur = U ? U + row * (long long)ldz + part * 32 : nullptr;
 #pragma unroll
           for (int j = 0; j < 32; j += 4) {
             const int m = part * 32 + j;
@@ -309,7 +309,7 @@ project_tc_kernel(const float* __restrict__ X, long long n, int d, int k, const 
 
 template <int KP>
 void launch_kp(Ctx& c, const float* dX, long long n, int d, int k, const float* dmean, const uint8_t* img, const float* dw,
-               float* dZ, float* dU) {
+               float* dZ, float* dU, int ldz) {
   constexpr uint32_t stage = 2 * PT_A_BYTES + 2 * KP * 128;
   constexpr uint32_t land = PT_PF * PT_LAND_BYTES;
   int nstages = (int)((225u * 1024u - land) / stage);   // 3 / 2 / 2 operand stages at KP = 32 / 64 / 128
@@ -320,9 +320,9 @@ void launch_kp(Ctx& c, const float* dX, long long n, int d, int k, const float* 
     DR4G_CUDA(cudaFuncSetAttribute(project_tc_kernel<KP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const long long ntiles = (n + PT_ROWS - 1) / PT_ROWS;
   const int grid = (int)(ntiles < c.sm_count ? ntiles : c.sm_count);
-  const int vec4 = (k % 4) == 0 && (reinterpret_cast<uintptr_t>(dZ) & 15) == 0 && (!dU || (reinterpret_cast<uintptr_t>(dU) & 15) == 0) &&
+  const int vec4 = (k % 4) == 0 && (ldz % 4) == 0 && (reinterpret_cast<uintptr_t>(dZ) & 15) == 0 && (!dU || (reinterpret_cast<uintptr_t>(dU) & 15) == 0) &&
                    (!dw || (reinterpret_cast<uintptr_t>(dw) & 15) == 0);
-  project_tc_kernel<KP><<<grid, PT_THREADS, smem, c.stream>>>(dX, n, d, k, dmean, img, dw, dZ, dU, nstages, vec4);
+  project_tc_kernel<KP><<<grid, PT_THREADS, smem, c.stream>>>(dX, n, d, k, dmean, img, dw, dZ, dU, nstages, vec4, ldz);
 }
 
 }  // namespace
@@ -335,7 +335,8 @@ bool project_tc_eligible(const Ctx& c, const float* dX, long long n, int d, int 
 }
 
 void launch_project_tc(Ctx& c, const float* dX, long long n, int d, int k, const float* dQ, const float* dmean,
-                       const float* dw, float* dZ, float* dU) {
+                       const float* dw, float* dZ, float* dU, int ldz) {
+  if (ldz <= 0) ldz = k;
   const int KP = k <= 32 ? 32 : (k <= 64 ? 64 : 128);
   const int nch = (d + PT_KC - 1) / PT_KC;
   const size_t img_bytes = (size_t)nch * 2 * KP * 128;
@@ -353,9 +354,9 @@ void launch_project_tc(Ctx& c, const float* dX, long long n, int d, int k, const
   project_prep_kernel<<<nch, 256, 0, c.stream>>>(dQ, d, k, KP, img);
   const float* sg = (dU && dw) ? dw : nullptr;
   float* du = (dU && dw) ? dU : nullptr;
-  if (KP == 32) launch_kp<32>(c, dX, n, d, k, dmean, img, sg, dZ, du);
-  else if (KP == 64) launch_kp<64>(c, dX, n, d, k, dmean, img, sg, dZ, du);
-  else launch_kp<128>(c, dX, n, d, k, dmean, img, sg, dZ, du);
+  if (KP == 32) launch_kp<32>(c, dX, n, d, k, dmean, img, sg, dZ, du, ldz);
+  else if (KP == 64) launch_kp<64>(c, dX, n, d, k, dmean, img, sg, dZ, du, ldz);
+  else launch_kp<128>(c, dX, n, d, k, dmean, img, sg, dZ, du, ldz);
   c.launches += 2;
   DR4G_CUDA(cudaGetLastError());
 }

@@ -34,7 +34,9 @@ def _problem(n, d, k, seed):
 # one tile, a single row, ragged last tile, d not a multiple of 16, every accumulator-tile count class (k = 1 .. 128),
 # config 5's shape (d = 4096, k = 100), more tiles than SMs
 SHAPES = [(128, 64, 32), (1, 8, 4), (100, 100, 12), (5000, 256, 32), (3001, 4096, 100), (2000, 322, 7), (999, 130, 128),
-          (40000, 64, 1), (30000, 512, 64), (777, 1000, 57)]
+          (40000, 64, 1), (30000, 512, 64), (777, 1000, 57),
+          # k > 128: column slices; odd d: zero-padded chunk copies
+          (4000, 256, 130), (3001, 333, 100), (20000, 99, 10), (2500, 1001, 200)]
 
 
 @pytest.mark.parametrize("n,d,k", SHAPES)

@@ -32,7 +32,9 @@ def _problem(n, d, k, seed):
 SHAPES = [(128, 64, 32), (1, 8, 4), (100, 100, 12), (5000, 256, 32), (70001, 512, 32), (3000, 1024, 64), (2000, 320, 100),
           (999, 132, 128), (40000, 64, 8), (300000, 256, 32),
           # k % 4 != 0 (scalar stores of the score rows): the usual small k of a PCA for plotting, C1's k = 10, k = 50
-          (20000, 256, 2), (5000, 100, 10), (7777, 512, 3), (30000, 784, 50), (1000, 64, 1), (2048, 128, 127)]
+          (20000, 256, 2), (5000, 100, 10), (7777, 512, 3), (30000, 784, 50), (1000, 64, 1), (2048, 128, 127),
+          # k > 128: column slices of the score matrices; d % 4 != 0: zero-padded chunk copies of X (both at once too)
+          (20000, 1024, 200), (9000, 512, 129), (20000, 1001, 32), (30000, 50, 10), (5000, 254, 200), (70000, 30, 5)]
 
 
 @pytest.mark.parametrize("n,d,k", SHAPES)
