@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py - PCA/TruncatedSVD fit throughput (rows/s) on B200, BASELINE.json's metric.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c4|c2|c3|c1|c5|c5s|r1|r2] [--impl reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c4|c2|c3|c1|c5|c5s|r1|r2|n1] [--impl reference]
 
 A step is one fit (the whole hot path: pilot shift, streamed Gram + column statistics, allreduce, centring,
 eigensolve, outputs) over one device-resident row shard of synthetic data.
@@ -12,7 +12,8 @@ eigensolve, outputs) over one device-resident row shard of synthetic data.
   c1: TruncatedSVD k=10 (default algorithm 'power'), 10,000 x 100 fp32                 (configs[0])
   c5: PCA k=100, 2,500,000 x 4096 fp64 per GPU = 20M x 4096 over 8 GPUs                (configs[4]); c5s: 2^18 rows of it
   r1, r2: the reference's own bench shapes (bench/run_benchmarks.py:45-53): 10,000 x 128 k=32 PCA, 50,000 x 256 k=64 TSVD power
-At N = 1 the secondary workloads (c2, c3, c1, r1, r2, c5s) run short in the same process and are attached under
+  n1: PCA k=8, 2^24 x 32 fp32: a narrow input (HBM-bound, AI = 16 flop/B), streamed with its rows folded 8-fold
+At N = 1 the secondary workloads (c2, c3, c1, r1, r2, n1, c5s) run short in the same process and are attached under
 "also".  N > 1: one process per GPU (torchrun), rows sharded, one NCCL allreduce of the d x d partials per fit, weak
 scaling (fixed shard per GPU).  Prints ONE JSON line on rank 0.
 `--impl reference` times the reference's own CPU backend (oracle/_ref/libdimreduce4cpu.so, else the numpy
@@ -50,8 +51,10 @@ WORKLOADS = {
                name="PCA cusolver k=32 10000x128 fp32 (reference bench/run_benchmarks.py:50)"),
     "r2": dict(kind="tsvd", n=50_000, d=256, k=64, algorithm="power", dtype="f32",
                name="TruncatedSVD power k=64 50000x256 fp32 (reference bench/run_benchmarks.py:51)"),
+    "n1": dict(kind="pca", n=2**24, d=32, k=8, algorithm="cusolver", dtype="f32",
+               name="PCA k=8 2^24x32 fp32 (narrow input: rows folded 8-fold into the 256-column pass)"),
 }
-ALSO_DEFAULT = ("c2", "c3", "c1", "r1", "r2", "c5s")
+ALSO_DEFAULT = ("c2", "c3", "c1", "r1", "r2", "n1", "c5s")
 
 
 def _peaks() -> dict:
@@ -224,7 +227,7 @@ def issued_factor(path: str, d: int) -> float:
     return 0.0
 
 
-def roofline(wl: dict, path: str, stages: dict, ms_per_step: float, peaks: dict, workload_key: str) -> dict | None:
+def roofline(wl: dict, path: str, stages: dict, ms_per_step: float, peaks: dict, workload_key: str, fold: int = 0) -> dict | None:
     """Roofline of the dominant streamed kernel (the Gram pass) and of the whole fit.  Algorithmic work per row
     (SURVEY 8d / DESIGN.md 3): d*sizeof(T) bytes and 2*d^2 flops; one launch processes the whole shard.  Which bound
     binds is decided from the time each peak would need: HBM = bytes / measured copy bandwidth, tensor = flops the kernel
@@ -245,11 +248,14 @@ def roofline(wl: dict, path: str, stages: dict, ms_per_step: float, peaks: dict,
     else:
         peak_tf = peaks["tf32_tflops_sustained" if long_kernel else "tf32_tflops"]
         peak_name = "TF32 dense"
-        issued = issued_factor(path, d)
+        # a narrow input folded f-fold runs the d' = f d kernel on n / f rows: f times the issued work per algorithmic flop
+        issued = issued_factor(path, d * fold) * fold if fold else issued_factor(path, d)
     t_hbm = bytes_alg / (peaks["hbm_gbs"] * 1e9)
     t_tensor = issued * flops_alg / (peak_tf * 1e12) if issued else 0.0
     ach_tf, ach_gb = flops_alg / sec / 1e12, bytes_alg / sec / 1e9
-    if t_tensor > t_hbm:
+    # (folded narrow inputs: the regime is the algorithmic one, AI = d/2 flop/B far below the ridge - the tensor work
+    # the fold wastes on products of different rows is this implementation's choice and shows in tensor_pipe_frac)
+    if t_tensor > t_hbm and not fold:
         roof = dict(bound="tensor", achieved=ach_tf, peak=peak_tf, unit="TFLOP/s", frac=ach_tf / peak_tf)
     else:
         roof = dict(bound="hbm", achieved=ach_gb, peak=peaks["hbm_gbs"], unit="GB/s", frac=ach_gb / peaks["hbm_gbs"])
@@ -273,6 +279,8 @@ def roofline(wl: dict, path: str, stages: dict, ms_per_step: float, peaks: dict,
                 fit_frac=(flops_alg / step_s / 1e12 / peak_tf) if roof["bound"] == "tensor"
                 else (bytes_alg / step_s / 1e9 / peaks["hbm_gbs"]),
                 dominant_stage=dominant, dominant_stage_ms=stages[dominant])
+    if fold:
+        roof["row_fold"] = fold
     if not f64 and path.endswith("bf16x3"):
         b = peaks["bf16_tflops_sustained" if long_kernel else "bf16_tflops"]
         roof["frac_of_bf16_peak"] = ach_tf / b
@@ -374,7 +382,8 @@ def time_fit(torch, dist, ctx, wl, X, steps, warmup, world, sampler=None):
         for kk, v in (st or {}).items():
             stage_acc.setdefault(kk, []).append(v)
     stages = {kk: float(np.mean(v)) for kk, v in stage_acc.items()}
-    return dict(ms_total=ms_total, ms_per_step=per, launches=int(launches), stages=stages, out=out, mark=mark, step=step)
+    return dict(ms_total=ms_total, ms_per_step=per, launches=int(launches), stages=stages, out=out, mark=mark, step=step,
+                fold=ctx.last_fold)
 
 
 def run_e2e(torch, dist, ctx, wl, X, rank, world, dev, steps):
@@ -471,7 +480,7 @@ def run_also(torch, dist, ctx, keys, rank, world, dev, peaks) -> dict:
             entry = dict(workload=wl["name"], value=wl["n"] * world * (2 if heavy else 10) / (r["ms_total"] * 1e-3),
                          unit="rows/s", ms_per_step=r["ms_per_step"], steps=2 if heavy else 10, stage_ms=r["stages"],
                          gram_kernel=path, gpu_launches=r["launches"],
-                         roofline=roofline(wl, path, r["stages"], r["ms_per_step"], peaks, key))
+                         roofline=roofline(wl, path, r["stages"], r["ms_per_step"], peaks, key, r.get("fold", 0)))
             if wl["dtype"] == "f32":
                 entry["parity_check"] = parity_check(torch, dist, ctx, wl, X, r["out"], world)
             # transform (K7) on the same shard: Z = (X - mean) Q^T, device resident
@@ -512,7 +521,7 @@ def main() -> None:
     ap.add_argument("--gram-split", type=int, default=0, help="pair kernel: 0 auto (bf16x3), 1 3xTF32, 2 bf16x3")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e-steps", type=int, default=3)
-    ap.add_argument("--also", default="auto", help="comma list of secondary workloads, 'auto' (N=1: c2,c3,c1,r1,r2,c5s), 'none'")
+    ap.add_argument("--also", default="auto", help="comma list of secondary workloads, 'auto' (N=1: c2,c3,c1,r1,r2,n1,c5s), 'none'")
     args = ap.parse_args()
     wl = dict(WORKLOADS[args.workload])
     if args.impl == "reference":
@@ -585,7 +594,7 @@ def main() -> None:
         also = run_also(torch, dist, ctx, keys, rank, world, dev, peaks)
 
     if rank == 0:
-        roof = roofline(wl, path, stages, r["ms_per_step"], peaks, args.workload)
+        roof = roofline(wl, path, stages, r["ms_per_step"], peaks, args.workload, r.get("fold", 0))
         cpu = None
         if not args.no_cpu_baseline and world == 1:
             rows = _cpu_rows(wl, 400_000)

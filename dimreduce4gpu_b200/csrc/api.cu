@@ -260,6 +260,22 @@ static void allgather_f64(Ctx& c, const double* send, double* recv, size_t count
 
 constexpr int kOversample = 10;  // same block oversampling as the CPU backend's randomized path (src/cpu_backend.cpp:170)
 
+
+// Row folding of narrow fp32 inputs (finalize.cu): f consecutive rows are streamed as one row of f d <= 256 columns, so
+// the pass runs on the CTA-pair tcgen05 kernel at its best shape whatever d is (the single-CTA kernel needs the same
+// time per ROW for every d <= 128: 2.5 TB/s at d = 128, 0.8 at d = 32, 0.2 at d = 8; folded: 3.6 TB/s for all of them).
+// f d must keep the 16-byte row pitch, so d % 4 != 0 folds by multiples of 2 or 4 and needs no padded copy either.
+// Small inputs stay as they are (100,000 x 64: 54 us unfolded, 66 us folded).  0: do not fold.
+static int gram_fold_factor(const Ctx& c, const float* dX, long long n, int d) {
+  if (!c.fold || c.gram_path != 0 || d < 1 || d > 128) return 0;
+  if ((reinterpret_cast<uintptr_t>(dX) & 15) != 0) return 0;
+  if ((double)n * (double)d < 16777216.0) return 0;
+  const int step = d % 4 == 0 ? 1 : (d % 2 == 0 ? 2 : 4);
+  const int f = (256 / d) / step * step;
+  if (f < 2 || f * d <= 128) return 0;
+  if (n / f < 1 || !gram_tc_eligible(c, dX, n / f, f * d)) return 0;
+  return f;
+}
 template <typename T>
 static void fit_impl(Ctx& c, const T* dX, long long n_local, int d, int k, int center, const params& p, T* dQ,
                      T* dw, T* dev, T* devr, T* dmean, StreamFit* sf = nullptr, int phase = 0) {
@@ -293,9 +309,14 @@ static void fit_impl(Ctx& c, const T* dX, long long n_local, int d, int k, int c
   else
     need += up256(power_workspace_bytes(d, l)) + up256((size_t)lp * 8) + up256((size_t)lp * d * 8);
   need += up256((size_t)(exact ? dp : lp) * 8) + up256((size_t)k * 4) + 64 * 256;
+  // Tiny fp32 inputs (<= 1 MB: the reference's own test shapes, 4 x 3 ... 256 x 256) take the generic kernel - fp64
+  // products of the fp32 input, fp64 accumulation - instead of the tensor-core split: the pass is launch-bound either
+  // way, and the split's ~1e-5 of G shows where a rank-deficient input is reconstructed from ALL its components
+  // (tests/test_gpu_reference_suite.py: 2.1e-6 against scikit-learn's 7.5e-7 and the reference's 1.75 x bound).
+  const bool tiny = sizeof(T) == 4 && c.gram_path == 0 && (double)n_local * (double)d <= 262144.0;
   bool want_tc = false;
   if constexpr (sizeof(T) == 4)
-    want_tc = c.gram_path != 1 && gram_tc_eligible(c, reinterpret_cast<const float*>(dX), n_local, d);
+    want_tc = !tiny && c.gram_path != 1 && gram_tc_eligible(c, reinterpret_cast<const float*>(dX), n_local, d);
   if (want_tc) need += up256(gram_tc_workspace_bytes(c, d));
   bool want_f64 = false;
   if constexpr (sizeof(T) == 8)
@@ -305,11 +326,20 @@ static void fit_impl(Ctx& c, const T* dX, long long n_local, int d, int k, int c
   // not 16-byte aligned - rows without a 16-byte pitch): the pass runs over zero-padded CHUNK COPIES of X (row pitch dpad)
   // and the padded moments are cut back to d afterwards.  These shapes used to take the generic kernel: 36 GB/s at
   // 500,000 x 1001 fp32, 25x slower than d = 1000.
+  int fold = 0;
+  if constexpr (sizeof(T) == 4) {
+    if (phase != 2) fold = gram_fold_factor(c, reinterpret_cast<const float*>(dX), n_local, d);
+    if (fold) {
+      const size_t df = (size_t)fold * d;
+      need += up256(df * df * 8) + up256(2 * df * 8) + up256(df * 4) + up256(dd * 8) + up256((size_t)2 * d * 8) +
+              up256(gram_tc_workspace_bytes(c, (int)df)) + 2048;
+    }
+  }
   int dpad = 0;
   long long pad_rows = 0;
   // (fp64 with d <= 128 stays on the generic kernel: the 128-wide tiles of gram_f64 are mostly padding there and the
   // copy costs more than it saves - 1M x 99: 2.8 ms generic, 3.5 ms padded)
-  if (phase != 2 && !want_tc && !want_f64 && c.gram_path == 0 && n_local > 0 && d >= 2 && (sizeof(T) == 4 || d > 128)) {
+  if (phase != 2 && !fold && !tiny && !want_tc && !want_f64 && c.gram_path == 0 && n_local > 0 && d >= 2 && (sizeof(T) == 4 || d > 128)) {
     const int q4 = sizeof(T) == 4 ? 4 : 2;
     dpad = (d + q4 - 1) / q4 * q4;
     pad_rows = (long long)(((size_t)128 << 20) / ((size_t)dpad * sizeof(T)));
@@ -379,6 +409,40 @@ static void fit_impl(Ctx& c, const T* dX, long long n_local, int d, int k, int c
   bool used_tc = false;
   c.last_gram_kernel = 0;
   bool padded_done = false;
+  c.last_fold = 0;
+  if (fold > 0) {
+    if constexpr (sizeof(T) == 4) {
+      const int df = fold * d;
+      const long long nf = n_local / fold, tail = n_local - nf * fold;
+      const float* Xf = reinterpret_cast<const float*>(dX);
+      double* Gf = c.arena.take_n<double>((size_t)df * df);
+      double* sqf = c.arena.take_n<double>((size_t)2 * df);
+      float* shf = c.arena.take_n<float>(df);
+      double* Gt = c.arena.take_n<double>(dd);
+      double* sqt = c.arena.take_n<double>((size_t)2 * d);
+      void* ws = c.arena.take(gram_tc_workspace_bytes(c, df));
+      DR4G_CUDA(cudaMemsetAsync(sqf, 0, (size_t)2 * df * 8, c.stream));
+      const float* shf_arg = nullptr;
+      if (shift_arg) {
+        launch_tile_shift(c, reinterpret_cast<const float*>(shift_arg), d, fold, shf);
+        shf_arg = shf;
+      }
+      launch_gram_tc(c, Xf, nf, df, shf_arg, Gf, sqf, sqf + df, ws);
+      if (tail > 0) {   // the last rows do not fill a folded row: fp64 products on the generic kernel
+        DR4G_CUDA(cudaMemsetAsync(Gt, 0, dd * 8, c.stream));
+        DR4G_CUDA(cudaMemsetAsync(sqt, 0, (size_t)2 * d * 8, c.stream));
+        const float* Xt = Xf + (size_t)nf * df;
+        launch_colstats<float>(c, Xt, tail, d, reinterpret_cast<const float*>(shift_arg), sqt, sqt + d);
+        launch_gram_generic<float>(c, Xt, tail, d, reinterpret_cast<const float*>(shift_arg), Gt);
+        launch_mirror_upper(c, Gt, d);
+      }
+      launch_unfold_moments(c, Gf, sqf, sqf + df, d, fold, tail > 0 ? Gt : nullptr, tail > 0 ? sqt : nullptr,
+                            tail > 0 ? sqt + d : nullptr, G, s, q);
+      padded_done = true;
+      used_tc = true;
+      c.last_fold = fold;
+    }
+  }
   if (dpad > 0) {
     T* Xp = c.arena.take_n<T>((size_t)pad_rows * dpad);
     double* Gp = c.arena.take_n<double>((size_t)dpad * dpad);
@@ -915,6 +979,7 @@ int dr4g_set_option(dr4g_ctx* ctx, const char* key, double value) {
   else if (k == "jacobi_sweeps") ctx->jacobi_sweeps = (int)value;
   else if (k == "timing") ctx->timing = (int)value;
   else if (k == "eig_solver") ctx->eig_solver = (int)value;
+  else if (k == "fold") ctx->fold = (int)value;
   else fail("unknown option '%s'", key);
   DR4G_API_END
 }
@@ -1173,6 +1238,7 @@ int dr4g_stage_times(dr4g_ctx* ctx, double* ms, int n) {
 
 int dr4g_last_gram_path(dr4g_ctx* ctx) { return ctx ? ctx->last_gram_path : 0; }
 int dr4g_last_proj_path(dr4g_ctx* ctx) { return ctx ? ctx->last_proj_path : 0; }
+int dr4g_last_fold(dr4g_ctx* ctx) { return ctx ? ctx->last_fold : 0; }
 long long dr4g_launch_count(dr4g_ctx* ctx) { return ctx ? ctx->launches : 0; }
 
 }  // extern "C"

@@ -82,6 +82,8 @@ struct Ctx {
   int jacobi_sweeps = 30;
   int eig_solver = 0;         // exact path: 0 tridiagonal route (top-k), 1 blocked Jacobi (all pairs), 2 tridiagonal route without the cluster-resident T1
   int timing = 1;             // record per-stage events
+  int fold = 1;               // narrow fp32 inputs (d <= 128): stream f rows as one row of f d <= 256 columns (api.cu)
+  int last_fold = 0;          // fold factor of the last pass (0: not folded)
   // telemetry
   int last_gram_path = 0;
   int last_gram_kernel = 0;   // tcgen05 path: 1 single-CTA kernel (gram_tc.cu), 2 CTA-pair kernel 3xTF32, 3 CTA-pair kernel bf16x3 (gram_tc2.cu)
@@ -91,7 +93,7 @@ struct Ctx {
   size_t proj_cap = 0;
   void* pad_buf = nullptr;    // K7: zero-padded chunk copy of X + padded components / mean (shapes without a 16-byte row pitch)
   size_t pad_cap = 0;
-  int proj_path = 0;          // 0 auto (tcgen05 where eligible), 1 CUDA-core kernels only
+  int proj_path = 0;          // 0 auto (tensor cores where eligible, tiny fp32 inputs on CUDA cores), 1 CUDA-core kernels only, 2 tensor cores wherever eligible
   int last_proj_path = 0;     // 1 CUDA cores, 2 tcgen05, 3 fp64 DMMA
   // tensor-map encoder (driver entry point fetched lazily)
   void* encode_tiled = nullptr;
@@ -151,6 +153,10 @@ int jacobi_padded_dim(int d);
 size_t jacobi_workspace_bytes(int dp);
 void launch_jacobi(Ctx& c, double* dA, double* dV, int dp, double* dW, void* workspace, double tol, int max_sweeps);
 void launch_pad_copy(Ctx& c, const double* src, int d, double* dst, int dp);
+// row folding of narrow fp32 inputs (finalize.cu): shift tiled f times; moments of the folded problem -> G, s, q
+void launch_tile_shift(Ctx& c, const float* shift, int d, int f, float* out);
+void launch_unfold_moments(Ctx& c, const double* Gf, const double* sf, const double* qf, int d, int f, const double* Gt,
+                           const double* st, const double* qt, double* G, double* s, double* q);
 template <typename T>
 void launch_pad_rows(Ctx& c, const T* src, long long rows, int d, int dp, T* dst);   // rows x d -> rows x dp, zero pad
 void launch_unpad_moments(Ctx& c, const double* Gp, const double* sp, const double* qp, int d, int dp, double* G, double* s,

@@ -210,4 +210,47 @@ void launch_pad_copy(Ctx& c, const double* src, int d, double* dst, int dp) {
   DR4G_CUDA(cudaGetLastError());
 }
 
+// ---------------------------------------------------------------- row folding (narrow X, api.cu)
+// f consecutive rows of an n x d matrix read as ONE row of f d columns: the streamed kernels then see the 256-column
+// problem they are built for, whatever d is (their time per row does not depend on d <= 128, so d = 8 ran at 0.2 TB/s).
+// The Gram of the folded matrix holds G in its f diagonal d x d blocks (the other blocks are products of different
+// rows: ignored), the folded column statistics hold s and q in f pieces.
+__global__ void tile_shift_kernel(const float* __restrict__ shift, int d, int f, float* __restrict__ out) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e < f * d) out[e] = shift[e % d];
+}
+
+// G = sum_g Gf[g d + i][g d + j] (+ Gt: the rows that did not fill a folded row), s, q likewise; fixed summation order
+__global__ void unfold_moments_kernel(const double* __restrict__ Gf, const double* __restrict__ sf, const double* __restrict__ qf,
+                                      int d, int f, const double* __restrict__ Gt, const double* __restrict__ st,
+                                      const double* __restrict__ qt, double* __restrict__ G, double* __restrict__ s,
+                                      double* __restrict__ q) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+  if (j >= d) return;
+  const size_t df = (size_t)f * d;
+  double a = Gt ? Gt[(size_t)i * d + j] : 0.0;
+  for (int g = 0; g < f; ++g) a += Gf[((size_t)g * d + i) * df + (size_t)g * d + j];
+  G[(size_t)i * d + j] = a;
+  if (i == 0) {
+    double b = st ? st[j] : 0.0, cq = qt ? qt[j] : 0.0;
+    for (int g = 0; g < f; ++g) { b += sf[(size_t)g * d + j]; cq += qf[(size_t)g * d + j]; }
+    s[j] = b;
+    q[j] = cq;
+  }
+}
+
+void launch_tile_shift(Ctx& c, const float* shift, int d, int f, float* out) {
+  tile_shift_kernel<<<ceil_div(f * d, 256), 256, 0, c.stream>>>(shift, d, f, out);
+  c.launches++;
+  DR4G_CUDA(cudaGetLastError());
+}
+
+void launch_unfold_moments(Ctx& c, const double* Gf, const double* sf, const double* qf, int d, int f, const double* Gt,
+                           const double* st, const double* qt, double* G, double* s, double* q) {
+  dim3 grid(ceil_div(d, 128), d);
+  unfold_moments_kernel<<<grid, 128, 0, c.stream>>>(Gf, sf, qf, d, f, Gt, st, qt, G, s, q);
+  c.launches++;
+  DR4G_CUDA(cudaGetLastError());
+}
+
 }  // namespace dr4g

@@ -265,7 +265,10 @@ void launch_project(Ctx& c, const T* dX, long long n, int d, int k, const T* dQ,
   // d % 4 != 0, fp64 odd d, unaligned base) go through zero-padded chunk copies of X (pad_rows_kernel) with the
   // components and the mean padded alike.  Both used to fall to the CUDA-core kernels below (0.16 TB/s at k = 200,
   // 0.55 TB/s at d = 1001).
-  if (c.proj_path != 1 && k >= 1 && d >= 2 && (long long)n * d >= (1ll << 16)) {
+  // Tiny fp32 inputs (<= 1 MB, like the Gram pass in api.cu) stay on the CUDA-core kernels: plain fp32 FMAs (1e-7 of
+  // |Z|) instead of the two-term bf16 split (2e-6), at the same launch-bound time.
+  const bool tiny = sizeof(T) == 4 && c.proj_path == 0 && (double)n * (double)d <= 262144.0;
+  if (!tiny && c.proj_path != 1 && k >= 1 && d >= 2 && (long long)n * d >= (1ll << 16)) {
     constexpr int q4 = sizeof(T) == 4 ? 4 : 2;
     const bool in_place = (d % q4) == 0 && (reinterpret_cast<uintptr_t>(dX) & 15) == 0 && (reinterpret_cast<uintptr_t>(dQ) & 15) == 0;
     const int dp = (d + q4 - 1) / q4 * q4;
@@ -322,7 +325,7 @@ void launch_project(Ctx& c, const T* dX, long long n, int d, int k, const T* dQ,
     return;
   }
   if constexpr (sizeof(T) == 4) {
-    if (c.proj_path != 1 && project_tc_eligible(c, dX, n, d, k, dZ, (dU && dw) ? dU : nullptr)) {
+    if (!tiny && c.proj_path != 1 && project_tc_eligible(c, dX, n, d, k, dZ, (dU && dw) ? dU : nullptr)) {
       launch_project_tc(c, dX, n, d, k, dQ, dmean, dw, dZ, dU);
       c.last_proj_path = 2;
       return;

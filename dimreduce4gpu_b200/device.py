@@ -372,6 +372,11 @@ class DeviceContext:
         return {0: "none", 1: "generic_dmma", 2: "tcgen05", 3: "tcgen05_pair", 4: "tcgen05_pair_bf16x3", 5: "dmma_f64_128"}[int(self._lib.dr4g_last_gram_path(self._h))]
 
     @property
+    def last_fold(self) -> int:
+        """Row-fold factor of the last fit's streamed pass (0: the input was not folded)."""
+        return int(self._lib.dr4g_last_fold(self._h))
+
+    @property
     def last_proj_path(self) -> str:
         return {0: "none", 1: "cuda_cores", 2: "tcgen05", 3: "dmma_f64"}[int(self._lib.dr4g_last_proj_path(self._h))]
 

@@ -83,10 +83,14 @@ DR4G_EXPORT void dr4g_ctx_destroy(dr4g_ctx* ctx);
 DR4G_EXPORT int dr4g_ctx_set_stream(dr4g_ctx* ctx, void* cuda_stream);
 /* Block until everything enqueued on the context's stream is done; returns deferred errors. */
 DR4G_EXPORT int dr4g_sync(dr4g_ctx* ctx);
-/* Tunables / test hooks.  Keys: "gram_path" (0 auto, 1 generic DMMA kernel, 2 tcgen05 kernels, 3 tcgen05 single-CTA kernel only),
+/* Tunables / test hooks.  Keys: "gram_path" (0 auto - fp32 inputs of <= 262144 elements take the generic kernel, narrow ones
+ * are row-folded, see "fold" -, 1 generic DMMA kernel, 2 tcgen05 kernels, 3 tcgen05 single-CTA kernel only),
  * "power_min_dim" (min(n, d) <= this takes the exact path whatever params.algorithm says, default 256 as
  * src/cpu_backend.cpp:347; 0 = off),
- * "proj_path" (projection: 0 auto = tcgen05 where eligible, 1 CUDA-core kernels),
+ * "proj_path" (projection: 0 auto = tensor cores where eligible except fp32 inputs of <= 262144 elements, 1 CUDA-core kernels,
+ * 2 tensor cores wherever eligible),
+ * "fold" (1 = default: fp32 inputs with d <= 128 and n d >= 2^24 are streamed f rows at a time as rows of f d <= 256 columns;
+ * 0 = off),
  * "gram_split" (CTA-pair kernel operands: 0 auto = 2 bf16x3 on kind::f16, 1 = 3xTF32 on kind::tf32),
  * "flush_rows" (rows between TMEM accumulator flushes), "pilot_rows", "jacobi_tol", "jacobi_sweeps",
  * "eig_solver" (exact path: 0 tridiagonal route for the top k, 1 blocked Jacobi), "timing". */
@@ -191,6 +195,9 @@ DR4G_EXPORT int dr4g_stage_times(dr4g_ctx* ctx, double* ms, int n);
 DR4G_EXPORT int dr4g_last_gram_path(dr4g_ctx* ctx);
 /* Which projection kernel the last transform used: 1 CUDA cores (project.cu), 2 tcgen05 (project_tc.cu). */
 DR4G_EXPORT int dr4g_last_proj_path(dr4g_ctx* ctx);
+/* Row-fold factor of the last fit's streamed pass: narrow fp32 inputs (d <= 128, n d >= 2^24) are read as n/f rows of
+ * f d <= 256 columns so that the pass runs on the CTA-pair tcgen05 kernel (option "fold" = 0 switches it off); 0: not folded. */
+DR4G_EXPORT int dr4g_last_fold(dr4g_ctx* ctx);
 DR4G_EXPORT long long dr4g_launch_count(dr4g_ctx* ctx);
 
 #ifdef __cplusplus

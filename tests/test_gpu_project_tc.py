@@ -42,7 +42,7 @@ SHAPES = [(128, 64, 32), (1, 8, 4), (100, 100, 12), (5000, 256, 32), (70001, 512
 def test_project_tc_matches_fp64(n, d, k, centered):
     import torch
 
-    ctx = _ctx()
+    ctx = _ctx(2)   # tensor cores wherever eligible (auto keeps inputs of <= 1 MB on the CUDA-core kernel)
     X, Q, mean, sigma = _problem(n, d, k, 5 * n + d + k)
     Z, U = ctx.transform(X, Q, mean=mean if centered else None, singular_values=sigma, want_u=True)
     ctx.sync()
@@ -79,3 +79,14 @@ def test_ineligible_shapes_fall_back():
     ctx.sync()
     assert ctx.last_proj_path == "cuda_cores"
     np.testing.assert_allclose(Z.cpu().numpy(), ((X - mean) @ Q.T).cpu().numpy(), atol=2e-3)
+
+
+def test_tiny_inputs_stay_on_cuda_cores_at_fp32_accuracy():
+    """proj_path = 0 (auto): n d <= 262144 elements -> plain fp32 FMAs, 1e-6 of max|Z| (the bf16 split gives 2e-6 .. 5e-6)."""
+    ctx = _ctx(0)
+    X, Q, mean, sigma = _problem(200, 80, 16, 9)
+    Z = ctx.transform(X, Q, mean=mean)
+    ctx.sync()
+    assert ctx.last_proj_path == "cuda_cores"
+    Zr = (X.double() - mean.double()) @ Q.double().T
+    assert float((Z.double() - Zr).abs().max()) < 1e-6 * float(Zr.abs().max())
