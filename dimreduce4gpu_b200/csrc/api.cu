@@ -217,6 +217,7 @@ static void ctx_delete(CtxFull* c) {
   c->io.release();
   if (c->proj_buf) cudaFree(c->proj_buf);
   if (c->pad_buf) cudaFree(c->pad_buf);
+  if (c->fold_buf) cudaFree(c->fold_buf);
   c->stage.release();
   if (c->switch_ev) cudaEventDestroy(c->switch_ev);
   c->sf.release();

@@ -93,6 +93,7 @@ struct Ctx {
   size_t proj_cap = 0;
   void* pad_buf = nullptr;    // K7: zero-padded chunk copy of X + padded components / mean (shapes without a 16-byte row pitch)
   size_t pad_cap = 0;
+  void* fold_buf = nullptr;   // K7 on row-folded narrow inputs: block-diagonal components, tiled mean / sigma (fixed 160 KB)
   int proj_path = 0;          // 0 auto (tensor cores where eligible, tiny fp32 inputs on CUDA cores), 1 CUDA-core kernels only, 2 tensor cores wherever eligible
   int last_proj_path = 0;     // 1 CUDA cores, 2 tcgen05, 3 fp64 DMMA
   // tensor-map encoder (driver entry point fetched lazily)

@@ -255,11 +255,64 @@ void launch_project_f32(Ctx& c, const float* dX, long long n, int d, int k, cons
 
 static inline size_t up256(size_t b) { return (b + 255) / 256 * 256; }
 
+// ---------------------------------------------------------------- row folding of narrow fp32 inputs
+// f consecutive rows of X read as one row of f d columns, projected on the block-diagonal image of the components
+// (f k x f d): the scores of the folded row ARE the f score rows of the original ones, contiguous in memory, so Z and U
+// need no rearrangement.  The tensor-core kernel's time per row does not depend on d, so d = 8 ran at 0.84 TB/s and
+// d = 32 at 3.2; folded to 256 columns all of them stream at 4.8 TB/s (B200, tools/fold_proj_probe.py).
+__global__ void fold_components_kernel(const float* __restrict__ Q, const float* __restrict__ mean, const float* __restrict__ w,
+                                       int d, int k, int f, float* __restrict__ Qf, float* __restrict__ mf, float* __restrict__ wf) {
+  const int fd = f * d, fk = f * k;
+  for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < fk * fd; e += gridDim.x * blockDim.x) {
+    const int r = e / fd, col = e - r * fd;
+    const int g = r / k, j = r - g * k;
+    Qf[e] = (col / d == g) ? Q[(size_t)j * d + (col - g * d)] : 0.0f;
+  }
+  if (blockIdx.x == 0) {
+    for (int e = threadIdx.x; e < fd; e += blockDim.x) mf[e] = mean ? mean[e % d] : 0.0f;
+    for (int e = threadIdx.x; e < fk; e += blockDim.x) wf[e] = w ? w[e % k] : 0.0f;
+  }
+}
+
+static int project_fold_factor(const Ctx& c, const void* dX, long long n, int d, int k, const void* dZ, const void* dU) {
+  if (!c.fold || c.proj_path != 0 || d < 1 || d > 32 || k < 1 || k > d) return 0;
+  if (((reinterpret_cast<uintptr_t>(dX) | reinterpret_cast<uintptr_t>(dZ) | reinterpret_cast<uintptr_t>(dU)) & 15) != 0) return 0;
+  if ((double)n * (double)d < 16777216.0) return 0;
+  const int step = d % 4 == 0 ? 1 : (d % 2 == 0 ? 2 : 4);
+  int f = 256 / d < 128 / k ? 256 / d : 128 / k;
+  f = f / step * step;
+  if (f < 2 || f * d < 64) return 0;
+  return f;
+}
+
 template <typename T>
 void launch_project(Ctx& c, const T* dX, long long n, int d, int k, const T* dQ, const T* dmean, const T* dw,
                     T* dZ, T* dU) {
   if (n <= 0) return;
   c.last_proj_path = 1;
+  if constexpr (sizeof(T) == 4) {
+    const int f = project_fold_factor(c, dX, n, d, k, dZ, dU);
+    if (d <= 32) c.last_fold = f;
+    if (f > 1) {
+      const int fd = f * d, fk = f * k;
+      if (!c.fold_buf) DR4G_CUDA(cudaMalloc(&c.fold_buf, 128 * 256 * 4 + 256 * 4 + 128 * 4 + 1024));
+      float* Qf = static_cast<float*>(c.fold_buf);
+      float* mf = Qf + 128 * 256;
+      float* wf = mf + 256 + 64;
+      fold_components_kernel<<<64, 256, 0, c.stream>>>(dQ, dmean, dw, d, k, f, Qf, mf, wf);
+      c.launches++;
+      DR4G_CUDA(cudaGetLastError());
+      const long long nf = n / f, tail = n - nf * f;
+      launch_project<float>(c, dX, nf, fd, fk, Qf, dmean ? mf : nullptr, dw ? wf : nullptr, dZ, dU);
+      const int path = c.last_proj_path;
+      if (tail > 0)
+        launch_project<float>(c, dX + (size_t)nf * fd, tail, d, k, dQ, dmean, dw, dZ + (size_t)nf * fk,
+                              dU ? dU + (size_t)nf * fk : nullptr);
+      c.last_proj_path = path;
+      c.last_fold = f;
+      return;
+    }
+  }
   // Tensor-core / DMMA kernels: at most 128 components per launch - wider k goes through in column slices of the score
   // matrices (row pitch k), X being re-read from HBM once per slice; shapes whose rows have no 16-byte pitch (fp32
   // d % 4 != 0, fp64 odd d, unaligned base) go through zero-padded chunk copies of X (pad_rows_kernel) with the

@@ -195,8 +195,9 @@ DR4G_EXPORT int dr4g_stage_times(dr4g_ctx* ctx, double* ms, int n);
 DR4G_EXPORT int dr4g_last_gram_path(dr4g_ctx* ctx);
 /* Which projection kernel the last transform used: 1 CUDA cores (project.cu), 2 tcgen05 (project_tc.cu). */
 DR4G_EXPORT int dr4g_last_proj_path(dr4g_ctx* ctx);
-/* Row-fold factor of the last fit's streamed pass: narrow fp32 inputs (d <= 128, n d >= 2^24) are read as n/f rows of
- * f d <= 256 columns so that the pass runs on the CTA-pair tcgen05 kernel (option "fold" = 0 switches it off); 0: not folded. */
+/* Row-fold factor of the last streamed pass (fit, or transform of an input with d <= 32): narrow fp32 inputs with n d >= 2^24 are
+ * read as n/f rows of f d <= 256 columns - the fit (d <= 128) on the CTA-pair tcgen05 Gram kernel, the projection (d <= 32) against
+ * the block-diagonal image of the components; option "fold" = 0 switches it off.  0: not folded. */
 DR4G_EXPORT int dr4g_last_fold(dr4g_ctx* ctx);
 DR4G_EXPORT long long dr4g_launch_count(dr4g_ctx* ctx);
 

@@ -131,3 +131,39 @@ def test_legacy_symbol_folds_its_chunks():
     Co, Zo = O.svd_flip_v(est.components_, Z)
     assert O.max_principal_angle(Cr, Co) < 1e-2
     assert np.max(np.abs(Zr - Zo)) < 5e-2 * ref.singular_values[0] / np.sqrt(n)   # 5 % of a typical leading score
+
+
+@pytest.mark.parametrize("n,d,k,f", [(2097152 + 5, 8, 2, 32), (524288 + 3, 32, 8, 8), (700001, 24, 5, 10), (5600003, 3, 2, 64),
+                                     (16777216 + 9, 1, 1, 128), (1048576 + 1, 16, 16, 8), (300000, 64, 8, 0)])
+@pytest.mark.parametrize("centered", [True, False])
+def test_folded_projection_matches_fp64_and_the_unfolded_kernel(n, d, k, f, centered):
+    """K7 on narrow inputs (d <= 32): f rows against the block-diagonal image of the components; Z and U land where the
+    unfolded kernel puts them."""
+    import torch
+
+    import dimreduce4gpu_b200 as pkg
+
+    g = torch.Generator(device="cuda").manual_seed(n + d + k)
+    X = _data(n, d, 3 * n + d, offset=True)
+    Q, _ = torch.linalg.qr(torch.randn(d, k, device="cuda", generator=g, dtype=torch.float64))
+    Q = Q.T.contiguous().float()
+    mean = X[:100000].mean(0).contiguous() if centered else None
+    sigma = torch.linspace(3.0, 1.0, k, device="cuda")
+    ctx = pkg.DeviceContext(0)
+    Z, U = ctx.transform(X, Q, mean=mean, singular_values=sigma, want_u=True)
+    ctx.sync()
+    assert ctx.last_fold == f, f"fold factor {ctx.last_fold}, expected {f}"
+    assert ctx.last_proj_path == "tcgen05"
+    ctx.set_option("fold", 0)
+    Z0, U0 = ctx.transform(X, Q, mean=mean, singular_values=sigma, want_u=True)
+    ctx.sync()
+    m = min(n, 300000)
+    rows = torch.cat([torch.arange(m, device="cuda"), torch.arange(n - 1000, n, device="cuda")])   # head and the tail rows
+    Zr = (X[rows].double() - (mean.double() if centered else 0.0)) @ Q.double().T
+    scale = float(Zr.abs().max())
+    ez = float((Z[rows].double() - Zr).abs().max()) / scale
+    eu = float((U[rows].double() - Zr / sigma.double()).abs().max()) / scale
+    e0 = float((Z - Z0).abs().max()) / scale
+    msg = f"n={n} d={d} k={k} f={f}: Z {ez:.2e}, U {eu:.2e} vs fp64; folded vs unfolded {e0:.2e}"
+    assert ez < 2e-5 and eu < 2e-5 and e0 < 2e-5, msg
+    assert float((U - U0).abs().max()) / scale < 2e-5, msg
