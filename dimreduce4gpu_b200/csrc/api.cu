@@ -1223,6 +1223,17 @@ int dr4g_eigh_topk_double(dr4g_ctx* ctx, double* dA, int d, int k, double* dW, d
   DR4G_API_END
 }
 
+int dr4g_eigh_topk_static_double(dr4g_ctx* ctx, double* dA, int d, int k, double* dW, double* dVt) {
+  DR4G_API_BEGIN
+  if (!ctx || !dA || !dW || !dVt) fail("dr4g_eigh_topk_static_double: null argument");
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  DeviceGuard g(ctx->device);
+  launch_eigh_topk_static(*ctx, dA, d, k, dW, dVt);   // no arena, no cudaMalloc / cudaFree: workspace is a static device array
+  DR4G_API_END
+}
+
+int dr4g_eigh_topk_static_max_d(void) { return eigh_topk_static_max_d(); }
+
 int dr4g_stage_times(dr4g_ctx* ctx, double* ms, int n) {
   if (!ctx || !ms || !ctx->stage_valid) return 0;
   DeviceGuard g(ctx->device);

@@ -168,6 +168,9 @@ void launch_unpad_moments(Ctx& c, const double* Gp, const double* sp, const doub
 // the k largest eigenvalues in descending order, dVt (k x d) the unit eigenvectors in rows.
 size_t eigh_topk_workspace_bytes(int d, int k);
 void launch_eigh_topk(Ctx& c, double* dA, int d, int k, double* dW, double* dVt, void* workspace);
+// the same with the workspace in a file-scope device array (no allocation at call time; d <= eigh_topk_static_max_d())
+void launch_eigh_topk_static(Ctx& c, double* dA, int d, int k, double* dW, double* dVt);
+int eigh_topk_static_max_d();
 
 // K5: subspace iteration on the d x d Gram/covariance ("power" algorithm).
 size_t power_workspace_bytes(int d, int l);

@@ -21,6 +21,7 @@
 // over the rows and one barrier.
 #include <cfloat>
 #include <cstdlib>
+#include <mutex>
 
 #include "common.cuh"
 #include "ptx_sm100.cuh"
@@ -1226,6 +1227,45 @@ void launch_eigh_topk(Ctx& c, double* dA, int d, int k, double* dW, double* dVt,
   else backtransform_kernel<<<k, 256, bt_smem, c.stream>>>(Vh, tau, d, k, dVt);
   c.launches += 5;
   DR4G_CUDA(cudaGetLastError());
+}
+
+// ---------------------------------------------------------------- allocation-free variant (dr4g_eigh_topk_static_double)
+// For callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it): the
+// same T1-T4 pipeline with its workspace (reflectors, tridiagonal, multisection values, inverse-iteration vectors) in a
+// file-scope device array instead of the context's grow-only arena.  d <= kStaticEighMaxD; every GPU that loads the
+// library holds the array (1,088 KiB) until exit.  All calls share it: calls that overlap on the GPU race.  Nothing in
+// it has to start at zero except the grid-barrier counter, which launch_eigh_topk clears itself on the stream.
+constexpr int kStaticEighMaxD = 256;
+constexpr size_t kStaticEighBytes = (size_t)2 * kStaticEighMaxD * kStaticEighMaxD * 8 + 65536;
+static __device__ __align__(256) unsigned char g_eigh_static_ws[kStaticEighBytes];
+
+int eigh_topk_static_max_d() { return kStaticEighMaxD; }
+
+void launch_eigh_topk_static(Ctx& c, double* dA, int d, int k, double* dW, double* dVt) {
+  if (d < 1 || d > kStaticEighMaxD)
+    fail("dr4g_eigh_topk_static_double: d=%d is beyond the static workspace (d <= %d); use dr4g_eigh_topk_double", d, kStaticEighMaxD);
+  if (k < 1 || k > d) fail("dr4g_eigh_topk_static_double: bad k=%d for d=%d", k, d);
+  if (eigh_topk_workspace_bytes(d, k) > kStaticEighBytes)
+    fail("dr4g_eigh_topk_static_double: d=%d k=%d needs %zu bytes, the static workspace has %zu", d, k,
+         eigh_topk_workspace_bytes(d, k), kStaticEighBytes);
+  // In host code the array's name is a host-side stand-in, not a device address: the address comes from
+  // cudaGetSymbolAddress, once per device, with that device current (the caller's DeviceGuard).
+  constexpr int kMaxDev = 64;
+  static void* addr[kMaxDev] = {};
+  static std::mutex mu;
+  if (c.device < 0 || c.device >= kMaxDev) fail("dr4g_eigh_topk_static_double: device index %d out of range", c.device);
+  void* ws = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(mu);
+    if (!addr[c.device]) {
+      void* p = nullptr;
+      DR4G_CUDA(cudaGetSymbolAddress(&p, g_eigh_static_ws));
+      if (!p) fail("dr4g_eigh_topk_static_double: cudaGetSymbolAddress returned a null address");
+      addr[c.device] = p;
+    }
+    ws = addr[c.device];
+  }
+  launch_eigh_topk(c, dA, d, k, dW, dVt, ws);
 }
 
 }  // namespace dr4g

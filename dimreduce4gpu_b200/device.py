@@ -357,6 +357,21 @@ class DeviceContext:
                "dr4g_eigh_topk_double")
         return w, Vt
 
+    def eigh_topk_static(self, work, k: int, w, Vt) -> None:
+        """dr4g_eigh_topk_static_double: eigh_topk with the workspace in the library's static device array - nothing is
+        allocated, here or in the library.  `work` (d x d float64, d <= 256) is DESTROYED; `w` (k,) and `Vt` (k, d) are
+        caller-provided float64 CUDA tensors.  Calls that overlap on the GPU share the workspace and race."""
+        for name, t in (("work", work), ("w", w), ("Vt", Vt)):
+            _need_cuda_contig(t, name, self.device)
+        d = work.shape[0]
+        if work.dim() != 2 or work.shape[1] != d or tuple(w.shape) != (k,) or tuple(Vt.shape) != (k, d):
+            raise ValueError("work must be (d, d), w (k,), Vt (k, d)")
+        if str(work.dtype) != "torch.float64" or str(w.dtype) != "torch.float64" or str(Vt.dtype) != "torch.float64":
+            raise ValueError("work, w, Vt must be float64")
+        self._on_torch_stream()
+        _check(self._lib.dr4g_eigh_topk_static_double(self._h, work.data_ptr(), d, int(k), w.data_ptr(), Vt.data_ptr()),
+               "dr4g_eigh_topk_static_double")
+
     # ------------------------------------------------------------------ telemetry
     def stage_times(self) -> Optional[dict]:
         """Per-stage device ms of the last fit (call after sync)."""

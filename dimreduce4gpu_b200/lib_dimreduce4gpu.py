@@ -65,6 +65,8 @@ def _bind(lib: ctypes.CDLL) -> None:
     lib.dr4g_comm_world.argtypes, lib.dr4g_comm_world.restype = [vp], ci
     lib.dr4g_eigh_double.argtypes, lib.dr4g_eigh_double.restype = [vp, vp, ci, vp, vp], ci
     lib.dr4g_eigh_topk_double.argtypes, lib.dr4g_eigh_topk_double.restype = [vp, vp, ci, ci, vp, vp], ci
+    lib.dr4g_eigh_topk_static_double.argtypes, lib.dr4g_eigh_topk_static_double.restype = [vp, vp, ci, ci, vp, vp], ci
+    lib.dr4g_eigh_topk_static_max_d.argtypes, lib.dr4g_eigh_topk_static_max_d.restype = [], ci
     lib.dr4g_stage_times.argtypes, lib.dr4g_stage_times.restype = [vp, c_double_p, ci], ci
     lib.dr4g_last_gram_path.argtypes, lib.dr4g_last_gram_path.restype = [vp], ci
     lib.dr4g_last_proj_path.argtypes, lib.dr4g_last_proj_path.restype = [vp], ci
@@ -83,6 +85,7 @@ EXPORTED_SYMBOLS = (
     "dr4g_inverse_transform_float", "dr4g_inverse_transform_double", "dr4g_colstats_float",
     "dr4g_colstats_double", "dr4g_gram_float", "dr4g_gram_double", "dr4g_eigh_double", "dr4g_eigh_topk_double", "dr4g_stage_times",
     "dr4g_last_gram_path", "dr4g_last_proj_path", "dr4g_last_fold", "dr4g_launch_count",
+    "dr4g_eigh_topk_static_double", "dr4g_eigh_topk_static_max_d",
     "dr4g_fit_transform_host_float", "dr4g_fit_transform_host_double",
     "dr4g_csr_to_dense_float", "dr4g_csr_to_dense_double",
     "dr4g_partial_fit_float", "dr4g_partial_fit_double", "dr4g_partial_fit_finalize_float",

@@ -185,6 +185,16 @@ DR4G_EXPORT int dr4g_eigh_double(dr4g_ctx* ctx, double* dA, int d, double* dW, d
  *             route the exact fit uses (replaces cusolverDn?syevd, src/matrix.cu:231-273): dW gets k
  *             eigenvalues in descending order, dVt (k x d, row-major) unit eigenvectors in rows. */
 DR4G_EXPORT int dr4g_eigh_topk_double(dr4g_ctx* ctx, double* dA, int d, int k, double* dW, double* dVt);
+/*   eigh_topk_static: dr4g_eigh_topk_double WITHOUT any allocation at call time.  No counterpart in the reference; added
+ *             for callers that cannot call cudaMalloc (CUDA graph capture, tight
+ *             serving loops, harnesses that forbid it).  The workspace (reflectors, tridiagonal, inverse-iteration
+ *             vectors) lives in a file-scope device array of 1,088 KiB that every GPU loading the library holds until
+ *             exit, so d <= dr4g_eigh_topk_static_max_d() = 256 (any 1 <= k <= d); larger d is rejected with an error
+ *             (dr4g_last_error).  Same inputs, outputs and results as dr4g_eigh_topk_double; asynchronous on the
+ *             context's stream.  All calls on a device share the array: calls that overlap on the GPU (two contexts /
+ *             streams) race - serialise them.  Calls no cudaMalloc / cudaFree / allocating routine. */
+DR4G_EXPORT int dr4g_eigh_topk_static_double(dr4g_ctx* ctx, double* dA, int d, int k, double* dW, double* dVt);
+DR4G_EXPORT int dr4g_eigh_topk_static_max_d(void);
 
 /* Per-stage device times (ms) of the last dr4g_fit_* on this context, valid after dr4g_sync:
  * [0] pilot shift, [1] Gram + column stats, [2] partial reduce + allreduce + centring,
