@@ -21,7 +21,13 @@ for r0 in range(0, n, slab):
 X *= torch.linspace(1, 3, d, device="cuda", dtype=dt)
 X += 0.5
 shift = X[:4096].mean(0).contiguous()
-if what in ("gram", "gram64"):
+if what == "fit":   # `fit N D K`: the whole PCA fit 3 times (narrow inputs: the row-folded pass)
+    k = int(sys.argv[4])
+    for _ in range(3):
+        r = ctx.fit(X, k, center=True, algorithm="cusolver")
+    ctx.sync()
+    print(what, n, d, k, ctx.last_gram_path, "fold", ctx.last_fold, float(r["singular_values"][0]))
+elif what in ("gram", "gram64"):
     if what == "gram":
         ctx.set_option("gram_path", 2)
         if len(sys.argv) > 4:
