@@ -684,7 +684,7 @@ bisect_kernel(const double* __restrict__ diag, const double* __restrict__ off, i
 //     of samples per feature is one big loose cluster (config 5: 100 eigenvalues 3e-4 ||T|| apart): processed
 //     sequentially the stage took 180 ms at d = 4096.
 // Z: k x d (rows), unit vectors of T.
-constexpr int kInvThreads = 128;
+constexpr int kInvThreads = 512;   // thread 0 carries the tridiagonal solves; the others matter in the Gram-Schmidt passes of tight clusters
 constexpr double kTightGap = 1e-7, kLooseGap = 1e-3;
 
 __device__ __forceinline__ double inv_block_sum(double v, double* red) {
@@ -726,6 +726,7 @@ invit_kernel(const double* __restrict__ diag, const double* __restrict__ off, in
   double* dg0 = z + d;      // diag - x (read-only during the factorisation)
   double* of0 = dg0 + d;    // off
   int* piv = reinterpret_cast<int*>(of0 + d);
+  double* coef = of0 + d + (d + 1) / 2;   // behind piv (d ints): Gram-Schmidt coefficients of a tight cluster, < k of them
   __shared__ double red[kInvThreads / 32];
   const int tid = threadIdx.x;
   const double eps = DBL_EPSILON;
@@ -805,13 +806,47 @@ invit_kernel(const double* __restrict__ diag, const double* __restrict__ off, in
         }
       }
       __syncthreads();
-      // re-orthogonalise against the cluster's earlier vectors, normalise
-      for (int p = j0; p < j; ++p) {
-        double dot = 0.0;
-        for (int i = tid; i < d; i += kInvThreads) dot += z[i] * Z[(size_t)p * d + i];
-        dot = inv_block_sum(dot, red);
-        for (int i = tid; i < d; i += kInvThreads) z[i] -= dot * Z[(size_t)p * d + i];
-        __syncthreads();
+      // re-orthogonalise against the cluster's earlier vectors, normalise.  Classical Gram-Schmidt, twice ("twice is
+      // enough"): all j - j0 coefficients of a pass are formed at once, one warp per earlier vector with four vectors in
+      // flight, then one update sweep - the modified Gram-Schmidt loop this replaces paid an L2 round trip and two block
+      // barriers per earlier vector and iteration (k = d = 256 on a rank-deficient matrix, a zero cluster of ~170: 43 ms)
+      if (j > j0) {
+        const int lane = tid & 31, warp = tid >> 5;
+        constexpr int NW = kInvThreads / 32;
+        for (int pass = 0; pass < 2; ++pass) {
+          for (int p0 = j0 + 4 * warp; p0 < j; p0 += 4 * NW) {
+            double acc[4] = {0.0, 0.0, 0.0, 0.0};
+            for (int i = lane; i < d; i += 32) {
+              const double zi = z[i];
+#pragma unroll
+              for (int u = 0; u < 4; ++u)
+                if (p0 + u < j) acc[u] = fma(zi, Z[(size_t)(p0 + u) * d + i], acc[u]);
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+              for (int u = 0; u < 4; ++u) acc[u] += __shfl_xor_sync(0xffffffffu, acc[u], o);
+            }
+            if (lane == 0) {
+#pragma unroll
+              for (int u = 0; u < 4; ++u) if (p0 + u < j) coef[p0 + u - j0] = acc[u];
+            }
+          }
+          __syncthreads();
+          for (int i = tid; i < d; i += kInvThreads) {
+            double a0 = z[i], a1 = 0.0, a2 = 0.0, a3 = 0.0;
+            int p = j0;
+            for (; p + 4 <= j; p += 4) {
+              a0 = fma(-coef[p - j0], Z[(size_t)p * d + i], a0);
+              a1 = fma(-coef[p + 1 - j0], Z[(size_t)(p + 1) * d + i], a1);
+              a2 = fma(-coef[p + 2 - j0], Z[(size_t)(p + 2) * d + i], a2);
+              a3 = fma(-coef[p + 3 - j0], Z[(size_t)(p + 3) * d + i], a3);
+            }
+            for (; p < j; ++p) a0 = fma(-coef[p - j0], Z[(size_t)p * d + i], a0);
+            z[i] = (a0 + a1) + (a2 + a3);
+          }
+          __syncthreads();
+        }
       }
       double mx = 0.0;
       for (int i = tid; i < d; i += kInvThreads) mx = fmax(mx, fabs(z[i]));
@@ -1212,9 +1247,9 @@ void launch_eigh_topk(Ctx& c, double* dA, int d, int k, double* dW, double* dVt,
     DR4G_CUDA(cudaFuncSetAttribute(bisect_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bs_smem));
   bisect_kernel<<<k, kBsThreads, bs_smem, c.stream>>>(diag, off, d, k, lam, info);
   // T3
-  const size_t iv_smem = (size_t)6 * d * sizeof(double) + (size_t)d * sizeof(int);
+  const size_t iv_smem = (size_t)6 * d * sizeof(double) + (size_t)((d + 1) / 2) * sizeof(double) + (size_t)k * sizeof(double);
   if (iv_smem > 227 * 1024)
-    fail("eigh_topk: d=%d needs %zu bytes of shared memory for the inverse iteration (limit 227 KB, d <= 4469)", d, iv_smem);
+    fail("eigh_topk: d=%d k=%d needs %zu bytes of shared memory for the inverse iteration (limit 227 KB)", d, k, iv_smem);
   static PerDeviceMax iv_smem_set;
   if (iv_smem > 48 * 1024 && iv_smem_set.need(c.device, iv_smem))
     DR4G_CUDA(cudaFuncSetAttribute(invit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)iv_smem));
