@@ -347,7 +347,7 @@ tridiag_cluster_kernel(const double* __restrict__ A, int d, double* __restrict__
   }
   cluster_barrier();  // also orders the zero-initialisation of pl before any remote push
 
-  double tprev = 0.0;
+  double tprev = 0.0, sprev = 0.0;   // tau and 1 / (x0 - beta) of reflector s-1
   int qfirst = 0, owner = 0, oslot = 0;   // row s belongs to CTA `owner`, slot `oslot` (s = owner + cs oslot)
   const int nslots = (d - rank + cs - 1) / cs;   // own rows: rank, rank + cs, ...
   for (int s = 0; s < d - 1; ++s) {
@@ -368,43 +368,88 @@ tridiag_cluster_kernel(const double* __restrict__ A, int d, double* __restrict__
     // published global copy cost ~1100 cycles per step here)
     double* row = rowp + (size_t)(s & 1) * d;
     TRI_TRACE(1);
-    double pv = 0.0;
-    for (int c = s + tid; c < d; c += kTriThreads) pv += pcur[c] * vn[c];
-    pv = tri_block_sum1(pv, red2, par);
-    TRI_TRACE(2);
-    const double kk = 0.5 * tprev * pv;
-    // v <- previous reflector, w = p - kk v, corrected row r = row - v_s w - w_s v: one sweep, every
-    // thread needs only its own column besides the scalars v_s and w_s
-    const double vs = vn[s], ws = pcur[s] - kk * vs;
-    double nrm2 = 0.0;
-    for (int c = tid; c < d; c += kTriThreads) {
-      const double vv = vn[c];
-      const double wc = c >= s ? pcur[c] - kk * vv : 0.0;
-      v[c] = vv;
-      w[c] = wc;
-      if (c >= s) {
-        const double r = row[c] - vs * wc - ws * vv;
-        row[c] = r;
-        if (c > s + 1) nrm2 += r * r;
+    double t = 0.0, beta = 0.0, scale = 0.0;
+    if constexpr (REG) {
+      // The reflector is kept UN-normalised in `vn`: u = corrected row s from column s+1 on, v' = scale (u - beta e_{s+1}).
+      // Everything the rows phase needs from it is linear in u, so the rows phase starts right behind the barrier of the
+      // norm's reduction and the chain sqrt -> beta -> tau, 1 / (x0 - beta) (~300 dependent cycles) runs under its loads;
+      // the normalised reflector is formed one step later, on the fly, where it is read as `v` (saves the sweep that
+      // wrote it and one CTA barrier per step).  vn holds u_{s-1} here; sprev = its scale; its unit entry is column s.
+      auto vprev_at = [&](int c) { return c == s ? (s > 0 ? 1.0 : 0.0) : (c > s ? vn[c] * sprev : 0.0); };
+      double pv = 0.0;
+      for (int c = s + tid; c < d; c += kTriThreads) pv += pcur[c] * vprev_at(c);
+      pv = tri_block_sum1(pv, red2, par);
+      TRI_TRACE(2);
+      const double kk = 0.5 * tprev * pv;
+      const double vs = s > 0 ? 1.0 : 0.0, ws = pcur[s] - kk * vs;
+      double nrm2 = 0.0;
+      for (int c = tid; c < d; c += kTriThreads) {
+        const double vv = vprev_at(c);
+        const double wc = c >= s ? pcur[c] - kk * vv : 0.0;
+        v[c] = vv;
+        w[c] = wc;
+        double u = 0.0;
+        if (c >= s) {
+          const double r = row[c] - vs * wc - ws * vv;
+          row[c] = r;
+          if (c > s) u = r;
+          if (c > s + 1) nrm2 += r * r;
+        }
+        vn[c] = u;
+        if (rank == 0 && s > 0) Vh[(size_t)(s - 1) * d + c] = vv;   // reflector s-1, normalised, exact zeros below its 1
       }
-    }
-    nrm2 = tri_block_sum1(nrm2, red2, par);
-    TRI_TRACE(3);
-    const double x0 = row[s + 1];
-    double beta = x0, t = 0.0, scale = 0.0;
-    if (nrm2 > 0.0 && s < d - 2) {
-      const double y2 = fma(x0, x0, nrm2);
-      const double nrm = y2 > 1e-290 && y2 < 1e290 ? fast_sqrt(y2) : sqrt(y2);
-      beta = x0 >= 0.0 ? -nrm : nrm;
-      t = (beta - x0) * fast_rcp(beta);
-      scale = fast_rcp(x0 - beta);
-    }
-    for (int c = tid; c < d; c += kTriThreads) vn[c] = c > s + 1 ? row[c] * scale : (c == s + 1 ? 1.0 : 0.0);
-    if (rank == 0) {
-      if (tid == 0) { diag[s] = row[s]; off[s] = beta; tau[s] = t; }
-      for (int c = tid; c < d; c += kTriThreads) Vh[(size_t)s * d + c] = c > s + 1 ? row[c] * scale : (c == s + 1 ? 1.0 : 0.0);
-    }
+      nrm2 = tri_block_sum1(nrm2, red2, par);   // its barrier also publishes v, w, vn and the corrected row
+      TRI_TRACE(3);
+      const double x0 = row[s + 1];
+      beta = x0;
+      if (nrm2 > 0.0 && s < d - 2) {
+        const double y2 = fma(x0, x0, nrm2);
+        const double nrm = y2 > 1e-290 && y2 < 1e290 ? fast_sqrt(y2) : sqrt(y2);
+        beta = x0 >= 0.0 ? -nrm : nrm;
+        t = (beta - x0) * fast_rcp(beta);
+        scale = fast_rcp(x0 - beta);
+      }
+      if (rank == 0 && tid == 0) { diag[s] = row[s]; off[s] = beta; tau[s] = t; }
+      sprev = scale;
+    } else {
+      double pv = 0.0;
+      for (int c = s + tid; c < d; c += kTriThreads) pv += pcur[c] * vn[c];
+      pv = tri_block_sum1(pv, red2, par);
+      TRI_TRACE(2);
+      const double kk = 0.5 * tprev * pv;
+      // v <- previous reflector, w = p - kk v, corrected row r = row - v_s w - w_s v: one sweep, every
+      // thread needs only its own column besides the scalars v_s and w_s
+      const double vs = vn[s], ws = pcur[s] - kk * vs;
+      double nrm2 = 0.0;
+      for (int c = tid; c < d; c += kTriThreads) {
+        const double vv = vn[c];
+        const double wc = c >= s ? pcur[c] - kk * vv : 0.0;
+        v[c] = vv;
+        w[c] = wc;
+        if (c >= s) {
+          const double r = row[c] - vs * wc - ws * vv;
+          row[c] = r;
+          if (c > s + 1) nrm2 += r * r;
+        }
+      }
+      nrm2 = tri_block_sum1(nrm2, red2, par);
+      TRI_TRACE(3);
+      const double x0 = row[s + 1];
+      beta = x0;
+      if (nrm2 > 0.0 && s < d - 2) {
+        const double y2 = fma(x0, x0, nrm2);
+        const double nrm = y2 > 1e-290 && y2 < 1e290 ? fast_sqrt(y2) : sqrt(y2);
+        beta = x0 >= 0.0 ? -nrm : nrm;
+        t = (beta - x0) * fast_rcp(beta);
+        scale = fast_rcp(x0 - beta);
+      }
+      for (int c = tid; c < d; c += kTriThreads) vn[c] = c > s + 1 ? row[c] * scale : (c == s + 1 ? 1.0 : 0.0);
+      if (rank == 0) {
+        if (tid == 0) { diag[s] = row[s]; off[s] = beta; tau[s] = t; }
+        for (int c = tid; c < d; c += kTriThreads) Vh[(size_t)s * d + c] = c > s + 1 ? row[c] * scale : (c == s + 1 ? 1.0 : 0.0);
+      }
     __syncthreads();
+    }
     TRI_TRACE(4);
     // own rows i > s: rank-2 update fused with p'_i; push p'_i into every CTA; publish row s+1
     double* pnext = pl + (size_t)(s & 1) * d;
@@ -422,14 +467,16 @@ tridiag_cluster_kernel(const double* __restrict__ A, int d, double* __restrict__
         any = any || act[k];
       }
       if (any) {                                // warp-uniform
-        double vi[NR], wi[NR], dx[NR], dy[NR];
+        double vi[NR], wi[NR], dx[NR], dy[NR], asel[NR];
 #pragma unroll
         for (int k = 0; k < NR; ++k) {
           vi[k] = act[k] ? v[irow[k]] : 0.0;
           wi[k] = act[k] ? w[irow[k]] : 0.0;
           dx[k] = 0.0;
           dy[k] = 0.0;
+          asel[k] = 0.0;
         }
+        const int jsel = (s + 1) >> 6, lsel = ((s + 1) & 63) >> 1;   // where column s+1 of an own row lives
         // Branch-free over the lanes: columns <= s of an own row are dead (never read again) and v' is exactly zero
         // there, so every lane updates its pair and adds it to the dot; an inactive row has vi = wi = 0 and stays
         // as it is.  (Per-lane tests compiled to divergent regions: ~290 cycles per 64 columns.)
@@ -452,13 +499,16 @@ tridiag_cluster_kernel(const double* __restrict__ A, int d, double* __restrict__
               a.y = fma(-wi[k], vv.y, fma(-vi[k], wv.y, a.y));
               dx[k] = fma(a.x, nv.x, dx[k]);
               dy[k] = fma(a.y, nv.y, dy[k]);
+              if (j == jsel) asel[k] = ((s + 1) & 1) ? a.y : a.x;   // warp-uniform test; used by lane lsel only
               if (inb) rr[k][j] = a;
             }
           }
         }
+        // A' v' = scale (A' u - beta A'[:, s+1]): the lane that holds column s+1 takes the second term
         double dot[NR];
 #pragma unroll
-        for (int k = 0; k < NR; ++k) dot[k] = dx[k] + dy[k];
+        for (int k = 0; k < NR; ++k) dot[k] = (dx[k] + dy[k]) - (lane == lsel ? beta * asel[k] : 0.0);
+        const double tsc = t * scale;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
 #pragma unroll
@@ -467,7 +517,7 @@ tridiag_cluster_kernel(const double* __restrict__ A, int d, double* __restrict__
         if (lane < cs && !last) {
 #pragma unroll
           for (int k = 0; k < NR; ++k)
-            if (act[k]) st_async_f64(&pnext[irow[k]], &xbar[(s + 1) & 1], (unsigned)lane, t * dot[k]);
+            if (act[k]) st_async_f64(&pnext[irow[k]], &xbar[(s + 1) & 1], (unsigned)lane, tsc * dot[k]);
         }
       }
       // the warp that holds row s+1 stages it in shared memory for the push below (after the last step: for diag[d-1])
@@ -545,6 +595,11 @@ tridiag_cluster_kernel(const double* __restrict__ A, int d, double* __restrict__
     }
     TRI_TRACE(5);
     TRI_TRACE(6);   // pushes issued; the wait for the next step's operands is event 1 of the next step
+  }
+  if constexpr (REG) {
+    // reflector d-2 (the identity: tau = 0, unit entry in column d-1) was never read back as `v`: its row of Vh
+    if (rank == 0 && d >= 2)
+      for (int c = tid; c < d; c += kTriThreads) Vh[(size_t)(d - 2) * d + c] = c == d - 1 ? 1.0 : 0.0;
   }
   cluster_barrier();   // no CTA may exit while its shared memory can still be a target
   if (d == 1) {
