@@ -1,0 +1,21 @@
+"""Random-shape sweep (tools/fuzz_shapes.py) as a test: fit + transform on shapes drawn around the dispatch boundaries - tiny
+inputs, row folding and its tails, padded chunk copies, single-CTA / CTA-pair Gram, k slices - against fp64 references
+formed on the GPU.  Gates: sigma 1e-4 (fp32) / 1e-10 (fp64), scores 2e-5 / 1e-11 of max|Z| (BASELINE.json north_star)."""
+from __future__ import annotations
+
+import subprocess
+import sys
+from pathlib import Path
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+TOOL = Path(__file__).resolve().parents[1] / "tools" / "fuzz_shapes.py"
+
+
+@pytest.mark.parametrize("seed,cases,dtype", [(11, 70, "f32"), (12, 70, "f32"), (13, 60, "f64")])
+def test_random_shapes_around_the_dispatch_boundaries(seed, cases, dtype):
+    r = subprocess.run([sys.executable, str(TOOL), str(seed), str(cases), dtype], capture_output=True, text=True, timeout=900)
+    tail = "\n".join(ln for ln in r.stdout.splitlines() if not ln.startswith("ok "))
+    assert r.returncode == 0 and "FUZZ PASSED" in r.stdout, tail[-3000:] + r.stderr[-2000:]
