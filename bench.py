@@ -3,7 +3,7 @@
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c4|c2|c3|c1|c5|c5s|r1|r2|n1] [--impl reference]
 
-A step is one fit (the whole hot path: pilot shift, streamed Gram + column statistics, allreduce, centring,
+A step is one fit (the whole hot path: pilot shift, streamed Gram + column statistics, exchange between ranks, centring,
 eigensolve, outputs) over one device-resident row shard of synthetic data.
   c4 (default, every N): PCA k=32, 2^25 x 512 fp32 per GPU = 256M x 512 over 8 GPUs    (BASELINE.json configs[3], the
                          north-star target; 64 GiB per GPU, so BENCH is the 1-GPU point of the weak-scaling curve)
@@ -14,7 +14,7 @@ eigensolve, outputs) over one device-resident row shard of synthetic data.
   r1, r2: the reference's own bench shapes (bench/run_benchmarks.py:45-53): 10,000 x 128 k=32 PCA, 50,000 x 256 k=64 TSVD power
   n1: PCA k=8, 2^24 x 32 fp32: a narrow input (HBM-bound, AI = 16 flop/B), streamed with its rows folded 8-fold
 At N = 1 the secondary workloads (c2, c3, c1, r1, r2, n1, c5s) run short in the same process and are attached under
-"also".  N > 1: one process per GPU (torchrun), rows sharded, one NCCL allreduce of the d x d partials per fit, weak
+"also".  N > 1: one process per GPU (torchrun), rows sharded, one NCCL collective on the d x d partials per fit, weak
 scaling (fixed shard per GPU).  Prints ONE JSON line on rank 0.
 `--impl reference` times the reference's own CPU backend (oracle/_ref/libdimreduce4cpu.so, else the numpy
 restatement) on a bounded row sample of the same workload on the host cores."""
@@ -388,7 +388,7 @@ def time_fit(torch, dist, ctx, wl, X, steps, warmup, world, sampler=None):
 
 def run_e2e(torch, dist, ctx, wl, X, rank, world, dev, steps):
     """Same metric through the reference-facing call with HOST buffers, host<->device copies inside the timed region:
-    pinned shard in, fit (sharded when N > 1: pilot + packed allreduce), projection, components / U / X_transformed
+    pinned shard in, fit (sharded when N > 1: one packed exchange), projection, components / U / X_transformed
     back out.  N = 1: the legacy C symbol the reference's ctypes layer binds (pca_float / truncated_svd_float /
     *_double).  N > 1: dr4g_fit_transform_host_* - the same routine behind the legacy symbols, on this rank's context and
     communicator (the reference has no multi-device entry point).  Plus, at N = 1, `pageable`: the drop-in estimator

@@ -97,8 +97,10 @@ DR4G_EXPORT int dr4g_sync(dr4g_ctx* ctx);
 DR4G_EXPORT int dr4g_set_option(dr4g_ctx* ctx, const char* key, double value);
 
 /* Row-sharded operation: rank 0 obtains a 128-byte NCCL unique id, the host layer ships it to
- * every rank, each rank calls dr4g_comm_init.  After that dr4g_fit_* all-reduces the packed
- * [Gram | column sums | column sums of squares | row count] partials once per fit. */
+ * every rank, each rank calls dr4g_comm_init.  After that dr4g_fit_* exchanges the packed
+ * [Gram | column sums | column sums of squares | row count | pilot shift] partials ONCE per fit: PCA all-gathers them and
+ * every rank re-bases them to the common shift and sums them in rank order (bit-identical models, no broadcast);
+ * TruncatedSVD (no shift) all-reduces them. */
 DR4G_EXPORT int dr4g_nccl_unique_id(void* out128);
 DR4G_EXPORT int dr4g_comm_init(dr4g_ctx* ctx, const void* unique_id128, int rank, int world);
 DR4G_EXPORT int dr4g_comm_world(dr4g_ctx* ctx);
@@ -129,10 +131,9 @@ DR4G_EXPORT int dr4g_fit_transform_host_double(dr4g_ctx* ctx, const double* X, l
  * over row chunks, so X never has to be device-resident as a whole (the reference's host-pointer symbols,
  * truncated_svd.py:98-107 / src/tsvd.cu:427-452, copy all of X to the device first).
  *   dr4g_partial_fit_*          one pass over a device-resident chunk (n x d); the first chunk fixes d, center,
- *                               the element type and, for center=1, the pilot shift (all-reduced when a
- *                               communicator is set: every rank must then make its first call together).
+ *                               the element type and, for center=1, this rank's pilot shift (no collective).
  *   dr4g_partial_fit_finalize_* exchange + eigensolve + outputs, exactly as dr4g_fit_* after its pass
- *                               (one all-reduce of the packed accumulators when a communicator is set);
+ *                               (one collective on the packed accumulators when a communicator is set);
  *                               the accumulated state stays valid (more chunks may follow).
  *   dr4g_partial_fit_reset      drop the accumulated state;  dr4g_partial_fit_rows: rows accumulated so far.
  * Asynchronous on ctx's stream: a chunk buffer may be reused once work queued after the call has completed. */
@@ -197,7 +198,7 @@ DR4G_EXPORT int dr4g_eigh_topk_static_double(dr4g_ctx* ctx, double* dA, int d, i
 DR4G_EXPORT int dr4g_eigh_topk_static_max_d(void);
 
 /* Per-stage device times (ms) of the last dr4g_fit_* on this context, valid after dr4g_sync:
- * [0] pilot shift, [1] Gram + column stats, [2] partial reduce + allreduce + centring,
+ * [0] pilot shift, [1] Gram + column stats, [2] exchange between ranks + centring,
  * [3] eigensolve (Jacobi or subspace iteration), [4] sort/flip/outputs, [5] total.
  * Returns the number of entries written (<= n). */
 DR4G_EXPORT int dr4g_stage_times(dr4g_ctx* ctx, double* ms, int n);
