@@ -18,6 +18,7 @@
 //   [3] eigensolve of C: blocked Jacobi ("cusolver") or subspace iteration (else)  (K4 / K5)
 //   [4] sort, sign, truncate, sigma / explained variance / ratio / mean            (K6)
 // transform is a second streamed pass (K7), shard-local.
+#include <condition_variable>
 #include <mutex>
 #include <map>
 #include <memory>
@@ -116,11 +117,13 @@ struct StreamFit {
 // (dimreduce4gpu/truncated_svd.py:72-86).  Here a few host threads fill a ring of pinned 32 MB buffers while the
 // previous buffers are in flight on the copy engine.
 struct HostStage {
-  static constexpr int NB = 3;
-  static constexpr size_t kSub = (size_t)32 << 20;
-  void* buf[NB] = {nullptr, nullptr, nullptr};
-  cudaEvent_t done[NB] = {nullptr, nullptr, nullptr};
-  bool busy[NB] = {false, false, false};
+  // four 8 MB buffers (round 2 began with three of 32 MB: a 51 MB array - the reference's own bench shape 50,000 x 256 -
+  // was two sub-chunks, so the host copy and the DMA hardly overlapped; 8 MB is ~0.15 ms on the link)
+  static constexpr int NB = 4;
+  static constexpr size_t kSub = (size_t)8 << 20;
+  void* buf[NB] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t done[NB] = {nullptr, nullptr, nullptr, nullptr};
+  bool busy[NB] = {false, false, false, false};
   int next = 0;
   // a D2H sub-chunk that is in flight into buf[b] and still has to be copied out to the caller's array
   struct Out { void* dst; size_t bytes; } out[NB] = {};
@@ -152,21 +155,68 @@ static int stage_threads() {
   return n;
 }
 
-static void parallel_memcpy(void* dst, const void* src, size_t bytes) {
-  const int nt = bytes < ((size_t)4 << 20) ? 1 : stage_threads();
-  if (nt <= 1) { std::memcpy(dst, src, bytes); return; }
-  const size_t per = ((bytes + nt - 1) / nt + 4095) & ~(size_t)4095;
-  std::vector<std::thread> th;
-  th.reserve(nt - 1);
-  for (int t = 1; t < nt; ++t) {
-    const size_t off = (size_t)t * per;
-    if (off >= bytes) break;
-    const size_t len = bytes - off < per ? bytes - off : per;
-    th.emplace_back([=] { std::memcpy(static_cast<char*>(dst) + off, static_cast<const char*>(src) + off, len); });
+// Persistent helpers for the staging copies (a std::thread per slice and sub-chunk cost more than the copy itself once the
+// sub-chunks are 8 MB).  One job at a time (the callers hold the context's mutex, the pool its own): the caller takes
+// slice 0, the workers the others; also used to touch fresh output pages from several cores at once.
+class CopyPool {
+ public:
+  static CopyPool& get() {
+    static CopyPool* p = new CopyPool(stage_threads() - 1);   // leaked on purpose: workers may outlive static destructors
+    return *p;
   }
-  std::memcpy(dst, src, per < bytes ? per : bytes);
-  for (auto& t : th) t.join();
-}
+  // src == nullptr: write-touch every page of dst (contents kept) - takes the page faults of a fresh array early
+  static void do_slice(char* d, const char* s, size_t len) {
+    if (s) { std::memcpy(d, s, len); return; }
+    for (size_t o = 0; o < len; o += 4096) { volatile char* q = d + o; *q = *q; }
+  }
+  void copy(void* dst, const void* src, size_t bytes) {
+    const int nt = bytes < ((size_t)1 << 20) ? 1 : (int)workers_.size() + 1;
+    if (nt <= 1) { do_slice(static_cast<char*>(dst), static_cast<const char*>(src), bytes); return; }
+    std::lock_guard<std::mutex> job(job_mu_);
+    const size_t per = ((bytes + nt - 1) / nt + 4095) & ~(size_t)4095;
+    {
+      std::lock_guard<std::mutex> lk(mu_);
+      dst_ = static_cast<char*>(dst); src_ = static_cast<const char*>(src); bytes_ = bytes; per_ = per;
+      pending_ = (int)workers_.size();
+      ++gen_;
+    }
+    cv_.notify_all();
+    do_slice(static_cast<char*>(dst), static_cast<const char*>(src), per < bytes ? per : bytes);
+    std::unique_lock<std::mutex> lk(mu_);
+    done_cv_.wait(lk, [&] { return pending_ == 0; });
+  }
+
+ private:
+  explicit CopyPool(int n) {
+    for (int i = 0; i < (n < 0 ? 0 : n); ++i) workers_.emplace_back([this, i] { run(i + 1); });
+    for (auto& t : workers_) t.detach();
+  }
+  void run(int slice) {
+    unsigned long long seen = 0;
+    for (;;) {
+      std::unique_lock<std::mutex> lk(mu_);
+      cv_.wait(lk, [&] { return gen_ != seen; });
+      seen = gen_;
+      char* d = dst_; const char* s = src_; const size_t bytes = bytes_, per = per_;
+      lk.unlock();
+      const size_t off = (size_t)slice * per;
+      if (off < bytes) do_slice(d + off, s ? s + off : nullptr, bytes - off < per ? bytes - off : per);
+      lk.lock();
+      if (--pending_ == 0) done_cv_.notify_one();
+    }
+  }
+  std::vector<std::thread> workers_;
+  std::mutex mu_, job_mu_;
+  std::condition_variable cv_, done_cv_;
+  unsigned long long gen_ = 0;
+  int pending_ = 0;
+  char* dst_ = nullptr;
+  const char* src_ = nullptr;
+  size_t bytes_ = 0, per_ = 0;
+};
+
+static void parallel_memcpy(void* dst, const void* src, size_t bytes) { CopyPool::get().copy(dst, src, bytes); }
+static void parallel_touch(void* dst, size_t bytes) { CopyPool::get().copy(dst, nullptr, bytes); }
 
 static bool is_pageable_host(const void* p) {
   cudaPointerAttributes a;
@@ -672,11 +722,14 @@ static void legacy_pipelined(CtxFull& c, bool is_pca, bool resident, const T* X,
   if (!c.copy_stream) DR4G_CUDA(cudaStreamCreateWithFlags(&c.copy_stream, cudaStreamNonBlocking));
   if (!c.out_stream) DR4G_CUDA(cudaStreamCreateWithFlags(&c.out_stream, cudaStreamNonBlocking));
   static const bool no_stage = getenv("DR4G_NO_STAGING") != nullptr;
-  // small arrays stay on the driver's own pageable path (pinning the ring costs ~10 ms per buffer, once per process)
-  const size_t stage_min = (size_t)16 << 20;
-  const bool x_pageable = !no_stage && (size_t)n * d * sizeof(T) >= stage_min && is_pageable_host(X);
-  const bool z_pageable = !no_stage && Xt && (size_t)n * k * sizeof(T) >= stage_min && is_pageable_host(Xt);
-  const bool u_pageable = !no_stage && U && (size_t)n * k * sizeof(T) >= stage_min && is_pageable_host(U);
+  // small arrays stay on the driver's own pageable path (the first use pins the 32 MB ring, once per process); from
+  // a few MB on the ring wins: the driver stages a pageable copy on one thread, and fresh output arrays (np.zeros of
+  // the wrapper) take their page faults there too (50,000 x 256, k = 64: 5 of 10.7 ms)
+  // (an input of one sub-chunk cannot overlap its host copy with its DMA: 10,000 x 128 got slower, 1.6 -> 2.3 ms)
+  const size_t stage_min_in = (size_t)12 << 20, stage_min_out = (size_t)4 << 20;
+  const bool x_pageable = !no_stage && (size_t)n * d * sizeof(T) >= stage_min_in && is_pageable_host(X);
+  const bool z_pageable = !no_stage && Xt && (size_t)n * k * sizeof(T) >= stage_min_out && is_pageable_host(Xt);
+  const bool u_pageable = !no_stage && U && (size_t)n * k * sizeof(T) >= stage_min_out && is_pageable_host(U);
   const size_t cx = (size_t)(resident ? n : 2 * chunk) * d * sizeof(T), cz = (size_t)(resident ? n : 2 * chunk) * k * sizeof(T);
   c.io.reserve(up256(cx) + 2 * up256(cz) + up256((size_t)k * d * sizeof(T)) + 3 * up256((size_t)k * sizeof(T)) +
                up256((size_t)d * sizeof(T)) + 8192);
@@ -731,6 +784,9 @@ static void legacy_pipelined(CtxFull& c, bool is_pca, bool resident, const T* X,
       if (!resident) DR4G_CUDA(cudaEventRecord(xfree[b], c.stream));
     }
     partial_fit_finalize_impl<T>(c, k, p, dQ, dw, dev, devr, dmean);
+    // while the device is busy with the eigensolve: take the page faults of the (fresh) score arrays on all helper threads
+    if (z_pageable) parallel_touch(Xt, (size_t)n * k * sizeof(T));
+    if (u_pageable) parallel_touch(U, (size_t)n * k * sizeof(T));
     // [2] scores
     for (long long i = 0; Xt && i < nchunks; ++i) {
       const int b = (int)(i & 1);
