@@ -33,8 +33,24 @@ def _candidate_paths() -> list[Path]:
     return cands
 
 
+_path_cache: dict[str | None, str] = {}   # DIMREDUCE4GPU_LIB_PATH value -> library found (successes only)
+
+
 def get_library_path() -> str | None:
-    """Full path of libdimreduce4gpu.so if it exists, else None (reference _native.py:37-50)."""
+    """Full path of libdimreduce4gpu.so if it exists, else None (reference _native.py:37-50).  A hit is remembered per
+    value of DIMREDUCE4GPU_LIB_PATH: the walk over the candidate directories (pathlib + lstat) cost ~25 us, four times
+    per fit_transform."""
+    key = os.environ.get("DIMREDUCE4GPU_LIB_PATH")
+    hit = _path_cache.get(key)
+    if hit is not None:
+        return hit
+    found = _find_library_path()
+    if found is not None:
+        _path_cache[key] = found
+    return found
+
+
+def _find_library_path() -> str | None:
     for base in _candidate_paths():
         try:
             c = base / _LIBNAME
@@ -64,6 +80,8 @@ def require_native_built() -> str:
 def load_library() -> ctypes.CDLL:
     """dlopen once, bind every symbol of include/dimreduce4gpu.h, cache the handle."""
     global _handle, _handle_path
+    if _handle is not None and _handle_path == get_library_path():   # fast path, no lock
+        return _handle
     with _lock:
         path = require_native_built()
         if _handle is not None and _handle_path == path:
@@ -92,8 +110,22 @@ def native_built() -> bool:
 native_available = native_built  # name used by the reference's examples/bench scripts
 
 
+_driver_ok: tuple[bool, int, str] | None = None
+
+
 def _cuda_driver_device_count() -> tuple[bool, int, str]:
-    """(ok, count, reason) through the driver API, as the reference does (_native.py:73-120)."""
+    """(ok, count, reason) through the driver API, as the reference does (_native.py:73-120).  A positive answer is
+    remembered for the life of the process (devices do not go away under a running process; a failure is re-probed)."""
+    global _driver_ok
+    if _driver_ok is not None:
+        return _driver_ok
+    res = _probe_cuda_driver()
+    if res[0]:
+        _driver_ok = res
+    return res
+
+
+def _probe_cuda_driver() -> tuple[bool, int, str]:
     try:
         libcuda = ctypes.CDLL("libcuda.so.1")
     except OSError as e:

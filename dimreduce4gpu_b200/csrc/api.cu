@@ -18,6 +18,7 @@
 //   [3] eigensolve of C: blocked Jacobi ("cusolver") or subspace iteration (else)  (K4 / K5)
 //   [4] sort, sign, truncate, sigma / explained variance / ratio / mean            (K6)
 // transform is a second streamed pass (K7), shard-local.
+#include <chrono>
 #include <condition_variable>
 #include <mutex>
 #include <map>
@@ -217,6 +218,25 @@ class CopyPool {
 
 static void parallel_memcpy(void* dst, const void* src, size_t bytes) { CopyPool::get().copy(dst, src, bytes); }
 static void parallel_touch(void* dst, size_t bytes) { CopyPool::get().copy(dst, nullptr, bytes); }
+
+// DR4G_LEGACY_TRACE=1: host-side timeline of a legacy call (microseconds since entry) on stderr
+struct LegacyTrace {
+  bool on;
+  std::chrono::steady_clock::time_point t0;
+  std::vector<std::pair<const char*, double>> ev;
+  LegacyTrace() : on(getenv("DR4G_LEGACY_TRACE") != nullptr), t0(std::chrono::steady_clock::now()) {}
+  void mark(const char* what) {
+    if (on) ev.emplace_back(what, std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t0).count());
+  }
+  ~LegacyTrace() {
+    if (!on) return;
+    fprintf(stderr, "[dr4g legacy trace]");
+    for (auto& e : ev) fprintf(stderr, " %s=%.0f", e.first, e.second);
+    fprintf(stderr, "\n");
+  }
+};
+static thread_local LegacyTrace* g_ltrace = nullptr;
+#define LTRACE(x) do { if (g_ltrace) g_ltrace->mark(x); } while (0)
 
 static bool is_pageable_host(const void* p) {
   cudaPointerAttributes a;
@@ -760,6 +780,7 @@ static void legacy_pipelined(CtxFull& c, bool is_pca, bool resident, const T* X,
       cudaEventDestroy(zfree[b]);
     }
   };
+  LTRACE("setup");
   try {
     // the copy stream must not overtake earlier work of this context that still reads the io arena
     DR4G_CUDA(cudaStreamSynchronize(c.stream));
@@ -783,7 +804,9 @@ static void legacy_pipelined(CtxFull& c, bool is_pca, bool resident, const T* X,
       partial_fit_impl<T>(c, xbuf(r0, b), rows, d, is_pca ? 1 : 0);
       if (!resident) DR4G_CUDA(cudaEventRecord(xfree[b], c.stream));
     }
+    LTRACE("pass_issued");
     partial_fit_finalize_impl<T>(c, k, p, dQ, dw, dev, devr, dmean);
+    LTRACE("finalize_issued");
     // while the device is busy with the eigensolve: take the page faults of the (fresh) score arrays on all helper threads
     if (z_pageable) parallel_touch(Xt, (size_t)n * k * sizeof(T));
     if (u_pageable) parallel_touch(U, (size_t)n * k * sizeof(T));
@@ -806,6 +829,7 @@ static void legacy_pipelined(CtxFull& c, bool is_pca, bool resident, const T* X,
       if (U) d2h_copy(c, U + (size_t)r0 * k, ubuf(r0, b), (size_t)rows * k * sizeof(T), u_pageable, c.out_stream);
       if (!resident) DR4G_CUDA(cudaEventRecord(zfree[b], c.out_stream));
     }
+    LTRACE("scores_issued");
     auto out = [&](T* dst, const T* src, size_t count) {
       if (dst) DR4G_CUDA(cudaMemcpyAsync(dst, src, count * sizeof(T), cudaMemcpyDefault, c.stream));
     };
@@ -814,10 +838,12 @@ static void legacy_pipelined(CtxFull& c, bool is_pca, bool resident, const T* X,
     out(ev, dev, k);
     out(evr, devr, k);
     if (is_pca) out(mean, dmean, d);
+    LTRACE("small_outputs");
     stage_drain(c.stage, true);   // copy-outs of the last staged score sub-chunks
     DR4G_CUDA(cudaStreamSynchronize(c.copy_stream));
     DR4G_CUDA(cudaStreamSynchronize(c.stream));
     DR4G_CUDA(cudaStreamSynchronize(c.out_stream));
+    LTRACE("synced");
   } catch (...) {
     for (int b = 0; b < HostStage::NB; ++b) { c.stage.busy[b] = false; c.stage.out[b] = HostStage::Out{}; }
     cudaStreamSynchronize(c.copy_stream);
@@ -841,8 +867,6 @@ static void host_fit_transform(CtxFull& c, bool is_pca, const T* X, long long n,
                                T* U, T* Xt, T* ev, T* evr, T* mean) {
   const size_t xbytes = (size_t)n * d * sizeof(T);
   const size_t zbytes = (size_t)n * k * sizeof(T);
-  size_t free_b = 0, total_b = 0;
-  DR4G_CUDA(cudaMemGetInfo(&free_b, &total_b));
   const char* env = getenv("DR4G_STREAM_ROWS");
   const long long forced = env ? atoll(env) : 0;
   // what the resident path would have to allocate on top of what the context already owns: the io arena (grown by
@@ -852,6 +876,11 @@ static void host_fit_transform(CtxFull& c, bool is_pca, const T* X, long long n,
   const size_t io_grow = io_need > c.io.cap ? io_need + (io_need >> 3) + ((size_t)1 << 20) - c.io.cap : 0;
   const size_t ws_need = (size_t)d * d * 8 * 6 + ((size_t)48 << 20);
   const size_t ws_grow = ws_need > c.arena.cap ? ws_need - c.arena.cap : 0;
+  // cudaMemGetInfo costs ~0.1 ms (a fifth of a 4 x 3 call): asked only when the call has to grow the arenas by more than
+  // 256 MB; a smaller growth that does not fit is caught below (cudaMalloc failure -> out-of-core pipeline)
+  size_t free_b = ~(size_t)0, total_b = 0;
+  if (forced <= 0 && io_grow + ws_grow > ((size_t)256 << 20)) DR4G_CUDA(cudaMemGetInfo(&free_b, &total_b));
+  LTRACE("meminfo");
   bool resident = forced <= 0 && (double)io_grow + (double)ws_grow <= 0.92 * (double)free_b;
   auto chunk_rows = [&](bool res) {
     long long chunk = forced > 0 ? forced : (long long)(((size_t)(res ? 128 : 256) << 20) / ((size_t)d * sizeof(T)));
@@ -897,9 +926,13 @@ static void legacy_entry(bool is_pca, const T* X, T* Q, T* w, T* U, T* Xt, T* ev
     if (k > d) k = d;
     if (n <= 0 || d <= 0 || k <= 0) fail("%s: empty problem (X_n=%lld X_m=%d k=%d)", name, n, d, p.k);
 
+    LegacyTrace ltrace;
+    g_ltrace = ltrace.on ? &ltrace : nullptr;
+    struct Unset { ~Unset() { g_ltrace = nullptr; } } unset;
     CtxFull* c = legacy_ctx(p.gpu_id);
     std::lock_guard<std::mutex> lk(c->mu);
     DeviceGuard guard(c->device);
+    LTRACE("ctx");
     if (p.verbose)
       fprintf(stderr, "[dimreduce4gpu] %s: algorithm=%s n=%lld d=%d k=%d device=%d\n", name,
               is_exact(p) ? "cusolver (blocked Jacobi)" : "power (subspace iteration)", n, d, k, c->device);
