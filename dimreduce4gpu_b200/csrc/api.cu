@@ -18,6 +18,9 @@
 //   [3] eigensolve of C: blocked Jacobi ("cusolver") or subspace iteration (else)  (K4 / K5)
 //   [4] sort, sign, truncate, sigma / explained variance / ratio / mean            (K6)
 // transform is a second streamed pass (K7), shard-local.
+#include <sys/mman.h>
+
+#include <atomic>
 #include <chrono>
 #include <condition_variable>
 #include <mutex>
@@ -218,6 +221,46 @@ class CopyPool {
 
 static void parallel_memcpy(void* dst, const void* src, size_t bytes) { CopyPool::get().copy(dst, src, bytes); }
 static void parallel_touch(void* dst, size_t bytes) { CopyPool::get().copy(dst, nullptr, bytes); }
+
+// Fresh output arrays (the wrapper's np.zeros: untouched calloc pages) take a page fault per 4 KB when they are first
+// written - 256 MB of scores cost ~10 ms of a 36 ms call.  While the input is still on its way to the device, helper
+// threads ask the kernel to back the arrays with huge pages where a 2 MB aligned piece exists (MADV_HUGEPAGE) and to
+// populate them writable in one go (MADV_POPULATE_WRITE, Linux >= 5.14): contents are kept, only the faults move out
+// of the copy-out.  Kernels without it (EINVAL) fall back to write-touching the pages from the copy pool.
+#ifndef MADV_POPULATE_WRITE
+#define MADV_POPULATE_WRITE 23
+#endif
+struct Prefault {
+  std::vector<std::thread> th;
+  std::atomic<int> failed{0};
+  void start(void* p, size_t bytes, int nthreads) {
+    static const bool off = getenv("DR4G_NO_MADVISE") != nullptr;
+    if (off || !p || bytes < ((size_t)4 << 20)) { failed = 1; return; }
+    const uintptr_t a = (reinterpret_cast<uintptr_t>(p) + 4095) & ~(uintptr_t)4095;
+    const uintptr_t e = (reinterpret_cast<uintptr_t>(p) + bytes) & ~(uintptr_t)4095;
+    if (e <= a) return;
+    const uintptr_t m2 = ((uintptr_t)2 << 20) - 1, a2 = (a + m2) & ~m2, e2 = e & ~m2;
+    if (e2 > a2) madvise(reinterpret_cast<void*>(a2), e2 - a2, MADV_HUGEPAGE);   // advice only: failure is harmless
+    const size_t per = (((e - a) + nthreads - 1) / nthreads + m2) & ~(size_t)m2;
+    for (int t = 0; t < nthreads; ++t) {
+      const uintptr_t lo = a + (uintptr_t)t * per;
+      if (lo >= e) break;
+      const uintptr_t hi = lo + per < e ? lo + per : e;
+      th.emplace_back([this, lo, hi] {
+        for (uintptr_t q = lo; q < hi; q += (size_t)16 << 20) {
+          const size_t len = hi - q < ((size_t)16 << 20) ? hi - q : ((size_t)16 << 20);
+          if (madvise(reinterpret_cast<void*>(q), len, MADV_POPULATE_WRITE) != 0) { failed = 1; return; }
+        }
+      });
+    }
+  }
+  bool finish() {   // true: every page is populated
+    for (auto& t : th) if (t.joinable()) t.join();
+    th.clear();
+    return failed.load() == 0;
+  }
+  ~Prefault() { finish(); }
+};
 
 // DR4G_LEGACY_TRACE=1: host-side timeline of a legacy call (microseconds since entry) on stderr
 struct LegacyTrace {
@@ -781,6 +824,9 @@ static void legacy_pipelined(CtxFull& c, bool is_pca, bool resident, const T* X,
     }
   };
   LTRACE("setup");
+  Prefault pf_z, pf_u;
+  if (z_pageable) pf_z.start(Xt, (size_t)n * k * sizeof(T), 2);
+  if (u_pageable) pf_u.start(U, (size_t)n * k * sizeof(T), 2);
   try {
     // the copy stream must not overtake earlier work of this context that still reads the io arena
     DR4G_CUDA(cudaStreamSynchronize(c.stream));
@@ -808,8 +854,9 @@ static void legacy_pipelined(CtxFull& c, bool is_pca, bool resident, const T* X,
     partial_fit_finalize_impl<T>(c, k, p, dQ, dw, dev, devr, dmean);
     LTRACE("finalize_issued");
     // while the device is busy with the eigensolve: take the page faults of the (fresh) score arrays on all helper threads
-    if (z_pageable) parallel_touch(Xt, (size_t)n * k * sizeof(T));
-    if (u_pageable) parallel_touch(U, (size_t)n * k * sizeof(T));
+    if (z_pageable && !pf_z.finish()) parallel_touch(Xt, (size_t)n * k * sizeof(T));
+    if (u_pageable && !pf_u.finish()) parallel_touch(U, (size_t)n * k * sizeof(T));
+    LTRACE("prefaulted");
     // [2] scores
     for (long long i = 0; Xt && i < nchunks; ++i) {
       const int b = (int)(i & 1);
