@@ -641,7 +641,7 @@ __device__ __forceinline__ int sturm_count(const double* __restrict__ dg, const 
 
 // One CTA (4 warps) per wanted eigenvalue (j-th largest, j = blockIdx.x).  lam[j] descending.
 // info[0] = ||T||_1-ish scale (max Gershgorin radius bound), written by warp 0 for T3.
-constexpr int kBsThreads = 512, kBsU = 1;   // sections per pass = kBsThreads * kBsU
+constexpr int kBsThreads = 256, kBsU = 1;   // sections per pass = kBsThreads * kBsU
 
 __global__ void __launch_bounds__(kBsThreads)
 bisect_kernel(const double* __restrict__ diag, const double* __restrict__ off, int d, int k,
@@ -681,51 +681,67 @@ bisect_kernel(const double* __restrict__ diag, const double* __restrict__ off, i
   const int j = blockIdx.x;   // one CTA per wanted eigenvalue
   if (j >= k) return;
   const int idx = d - 1 - j;  // 0-based index in ascending order: count(x) <= idx  <=>  x <= lambda_idx
-  // kBsThreads * kBsU sections per pass, one Sturm recurrence per thread: with 4 recurrences per thread the pass was
-  // bound by the fp64 issue rate of the four schedulers (138 us at d = 256, k = 32), one per thread leaves the
-  // 255-step dependent chain (~130 cycles per step).  A pass narrows the interval 513-fold (1024 threads and four
-  // passes to 2e-12 ||T|| were slower: two warps' worth of fp64 issue per scheduler again).
+  if (!(tnorm > 0.0)) {       // zero matrix
+    if (tid == 0) lam[j] = 0.0;
+    return;
+  }
+  // Sturm count in PRODUCT form on T / ||T||: p_0 = 1, p_1 = d_0 - x, p_i = (d_{i-1} - x) p_{i-1} - e_{i-2}^2 p_{i-2}; the
+  // pivots of the LDL^T form are q_i = p_i / p_{i-1}, so the count of negative pivots is the count of sign changes of
+  // p.  The dependent chain is ONE fma per row (the product e^2 p_{i-2} is a step old) instead of fma + reciprocal
+  // (~5 dependent fp64 operations): 255 steps of ~130 cycles were 82 us of the 0.73 ms eigensolve at d = 256.  The pair
+  // (p_{i-1}, p_i) is rescaled by a power of two every 8 rows (|d - x| <= 2, e^2 <= 1 after the scaling by ||T||: at most
+  // 3^8 of growth in between); an exact zero counts as a negative pivot, like dlaebz's -pivmin.
+  __syncthreads();            // everybody has read the Gershgorin bounds off dg / e2
+  const double inv = 1.0 / tnorm;
+  for (int i = tid; i < d; i += blockDim.x) { dg[i] *= inv; e2[i] *= inv * inv; }
+  __syncthreads();
+  lo *= inv;
+  hi *= inv;
+  // kBsThreads sections per pass, one recurrence per thread; a pass narrows the interval 513-fold
   __shared__ int s_first[kBsThreads / 32];
   const int S = kBsU * kBsThreads;
-  const double atol = 1e-13 * tnorm + 2.0 * pivmin;   // five 513-section passes from the Gershgorin interval; T3 refines by Rayleigh quotient
+  const double atol = 1e-13;   // of ||T||: five 513-section passes from the Gershgorin interval; T3 refines by Rayleigh quotient
   for (int it = 0; it < 12; ++it) {
     const double width = hi - lo;
     if (!(width > atol)) break;   // CTA-uniform: lo, hi are identical in every thread
-    double x[kBsU], q[kBsU];
-    int cnt[kBsU];
+    const double x = lo + width * (double)(tid + 1) / (double)(S + 1);
+    double pp = 1.0, pc = dg[0] - x;
+    if (pc == 0.0) pc = -1e-300;
+    int cnt = pc < 0.0;
+    int i = 1;
+    auto step = [&](int r) {
+      double pn = fma(dg[r] - x, pc, -(e2[r - 1] * pp));
+      if (pn == 0.0) pn = pc < 0.0 ? 1e-300 : -1e-300;          // virtual sign opposite to p_{i-1}: a negative pivot
+      cnt += (__double2hiint(pn) ^ __double2hiint(pc)) < 0;     // sign change
+      pp = pc;
+      pc = pn;
+    };
+    for (; i + 8 <= d; i += 8) {
 #pragma unroll
-    for (int u = 0; u < kBsU; ++u) {
-      x[u] = lo + width * (double)(kBsU * tid + u + 1) / (double)(S + 1);
-      q[u] = dg[0] - x[u];
-      if (fabs(q[u]) < pivmin) q[u] = -pivmin;
-      cnt[u] = q[u] < 0.0;
+      for (int u = 0; u < 8; ++u) step(i + u);
+      // rescale by 2^-(exponent of the larger one)
+      const int ec = (__double2hiint(pc) >> 20) & 0x7ff, ep = (__double2hiint(pp) >> 20) & 0x7ff;
+      const int em = ec > ep ? ec : ep;
+      const double sc = __hiloint2double((2046 - (em < 1 ? 1 : (em > 2045 ? 2045 : em))) << 20, 0);
+      pc *= sc;
+      pp *= sc;
+      if (pc == 0.0) pc = (cnt & 1) ? -1e-300 : 1e-300;          // underflow: keep the sign the count implies
     }
-    for (int i = 1; i < d; ++i) {
-      const double di = dg[i], ei = e2[i - 1];
-#pragma unroll
-      for (int u = 0; u < kBsU; ++u) {
-        q[u] = di - x[u] - ei * fast_rcp(q[u]);
-        if (fabs(q[u]) < pivmin) q[u] = -pivmin;
-        cnt[u] += q[u] < 0.0;
-      }
-    }
-    int fl = kBsU;
-#pragma unroll
-    for (int u = kBsU - 1; u >= 0; --u) if (cnt[u] > idx) fl = u;  // counts are monotone in x: first shift right of lambda_idx
-    const unsigned m = __ballot_sync(0xffffffffu, fl < kBsU);
+    for (; i < d; ++i) step(i);
+    const int fl = cnt > idx ? 0 : 1;   // counts are monotone in x up to rounding: first shift right of lambda_idx
+    const unsigned m = __ballot_sync(0xffffffffu, fl == 0);
     const int lane1 = m ? __ffs(m) - 1 : 0;
-    const int u1 = __shfl_sync(0xffffffffu, fl, lane1);
-    if (lane == 0) s_first[warp] = m ? (warp * 32 + lane1) * kBsU + u1 : S;
+    if (lane == 0) s_first[warp] = m ? warp * 32 + lane1 : S;
     __syncthreads();
     int first = S;
-    for (int i = 0; i < nwarp; ++i) first = min(first, s_first[i]);
+    for (int w = 0; w < nwarp; ++w) first = min(first, s_first[w]);
     __syncthreads();
     const double nlo = first == 0 ? lo : lo + width * (double)first / (double)(S + 1);
     const double nhi = first == S ? hi : lo + width * (double)(first + 1) / (double)(S + 1);
     lo = nlo;
     hi = nhi;
   }
-  if (tid == 0) lam[j] = 0.5 * (lo + hi);
+  if (tid == 0) lam[j] = 0.5 * (lo + hi) * tnorm;
 }
 
 // ---------------------------------------------------------------- T3: eigenvectors by inverse iteration
