@@ -1007,57 +1007,102 @@ invit_orth_kernel(const double* __restrict__ lam, const double* __restrict__ inf
 __global__ void __launch_bounds__(256)
 backtransform_kernel(const double* __restrict__ Vh, const double* __restrict__ tau, int d, int k,
                      double* __restrict__ Z) {
+  // One CTA per vector, TWO reflectors per block reduction (as backtransform_pair_kernel does per warp): with
+  // a = v_s.z, b = v_{s-1}.z, g = v_{s-1}.v_s reduced together, H_{s-1} H_s z = z - ca v_s - cb v_{s-1},
+  // ca = tau_s a, cb = tau_{s-1} (b - ca g).  One reflector per reduction took two CTA barriers each (441 us at d = 784).
   extern __shared__ double bt_sm[];
   double* z = bt_sm;
-  __shared__ double red[8];
-  const int tid = threadIdx.x, j = blockIdx.x;
+  __shared__ double red[2][3][8];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, j = blockIdx.x;
   for (int i = tid; i < d; i += 256) z[i] = Z[(size_t)j * d + i];
   __syncthreads();
-  // reflector rows are prefetched one step ahead (registers), so the L2 latency is off the
-  // dependent chain; d <= 256 * kBtPer elements per row, longer rows fall back to direct loads
-  constexpr int kBtPer = 4;
-  const bool pre = d <= 256 * kBtPer;
-  double nxt[kBtPer];
-  auto fetch = [&](int s) {
-    const double* vr = Vh + (size_t)s * d;
-#pragma unroll
-    for (int u = 0; u < kBtPer; ++u) {
-      const int i = tid + 256 * u;
-      nxt[u] = (i > s && i < d) ? __ldg(&vr[i]) : 0.0;
-    }
-  };
-  if (pre && d >= 3) fetch(d - 3);
-  for (int s = d - 3; s >= 0; --s) {
-    const double t = tau[s];
-    double cur[kBtPer];
-#pragma unroll
-    for (int u = 0; u < kBtPer; ++u) cur[u] = nxt[u];
-    if (pre && s > 0) fetch(s - 1);
-    if (t == 0.0) continue;
+  int s = d - 3, par = 0;
+  if (s >= 0 && ((d - 2) & 1)) {   // odd count: one single reflector first
     const double* vr = Vh + (size_t)s * d;
     double dot = 0.0;
-    if (pre) {
-#pragma unroll
-      for (int u = 0; u < kBtPer; ++u) { const int i = tid + 256 * u; if (i < d) dot += cur[u] * z[i]; }
-    } else {
-      for (int i = s + 1 + tid; i < d; i += 256) dot += vr[i] * z[i];
-    }
+    for (int i = s + 1 + tid; i < d; i += 256) dot += vr[i] * z[i];
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
-    if ((tid & 31) == 0) red[tid >> 5] = dot;
+    if (lane == 0) red[par][0][warp] = dot;
     __syncthreads();
     double tot = 0.0;
 #pragma unroll
-    for (int wv = 0; wv < 8; ++wv) tot += red[wv];
-    tot *= t;
+    for (int wv = 0; wv < 8; ++wv) tot += red[par][0][wv];
+    tot *= tau[s];
+    for (int i = s + 1 + tid; i < d; i += 256) z[i] -= tot * vr[i];
+    __syncthreads();
+    par ^= 1;
+    --s;
+  }
+  // rows are prefetched one pair ahead (registers) for d <= 256 * kBtPer, so the L2 latency is off the dependent chain
+  constexpr int kBtPer = 4;
+  const bool pre = d <= 256 * kBtPer;
+  double na[kBtPer], nb[kBtPer];
+  auto fetch = [&](int sp) {   // reflectors sp and sp - 1 (T1 stores exact zeros below a reflector's leading 1)
+#pragma unroll
+    for (int u = 0; u < kBtPer; ++u) {
+      const int i = tid + 256 * u;
+      const bool in = i < d && sp >= 1;
+      na[u] = in ? __ldg(&Vh[(size_t)sp * d + i]) : 0.0;
+      nb[u] = in ? __ldg(&Vh[(size_t)(sp - 1) * d + i]) : 0.0;
+    }
+  };
+  auto i0 = [&](int from) { return tid >= from ? tid : tid + (from - tid + 255) / 256 * 256; };   // first i >= from with i = tid mod 256
+  if (pre) fetch(s);
+  for (; s >= 1; s -= 2) {
+    const double ta = tau[s], tb = tau[s - 1];
+    double ca[kBtPer], cb[kBtPer];
+    double a = 0.0, b = 0.0, g = 0.0;
+    const double* va = Vh + (size_t)s * d;
+    const double* vb = va - d;
     if (pre) {
 #pragma unroll
-      for (int u = 0; u < kBtPer; ++u) { const int i = tid + 256 * u; if (i < d) z[i] -= tot * cur[u]; }
+      for (int u = 0; u < kBtPer; ++u) { ca[u] = na[u]; cb[u] = nb[u]; }
+      fetch(s - 2);
+#pragma unroll
+      for (int u = 0; u < kBtPer; ++u) {
+        const int i = tid + 256 * u;
+        const double zi = i < d ? z[i] : 0.0;
+        a = fma(ca[u], zi, a);
+        b = fma(cb[u], zi, b);
+        g = fma(ca[u], cb[u], g);
+      }
     } else {
-      for (int i = s + 1 + tid; i < d; i += 256) z[i] -= tot * vr[i];
+      // v_{s-1} starts at column s, v_s at s + 1 (zeros below); a thread keeps the elements i = tid mod 256 for good
+      for (int i = i0(s); i < d; i += 256) {
+        const double x = va[i], y = vb[i], zi = z[i];
+        a = fma(x, zi, a);
+        b = fma(y, zi, b);
+        g = fma(x, y, g);
+      }
     }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      a += __shfl_xor_sync(0xffffffffu, a, o);
+      b += __shfl_xor_sync(0xffffffffu, b, o);
+      g += __shfl_xor_sync(0xffffffffu, g, o);
+    }
+    if (lane == 0) { red[par][0][warp] = a; red[par][1][warp] = b; red[par][2][warp] = g; }
     __syncthreads();
+    double A = 0.0, B = 0.0, G = 0.0;
+#pragma unroll
+    for (int wv = 0; wv < 8; ++wv) { A += red[par][0][wv]; B += red[par][1][wv]; G += red[par][2][wv]; }
+    par ^= 1;
+    const double fa = ta * A;
+    const double fb = tb * fma(-fa, G, B);
+    if (pre) {
+#pragma unroll
+      for (int u = 0; u < kBtPer; ++u) {
+        const int i = tid + 256 * u;
+        if (i < d) z[i] = fma(-fb, cb[u], fma(-fa, ca[u], z[i]));
+      }
+    } else {
+      for (int i = i0(s); i < d; i += 256) z[i] = fma(-fb, vb[i], fma(-fa, va[i], z[i]));
+    }
+    // every thread reads and writes only ITS elements of z; the partials alternate between two buffers, so one barrier
+    // per pair is enough (a warp that races ahead writes the other buffer; a third pair cannot start before the second's barrier)
   }
+  __syncthreads();
   for (int i = tid; i < d; i += 256) Z[(size_t)j * d + i] = z[i];
 }
 
