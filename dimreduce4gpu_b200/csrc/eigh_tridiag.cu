@@ -779,7 +779,7 @@ __device__ __forceinline__ double hash_uniform(unsigned a, unsigned b) {
 __global__ void __launch_bounds__(kInvThreads)
 invit_kernel(const double* __restrict__ diag, const double* __restrict__ off, int d, int k,
              const double* __restrict__ lam, const double* __restrict__ info, double* __restrict__ lam_out,
-             double* __restrict__ Z) {
+             double* __restrict__ Z, double* __restrict__ coef_g) {
   const int j0 = blockIdx.x;
   const double tnorm = info[0];
   const double ortol = kTightGap * tnorm;
@@ -797,7 +797,9 @@ invit_kernel(const double* __restrict__ diag, const double* __restrict__ off, in
   double* dg0 = z + d;      // diag - x (read-only during the factorisation)
   double* of0 = dg0 + d;    // off
   int* piv = reinterpret_cast<int*>(of0 + d);
-  double* coef = of0 + d + (d + 1) / 2;   // behind piv (d ints): Gram-Schmidt coefficients of a tight cluster, < k of them
+  // Gram-Schmidt coefficients of a tight cluster (fewer than k): behind piv (d ints) in shared memory, or - when
+  // 6.5 d + k doubles pass the 227 KB (d = 4096 with k > ~2300) - in a global array of k doubles, clusters being disjoint
+  double* coef = coef_g ? coef_g + j0 : of0 + d + (d + 1) / 2;
   __shared__ double red[kInvThreads / 32];
   const int tid = threadIdx.x;
   const double eps = DBL_EPSILON;
@@ -1269,6 +1271,7 @@ size_t eigh_topk_workspace_bytes(int d, int k) {
          + tri_r256((size_t)4 * d * 8)    // p' / published-row exchange
          + tri_r256((size_t)k * 8)        // lam
          + tri_r256((size_t)k * d * 8)    // inverse-iteration vectors before the loose-cluster Gram-Schmidt step
+         + tri_r256((size_t)k * 8)        // Gram-Schmidt coefficients of tight clusters when they do not fit shared memory
          + 256 + 256;                     // info, ctrl
 }
 
@@ -1285,6 +1288,7 @@ void launch_eigh_topk(Ctx& c, double* dA, int d, int k, double* dW, double* dVt,
   TriCtrl* ctrl = reinterpret_cast<TriCtrl*>(take(256));
   double* lam = reinterpret_cast<double*>(take((size_t)k * 8));
   double* Zraw = reinterpret_cast<double*>(take((size_t)k * d * 8));
+  double* coef_ws = reinterpret_cast<double*>(take((size_t)k * 8));
   DR4G_CUDA(cudaMemsetAsync(ctrl, 0, sizeof(TriCtrl), c.stream));
 
   // T1: d <= 512 runs inside one thread-block cluster (hardware barrier, DSMEM exchange); larger d uses
@@ -1363,13 +1367,16 @@ void launch_eigh_topk(Ctx& c, double* dA, int d, int k, double* dW, double* dVt,
     DR4G_CUDA(cudaFuncSetAttribute(bisect_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bs_smem));
   bisect_kernel<<<k, kBsThreads, bs_smem, c.stream>>>(diag, off, d, k, lam, info);
   // T3
-  const size_t iv_smem = (size_t)6 * d * sizeof(double) + (size_t)((d + 1) / 2) * sizeof(double) + (size_t)k * sizeof(double);
+  size_t iv_smem = (size_t)6 * d * sizeof(double) + (size_t)((d + 1) / 2) * sizeof(double);
   if (iv_smem > 227 * 1024)
-    fail("eigh_topk: d=%d k=%d needs %zu bytes of shared memory for the inverse iteration (limit 227 KB)", d, k, iv_smem);
+    fail("eigh_topk: d=%d needs %zu bytes of shared memory for the inverse iteration (limit 227 KB, d <= 4469)", d, iv_smem);
+  double* coef_g = nullptr;
+  if (iv_smem + (size_t)k * sizeof(double) <= 227 * 1024) iv_smem += (size_t)k * sizeof(double);
+  else coef_g = coef_ws;
   static PerDeviceMax iv_smem_set;
   if (iv_smem > 48 * 1024 && iv_smem_set.need(c.device, iv_smem))
     DR4G_CUDA(cudaFuncSetAttribute(invit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)iv_smem));
-  invit_kernel<<<k, kInvThreads, iv_smem, c.stream>>>(diag, off, d, k, lam, info, dW, Zraw);
+  invit_kernel<<<k, kInvThreads, iv_smem, c.stream>>>(diag, off, d, k, lam, info, dW, Zraw, coef_g);
   invit_orth_kernel<<<k, 256, (size_t)k * sizeof(double), c.stream>>>(lam, info, d, k, Zraw, dVt);
   // T4
   const size_t bt_smem = (size_t)d * sizeof(double);

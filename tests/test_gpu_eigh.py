@@ -51,7 +51,8 @@ def test_eigh_topk_matches_lapack(kind, d, k):
     assert np.max(np.abs(Vt @ Vt.T - np.eye(k))) < 1e-11
 
 
-@pytest.mark.parametrize("d,k,kind", [(1024, 64, "aniso"), (1030, 16, "lowrank"), (2048, 40, "aniso"), (4096, 100, "geom")])
+@pytest.mark.parametrize("d,k,kind", [(1024, 64, "aniso"), (1030, 16, "lowrank"), (2048, 40, "aniso"), (4096, 100, "geom"),
+                                      (4096, 2500, "lowrank4k")])
 def test_eigh_topk_large_d_matches_lapack(d, k, kind):
     """d > 512: the cooperative-grid tridiagonalisation (rows in shared memory at 1024, in L2 above), the inverse
     iteration at its shared-memory limit (d = 4096 = BASELINE config 5) and the CTA-per-vector back-transformation."""
@@ -59,7 +60,11 @@ def test_eigh_topk_large_d_matches_lapack(d, k, kind):
 
     import dimreduce4gpu_b200 as pkg
 
-    if kind == "geom":
+    if kind == "lowrank4k":   # k beyond the rank: a zero cluster whose Gram-Schmidt coefficients live in global memory
+        rng = np.random.default_rng(3)
+        B = rng.standard_normal((d, 2450))
+        A = B @ B.T
+    elif kind == "geom":
         rng = np.random.default_rng(d)
         X = rng.standard_normal((d + 200, d)) * np.geomspace(4.0, 0.5, d)
         A = X.T @ X
