@@ -1371,7 +1371,9 @@ void launch_eigh_topk(Ctx& c, double* dA, int d, int k, double* dW, double* dVt,
   if (iv_smem > 227 * 1024)
     fail("eigh_topk: d=%d needs %zu bytes of shared memory for the inverse iteration (limit 227 KB, d <= 4469)", d, iv_smem);
   double* coef_g = nullptr;
-  if (iv_smem + (size_t)k * sizeof(double) <= 227 * 1024) iv_smem += (size_t)k * sizeof(double);
+  // (k <= 512: 4 KB of shared memory at most; beyond that the coefficients would cost resident CTAs per SM - at
+  // k = d = 2100 one instead of two - for the sake of tight clusters, which are rare)
+  if (k <= 512 && iv_smem + (size_t)k * sizeof(double) <= 227 * 1024) iv_smem += (size_t)k * sizeof(double);
   else coef_g = coef_ws;
   static PerDeviceMax iv_smem_set;
   if (iv_smem > 48 * 1024 && iv_smem_set.need(c.device, iv_smem))
