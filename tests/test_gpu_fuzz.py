@@ -19,3 +19,14 @@ def test_random_shapes_around_the_dispatch_boundaries(seed, cases, dtype):
     r = subprocess.run([sys.executable, str(TOOL), str(seed), str(cases), dtype], capture_output=True, text=True, timeout=900)
     tail = "\n".join(ln for ln in r.stdout.splitlines() if not ln.startswith("ok "))
     assert r.returncode == 0 and "FUZZ PASSED" in r.stdout, tail[-3000:] + r.stderr[-2000:]
+
+
+HOST_TOOL = Path(__file__).resolve().parents[1] / "tools" / "fuzz_host.py"
+
+
+def test_random_shapes_through_the_host_pointer_symbols_around_the_staging_thresholds():
+    """numpy in, numpy out (pca_* / truncated_svd_*, fp32 and fp64): inputs around 8 / 12 / 24 / 40 MB, score arrays around 4 / 8 MB
+    - the sizes at which the pinned ring, the copy pool and the early page population switch on - against numpy fp64."""
+    r = subprocess.run([sys.executable, str(HOST_TOOL), "5", "40"], capture_output=True, text=True, timeout=900)
+    tail = "\n".join(ln for ln in r.stdout.splitlines() if not ln.startswith("ok "))
+    assert r.returncode == 0 and "HOSTFUZZ PASSED" in r.stdout, tail[-3000:] + r.stderr[-2000:]
