@@ -331,6 +331,13 @@ static void ctx_delete(CtxFull* c) {
   if (c->proj_buf) cudaFree(c->proj_buf);
   if (c->pad_buf) cudaFree(c->pad_buf);
   if (c->fold_buf) cudaFree(c->fold_buf);
+  for (int r = 0; r < kP2PMaxWorld; ++r) {
+    if (!c->p2p_peer[r]) continue;
+    if (r == c->rank) cudaFree(c->p2p_peer[r]);
+    else cudaIpcCloseMemHandle(c->p2p_peer[r]);
+    c->p2p_peer[r] = nullptr;
+  }
+  if (c->p2p_status_host) cudaFreeHost(const_cast<int*>(c->p2p_status_host));
   c->stage.release();
   if (c->switch_ev) cudaEventDestroy(c->switch_ev);
   c->sf.release();
@@ -635,16 +642,29 @@ static void fit_impl(Ctx& c, const T* dX, long long n_local, int d, int k, int c
   // [2] combine ranks, centre.  PCA: ONE all-gather of [G | s | q | n | c_r], re-based to the common shift and summed in
   // rank order on every rank (bit-identical everywhere).  TruncatedSVD has no shift: one all-reduce.
   const double* moments = packed;
+  c.last_exchange = 0;
   if (c.world > 1 && center) {
-    double* gathered = c.arena.take_n<double>((size_t)c.world * ext_count);
     double* merged = c.arena.take_n<double>(ext_count);
-    allgather_f64(c, packed, gathered, ext_count);
+    const double* gathered = nullptr;
+    if (c.p2p_status_host && *c.p2p_status_host != 0)
+      fail("peer-memory exchange: rank %d never arrived in an earlier exchange (waited 4 s)", *c.p2p_status_host - 1);
+    if (c.p2p_ready && c.exchange != 1 && (long long)ext_count <= c.p2p_cap) {
+      // ONE kernel: push the partials into every peer's buffer over NVLink, release a flag, wait for everybody's (p2p.cu)
+      gathered = launch_p2p_allgather(c, packed, (long long)ext_count);
+      c.last_exchange = 2;
+    } else {
+      double* g = c.arena.take_n<double>((size_t)c.world * ext_count);
+      allgather_f64(c, packed, g, ext_count);
+      gathered = g;
+      c.last_exchange = 1;
+    }
     launch_rebase_sum(c, gathered, c.world, d, merged);
     moments = merged;
     cnt = merged + dd + 2 * (size_t)d;
     shift_d_arg = cnt + 1;
   } else {
     allreduce_f64(c, packed, packed_count);
+    if (c.world > 1) c.last_exchange = 1;
   }
   double* C = c.arena.take_n<double>(dd);
   launch_center(c, moments, d, center, shift_d_arg, C, mean_d, total_var);
@@ -1117,6 +1137,7 @@ int dr4g_set_option(dr4g_ctx* ctx, const char* key, double value) {
   else if (k == "timing") ctx->timing = (int)value;
   else if (k == "eig_solver") ctx->eig_solver = (int)value;
   else if (k == "fold") ctx->fold = (int)value;
+  else if (k == "exchange") ctx->exchange = (int)value;
   else fail("unknown option '%s'", key);
   DR4G_API_END
 }
@@ -1153,6 +1174,58 @@ int dr4g_comm_init(dr4g_ctx* ctx, const void* unique_id128, int rank, int world)
 }
 
 int dr4g_comm_world(dr4g_ctx* ctx) { return ctx ? ctx->world : 0; }
+
+int dr4g_p2p_prepare(dr4g_ctx* ctx, long long capacity_doubles, void* out_handle64) {
+  DR4G_API_BEGIN
+  if (!ctx || !out_handle64) fail("null argument");
+  if (ctx->world < 2 || ctx->world > kP2PMaxWorld) fail("dr4g_p2p_prepare: needs a communicator of 2..%d ranks (dr4g_comm_init first)", kP2PMaxWorld);
+  if (capacity_doubles < 1) fail("dr4g_p2p_prepare: bad capacity");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  DeviceGuard g(ctx->device);
+  if (ctx->p2p_peer[ctx->rank]) fail("dr4g_p2p_prepare: already prepared");
+  const size_t bytes = p2p_buffer_doubles(ctx->world, capacity_doubles) * sizeof(double);
+  void* buf = nullptr;
+  DR4G_CUDA(cudaMalloc(&buf, bytes));
+  DR4G_CUDA(cudaMemset(buf, 0, bytes));
+  cudaIpcMemHandle_t h;
+  cudaError_t e = cudaIpcGetMemHandle(&h, buf);
+  if (e != cudaSuccess) { cudaFree(buf); cudaGetLastError(); fail("cudaIpcGetMemHandle: %s", cudaGetErrorString(e)); }
+  if (!ctx->p2p_status_host) {
+    int* hs = nullptr;
+    DR4G_CUDA(cudaHostAlloc(&hs, 64, cudaHostAllocMapped));
+    *hs = 0;
+    int* ds = nullptr;
+    DR4G_CUDA(cudaHostGetDevicePointer(&ds, hs, 0));
+    ctx->p2p_status_host = hs;
+    ctx->p2p_status = ds;
+  }
+  ctx->p2p_peer[ctx->rank] = static_cast<double*>(buf);
+  ctx->p2p_cap = capacity_doubles;
+  std::memcpy(out_handle64, &h, sizeof(h));
+  DR4G_API_END
+}
+
+int dr4g_p2p_connect(dr4g_ctx* ctx, const void* handles) {
+  DR4G_API_BEGIN
+  if (!ctx || !handles) fail("null argument");
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  DeviceGuard g(ctx->device);
+  if (!ctx->p2p_peer[ctx->rank]) fail("dr4g_p2p_connect: dr4g_p2p_prepare first");
+  for (int r = 0; r < ctx->world; ++r) {
+    if (r == ctx->rank || ctx->p2p_peer[r]) continue;
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, static_cast<const char*>(handles) + (size_t)r * sizeof(h), sizeof(h));
+    void* p = nullptr;
+    cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) { cudaGetLastError(); fail("cudaIpcOpenMemHandle (rank %d): %s", r, cudaGetErrorString(e)); }
+    ctx->p2p_peer[r] = static_cast<double*>(p);
+  }
+  ctx->p2p_ready = true;
+  DR4G_API_END
+}
+
+int dr4g_last_exchange_path(dr4g_ctx* ctx) { return ctx ? ctx->last_exchange : 0; }
 
 #define DR4G_FIT(NAME, T)                                                                                   \
   int NAME(dr4g_ctx* ctx, const T* dX, long long n_local, int d, int k, int center, params p, T* dQ, T* dw,  \

@@ -53,6 +53,8 @@ struct Arena {
   void release();
 };
 
+constexpr int kP2PMaxWorld = 16;   // ranks of one NVSwitch box the peer-memory exchange (p2p.cu) can address
+
 struct Ctx {
   int device = 0;
   int sm_count = 148;
@@ -71,6 +73,15 @@ struct Ctx {
   // NCCL
   void* comm = nullptr;
   int rank = 0, world = 1;
+  // peer-memory exchange (p2p.cu): every rank's exchange buffer mapped here (own buffer at [rank])
+  bool p2p_ready = false;
+  long long p2p_cap = 0;                 // doubles per slot
+  double* p2p_peer[kP2PMaxWorld] = {};
+  unsigned long long p2p_epoch = 0;
+  int* p2p_status = nullptr;             // device view of a mapped host word: != 0 after a wait that gave up
+  volatile int* p2p_status_host = nullptr;
+  int exchange = 0;                      // 0 auto (peer memory when set up and the payload fits), 1 NCCL only
+  int last_exchange = 0;                 // 0 none, 1 NCCL, 2 peer memory
   // options
   int gram_path = 0;          // 0 auto, 1 generic, 2 tcgen05 (pair kernel where eligible), 3 tcgen05 single-CTA kernel only,
                               // 5 first-generation 64 x 64 DMMA kernel for fp64 input too (cross-check of gram_f64.cu)
@@ -145,6 +156,9 @@ void launch_add_f64(Ctx& c, double* acc, const double* x, size_t count);  // acc
 // gathered: world x (d*d + 3d + 1) doubles [G | s | q | n | c_r] of every rank; out (same layout) <- moments re-based to the
 // common shift and summed in rank order (finalize.cu)
 void launch_rebase_sum(Ctx& c, const double* gathered, int world, int d, double* out);
+// exchange over NVLink peer memory (p2p.cu)
+size_t p2p_buffer_doubles(int world, long long cap);
+const double* launch_p2p_allgather(Ctx& c, const double* src, long long count);
 void launch_center(Ctx& c, const double* packed, int d, int center, const double* shift_d,
                    double* dC /* d x d, may alias packed G */, double* dmean, double* dtotal_var);
 

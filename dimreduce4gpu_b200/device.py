@@ -121,6 +121,27 @@ class DeviceContext:
         dist.broadcast_object_list(uid, src=0)
         with torch.cuda.device(self.device):
             self.init_comm(uid[0], rank, world)
+            self._init_p2p(dist, rank, world)
+
+    def _init_p2p(self, dist, rank: int, world: int) -> None:
+        """Peer-memory exchange (csrc/p2p.cu) when every rank can map every other rank's buffer (one NVSwitch box);
+        any failure on any rank leaves all ranks on NCCL.  DR4G_P2P_MAX_D (default 1024, 0 = off) sizes the buffers."""
+        import os
+
+        max_d = int(os.environ.get("DR4G_P2P_MAX_D", "1024"))
+        handle = ctypes.create_string_buffer(64)
+        ok = 0 < max_d and 2 <= world <= 16
+        if ok:
+            ok = self._lib.dr4g_p2p_prepare(self._h, max_d * max_d + 3 * max_d + 1, handle) == 0
+        got = [None] * world
+        dist.all_gather_object(got, (bool(ok), handle.raw))
+        if not all(g[0] for g in got):
+            return
+        ok = self._lib.dr4g_p2p_connect(self._h, b"".join(g[1] for g in got)) == 0
+        got = [None] * world
+        dist.all_gather_object(got, bool(ok))
+        if not all(got):
+            self.set_option("exchange", 1)   # somebody could not map a peer: everybody stays on NCCL
 
     # ------------------------------------------------------------------ fit / transform
     @_serialized
@@ -385,6 +406,10 @@ class DeviceContext:
     @property
     def last_gram_path(self) -> str:
         return {0: "none", 1: "generic_dmma", 2: "tcgen05", 3: "tcgen05_pair", 4: "tcgen05_pair_bf16x3", 5: "dmma_f64_128"}[int(self._lib.dr4g_last_gram_path(self._h))]
+
+    @property
+    def last_exchange_path(self) -> str:
+        return {0: "none", 1: "nccl", 2: "peer_memory"}[int(self._lib.dr4g_last_exchange_path(self._h))]
 
     @property
     def last_fold(self) -> int:

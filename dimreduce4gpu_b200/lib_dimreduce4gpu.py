@@ -71,6 +71,9 @@ def _bind(lib: ctypes.CDLL) -> None:
     lib.dr4g_last_gram_path.argtypes, lib.dr4g_last_gram_path.restype = [vp], ci
     lib.dr4g_last_proj_path.argtypes, lib.dr4g_last_proj_path.restype = [vp], ci
     lib.dr4g_last_fold.argtypes, lib.dr4g_last_fold.restype = [vp], ci
+    lib.dr4g_p2p_prepare.argtypes, lib.dr4g_p2p_prepare.restype = [vp, ctypes.c_longlong, vp], ci
+    lib.dr4g_p2p_connect.argtypes, lib.dr4g_p2p_connect.restype = [vp, vp], ci
+    lib.dr4g_last_exchange_path.argtypes, lib.dr4g_last_exchange_path.restype = [vp], ci
     lib.dr4g_launch_count.argtypes, lib.dr4g_launch_count.restype = [vp], ll
     lib.dr4g_partial_fit_reset.argtypes, lib.dr4g_partial_fit_reset.restype = [vp], ci
     lib.dr4g_partial_fit_rows.argtypes, lib.dr4g_partial_fit_rows.restype = [vp], ll
@@ -86,6 +89,7 @@ EXPORTED_SYMBOLS = (
     "dr4g_colstats_double", "dr4g_gram_float", "dr4g_gram_double", "dr4g_eigh_double", "dr4g_eigh_topk_double", "dr4g_stage_times",
     "dr4g_last_gram_path", "dr4g_last_proj_path", "dr4g_last_fold", "dr4g_launch_count",
     "dr4g_eigh_topk_static_double", "dr4g_eigh_topk_static_max_d",
+    "dr4g_p2p_prepare", "dr4g_p2p_connect", "dr4g_last_exchange_path",
     "dr4g_fit_transform_host_float", "dr4g_fit_transform_host_double",
     "dr4g_csr_to_dense_float", "dr4g_csr_to_dense_double",
     "dr4g_partial_fit_float", "dr4g_partial_fit_double", "dr4g_partial_fit_finalize_float",

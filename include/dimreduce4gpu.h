@@ -104,6 +104,15 @@ DR4G_EXPORT int dr4g_set_option(dr4g_ctx* ctx, const char* key, double value);
 DR4G_EXPORT int dr4g_nccl_unique_id(void* out128);
 DR4G_EXPORT int dr4g_comm_init(dr4g_ctx* ctx, const void* unique_id128, int rank, int world);
 DR4G_EXPORT int dr4g_comm_world(dr4g_ctx* ctx);
+/* Exchange over NVLink peer memory instead of NCCL (one NVSwitch box, one process per GPU; csrc/p2p.cu): after dr4g_comm_init
+ * every rank calls dr4g_p2p_prepare (allocates its exchange buffer for payloads of up to capacity_doubles = d^2 + 3 d + 1 doubles
+ * and returns its 64-byte cudaIpcMemHandle), the host layer all-gathers the handles, every rank calls dr4g_p2p_connect with the
+ * world x 64 bytes in rank order.  From then on the centred (PCA) fit exchanges its partials with ONE kernel that pushes them
+ * into every peer's buffer, releases a flag and waits for the peers' flags; larger payloads, the uncentred fit and
+ * option "exchange" = 1 keep NCCL.  dr4g_last_exchange_path: 0 none, 1 NCCL, 2 peer memory. */
+DR4G_EXPORT int dr4g_p2p_prepare(dr4g_ctx* ctx, long long capacity_doubles, void* out_handle64);
+DR4G_EXPORT int dr4g_p2p_connect(dr4g_ctx* ctx, const void* handles);
+DR4G_EXPORT int dr4g_last_exchange_path(dr4g_ctx* ctx);
 
 /* fit on a device-resident row shard.  dX: n_local x d row-major on ctx's device.  center=1 ->
  * PCA (covariance of centred data), 0 -> TruncatedSVD.  p supplies algorithm / n_iter /

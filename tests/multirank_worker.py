@@ -102,6 +102,24 @@ def main() -> None:
         if alg == "cusolver":   # shard-local scores of the exact model (the flat spectrum leaves 'power' a rotated basis)
             Z = ctx.transform(Xg, res["components"], mean=res["mean"]).cpu().numpy()
         progress(f"sharded fit {alg} done")
+    # the exchange ran as ONE kernel over NVLink peer memory (csrc/p2p.cu); NCCL's all-gather gives the same bits
+    path = ctx.last_exchange_path
+    progress(f"exchange path: {path}")
+    if os.environ.get("DR4G_P2P_MAX_D", "1024") != "0":
+        assert path == "peer_memory", f"exchange went through {path}"
+        ctx.set_option("exchange", 1)
+        res_n = ctx.fit(Xg, k, center=True, algorithm="cusolver")
+        ctx.sync()
+        assert ctx.last_exchange_path == "nccl"
+        for name in ("components", "singular_values", "explained_variance_ratio", "mean"):
+            assert np.array_equal(res_n[name].cpu().numpy(), out["cusolver"][name]), f"{name}: peer-memory and NCCL exchange differ"
+        ctx.set_option("exchange", 0)
+        for _ in range(5):   # repeated exchanges: both parities of the buffers, epochs in step on all ranks
+            res_p = ctx.fit(Xg, k, center=True, algorithm="cusolver")
+        ctx.sync()
+        assert ctx.last_exchange_path == "peer_memory"
+        assert np.array_equal(res_p["components"].cpu().numpy(), out["cusolver"]["components"])
+        progress("peer-memory exchange checked against NCCL")
     # streaming fit across ranks: every rank feeds its shard in two chunks (the first call carries the pilot
     # allreduce), finalize all-reduces the packed accumulators: same model as the one-pass sharded fit
     progress("transform done")
