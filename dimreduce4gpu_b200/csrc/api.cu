@@ -1119,6 +1119,8 @@ int dr4g_sync(dr4g_ctx* ctx) {
   if (!ctx) fail("null context");
   DeviceGuard g(ctx->device);
   DR4G_CUDA(cudaStreamSynchronize(ctx->stream));
+  if (ctx->p2p_status_host && *ctx->p2p_status_host != 0)
+    fail("peer-memory exchange: rank %d never arrived (waited 4 s); results of the last sharded fit are invalid", *ctx->p2p_status_host - 1);
   DR4G_API_END
 }
 
