@@ -39,3 +39,14 @@ def test_two_gpus_nccl_sharded_fit_matches_reference():
         pytest.skip("needs 2 GPUs on the box")
     out = _launch("gpu", 40000, 256, 16, 240)
     assert "MULTIRANK_GPU_OK" in out
+
+
+@pytest.mark.gpu
+def test_two_gpus_row_folded_narrow_shards_match_reference():
+    """d = 32 shards of 600,000 rows: each rank's pass is row-folded 8-fold; the sharded model against the reference backend."""
+    import torch
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs on the box")
+    out = _launch("gpu-fold", 600000, 32, 8, 300)
+    assert "MULTIRANK_FOLD_OK" in out
