@@ -397,6 +397,19 @@ static int gram_fold_factor(const Ctx& c, const float* dX, long long n, int d) {
   if (n / f < 1 || !gram_tc_eligible(c, dX, n / f, f * d)) return 0;
   return f;
 }
+// fp64: the same fold onto gram_f64.cu's 128 x 128 DMMA tiles.  That kernel spends the fp64 pipe on a full 128-wide tile
+// whatever d is (4M x 64: 11.4 ms, 8M x 32: 22 ms, 16M x 16: 44 ms for 2 GiB each); folded to 256 columns they all take the
+// three tiles of a 256-column problem on n / f rows (~4.3 ms).  f d must be even (16-byte rows for cp.async).
+static int gram_fold_factor(const Ctx& c, const double* dX, long long n, int d) {
+  if (!c.fold || c.gram_path != 0 || d < 1 || d > 128) return 0;
+  if ((reinterpret_cast<uintptr_t>(dX) & 15) != 0) return 0;
+  if ((double)n * (double)d < 8388608.0) return 0;
+  const int step = d % 2 == 0 ? 1 : 2;
+  const int f = (256 / d) / step * step;
+  if (f < 2 || f * d <= 128) return 0;
+  if (n / f < 1 || !gram_f64_eligible(c, dX, n / f, f * d)) return 0;
+  return f;
+}
 template <typename T>
 static void fit_impl(Ctx& c, const T* dX, long long n_local, int d, int k, int center, const params& p, T* dQ,
                      T* dw, T* dev, T* devr, T* dmean, StreamFit* sf = nullptr, int phase = 0) {
@@ -454,6 +467,13 @@ static void fit_impl(Ctx& c, const T* dX, long long n_local, int d, int k, int c
       const size_t df = (size_t)fold * d;
       need += up256(df * df * 8) + up256(2 * df * 8) + up256(df * 4) + up256(dd * 8) + up256((size_t)2 * d * 8) +
               up256(gram_tc_workspace_bytes(c, (int)df)) + 2048;
+    }
+  } else {
+    if (phase != 2) fold = gram_fold_factor(c, reinterpret_cast<const double*>(dX), n_local, d);
+    if (fold) {
+      const size_t df = (size_t)fold * d;
+      need += up256(df * df * 8) + up256(df * 8) + up256(dd * 8) + up256(gram_f64_workspace_bytes(c, n_local / fold, (int)df)) + 2048;
+      want_f64 = false;   // the folded pass replaces the unfolded one
     }
   }
   int dpad = 0;
@@ -561,6 +581,34 @@ static void fit_impl(Ctx& c, const T* dX, long long n_local, int d, int k, int c
                             tail > 0 ? sqt + d : nullptr, G, s, q);
       padded_done = true;
       used_tc = true;
+      c.last_fold = fold;
+    } else {
+      const int df = fold * d;
+      const long long nf = n_local / fold, tail = n_local - nf * fold;
+      const double* Xd = reinterpret_cast<const double*>(dX);
+      const double* shd = reinterpret_cast<const double*>(shift_arg);
+      double* Gf = c.arena.take_n<double>((size_t)df * df);
+      double* shf = c.arena.take_n<double>(df);
+      double* Gt = c.arena.take_n<double>(dd);
+      void* ws = c.arena.take(gram_f64_workspace_bytes(c, nf, df));
+      // s and q: one column-statistics pass over the rows as they are (K1); G: the folded rows on the DMMA tiles
+      launch_colstats<double>(c, Xd, n_local, d, shd, s, q);
+      DR4G_CUDA(cudaMemsetAsync(Gf, 0, (size_t)df * df * 8, c.stream));
+      const double* shf_arg = nullptr;
+      if (shd) {
+        launch_tile_shift(c, shd, d, fold, shf);
+        shf_arg = shf;
+      }
+      launch_gram_f64(c, Xd, nf, df, shf_arg, Gf, ws);
+      launch_mirror_upper(c, Gf, df);   // a d x d diagonal block may straddle two 128-column tiles
+      if (tail > 0) {
+        DR4G_CUDA(cudaMemsetAsync(Gt, 0, dd * 8, c.stream));
+        launch_gram_generic<double>(c, Xd + (size_t)nf * df, tail, d, shd, Gt);
+        launch_mirror_upper(c, Gt, d);
+      }
+      launch_unfold_moments(c, Gf, nullptr, nullptr, d, fold, tail > 0 ? Gt : nullptr, nullptr, nullptr, G, nullptr, nullptr);
+      padded_done = true;
+      c.last_gram_kernel = 4;
       c.last_fold = fold;
     }
   }

@@ -170,6 +170,7 @@ void launch_jacobi(Ctx& c, double* dA, double* dV, int dp, double* dW, void* wor
 void launch_pad_copy(Ctx& c, const double* src, int d, double* dst, int dp);
 // row folding of narrow fp32 inputs (finalize.cu): shift tiled f times; moments of the folded problem -> G, s, q
 void launch_tile_shift(Ctx& c, const float* shift, int d, int f, float* out);
+void launch_tile_shift(Ctx& c, const double* shift, int d, int f, double* out);
 void launch_unfold_moments(Ctx& c, const double* Gf, const double* sf, const double* qf, int d, int f, const double* Gt,
                            const double* st, const double* qt, double* G, double* s, double* q);
 template <typename T>

@@ -215,7 +215,8 @@ void launch_pad_copy(Ctx& c, const double* src, int d, double* dst, int dp) {
 // problem they are built for, whatever d is (their time per row does not depend on d <= 128, so d = 8 ran at 0.2 TB/s).
 // The Gram of the folded matrix holds G in its f diagonal d x d blocks (the other blocks are products of different
 // rows: ignored), the folded column statistics hold s and q in f pieces.
-__global__ void tile_shift_kernel(const float* __restrict__ shift, int d, int f, float* __restrict__ out) {
+template <typename T>
+__global__ void tile_shift_kernel(const T* __restrict__ shift, int d, int f, T* __restrict__ out) {
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e < f * d) out[e] = shift[e % d];
 }
@@ -231,7 +232,7 @@ __global__ void unfold_moments_kernel(const double* __restrict__ Gf, const doubl
   double a = Gt ? Gt[(size_t)i * d + j] : 0.0;
   for (int g = 0; g < f; ++g) a += Gf[((size_t)g * d + i) * df + (size_t)g * d + j];
   G[(size_t)i * d + j] = a;
-  if (i == 0) {
+  if (i == 0 && sf != nullptr) {   // (the fp64 fold takes s and q from a column-statistics pass over the unfolded rows)
     double b = st ? st[j] : 0.0, cq = qt ? qt[j] : 0.0;
     for (int g = 0; g < f; ++g) { b += sf[(size_t)g * d + j]; cq += qf[(size_t)g * d + j]; }
     s[j] = b;
@@ -240,7 +241,12 @@ __global__ void unfold_moments_kernel(const double* __restrict__ Gf, const doubl
 }
 
 void launch_tile_shift(Ctx& c, const float* shift, int d, int f, float* out) {
-  tile_shift_kernel<<<ceil_div(f * d, 256), 256, 0, c.stream>>>(shift, d, f, out);
+  tile_shift_kernel<float><<<ceil_div(f * d, 256), 256, 0, c.stream>>>(shift, d, f, out);
+  c.launches++;
+  DR4G_CUDA(cudaGetLastError());
+}
+void launch_tile_shift(Ctx& c, const double* shift, int d, int f, double* out) {
+  tile_shift_kernel<double><<<ceil_div(f * d, 256), 256, 0, c.stream>>>(shift, d, f, out);
   c.launches++;
   DR4G_CUDA(cudaGetLastError());
 }

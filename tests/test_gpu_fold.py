@@ -167,3 +167,36 @@ def test_folded_projection_matches_fp64_and_the_unfolded_kernel(n, d, k, f, cent
     msg = f"n={n} d={d} k={k} f={f}: Z {ez:.2e}, U {eu:.2e} vs fp64; folded vs unfolded {e0:.2e}"
     assert ez < 2e-5 and eu < 2e-5 and e0 < 2e-5, msg
     assert float((U - U0).abs().max()) / scale < 2e-5, msg
+
+
+@pytest.mark.parametrize("center", [True, False], ids=["pca", "tsvd"])
+@pytest.mark.parametrize("n,d,k,f", [(131072 + 3, 64, 8, 4), (300007, 32, 6, 8), (600011, 15, 4, 16), (70000, 128, 12, 2),
+                                     (200001, 45, 5, 4), (8388608 + 5, 1, 1, 256), (60000, 129, 5, 0)])
+def test_folded_fp64_fit_matches_unfolded_fit_and_fp64_eigenvalues(n, d, k, f, center):
+    """fp64 inputs with d <= 128 and n d >= 2^23: f rows as one row of f d <= 256 columns on the 128 x 128 DMMA tiles
+    (csrc/api.cu: gram_fold_factor for double); gates of the fp64 path: 1e-10 on sigma (BASELINE.json north_star)."""
+    import torch
+
+    import dimreduce4gpu_b200 as pkg
+
+    X = _data(n, d, 11 * d + k, offset=center).double()
+    X = (X + 1e-3 * torch.randn(n, d, device="cuda", dtype=torch.float64, generator=torch.Generator(device="cuda").manual_seed(n))).contiguous()
+    ctx = pkg.DeviceContext(0)
+    a = _np(ctx.fit(X, k, center=center, algorithm="cusolver"))
+    ctx.sync()
+    assert ctx.last_fold == f, f"fold factor {ctx.last_fold}, expected {f}"
+    ctx.set_option("fold", 0)
+    b = _np(ctx.fit(X, k, center=center, algorithm="cusolver"))
+    ctx.sync()
+    assert ctx.last_fold == 0
+    mu = X.mean(0) if center else torch.zeros(d, device="cuda", dtype=torch.float64)
+    ev = torch.linalg.eigvalsh((X - mu).T @ (X - mu)).flip(0)[:k].clamp(min=0).sqrt().cpu().numpy()
+    e_ab = _rel(a["singular_values"], b["singular_values"])
+    e_ref = _rel(a["singular_values"], ev)
+    msg = f"n={n} d={d} k={k} f={f}: sigma folded vs unfolded {e_ab:.1e}, vs fp64 eigenvalues {e_ref:.1e}"
+    assert e_ab < 1e-11 and e_ref < 1e-10, msg
+    assert _rel(a["explained_variance_ratio"], b["explained_variance_ratio"]) < 1e-11, msg
+    if center:
+        assert np.max(np.abs(a["mean"] - mu.cpu().numpy())) < 1e-12 * (1 + float(mu.abs().max())), msg
+    if d > 1 and k < d:
+        assert O.max_principal_angle(a["components"], b["components"]) < 1e-8, msg
