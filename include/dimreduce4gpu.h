@@ -89,8 +89,8 @@ DR4G_EXPORT int dr4g_sync(dr4g_ctx* ctx);
  * src/cpu_backend.cpp:347; 0 = off),
  * "proj_path" (projection: 0 auto = tensor cores where eligible except fp32 inputs of <= 262144 elements, 1 CUDA-core kernels,
  * 2 tensor cores wherever eligible),
- * "fold" (1 = default: fp32 inputs with d <= 128 and n d >= 2^24 are streamed f rows at a time as rows of f d <= 256 columns;
- * 0 = off),
+ * "fold" (1 = default: inputs with d <= 128 and n d >= 2^24 (fp32) / 2^23 (fp64) are streamed f rows at a time as rows of
+ * f d <= 256 columns; 0 = off),
  * "gram_split" (CTA-pair kernel operands: 0 auto = 2 bf16x3 on kind::f16, 1 = 3xTF32 on kind::tf32),
  * "flush_rows" (rows between TMEM accumulator flushes), "pilot_rows", "jacobi_tol", "jacobi_sweeps",
  * "eig_solver" (exact path: 0 tridiagonal route for the top k, 1 blocked Jacobi), "timing". */
