@@ -117,3 +117,24 @@ def test_product_never_imports_oracle():
         assert not pat.search(py.read_text()), py
     for cu in (ROOT / "dimreduce4gpu_b200" / "csrc").glob("*"):
         assert "libdimreduce4cpu" not in cu.read_text(), cu
+
+
+def test_library_path_cache_follows_the_environment_variable(lib_path, monkeypatch, tmp_path):
+    """get_library_path() remembers a hit per value of DIMREDUCE4GPU_LIB_PATH (the reference re-walks the directories on
+    every call, _native.py:37-50): changing the variable must still be honoured, and a miss is not remembered."""
+    from dimreduce4gpu_b200 import _native
+
+    from pathlib import Path
+
+    monkeypatch.delenv("DIMREDUCE4GPU_LIB_PATH", raising=False)
+    default = _native.get_library_path()
+    assert default == str(lib_path)
+    assert _native.get_library_path() == default   # cached hit
+    copy = tmp_path / "libdimreduce4gpu.so"
+    copy.write_bytes(Path(lib_path).read_bytes())
+    monkeypatch.setenv("DIMREDUCE4GPU_LIB_PATH", str(copy))
+    assert _native.get_library_path() == str(copy)
+    monkeypatch.setenv("DIMREDUCE4GPU_LIB_PATH", str(tmp_path / "nowhere"))
+    assert _native.get_library_path() == default          # falls through to the package directory, like the reference
+    monkeypatch.delenv("DIMREDUCE4GPU_LIB_PATH")
+    assert _native.get_library_path() == default
